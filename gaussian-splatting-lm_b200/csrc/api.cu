@@ -1,0 +1,230 @@
+// =============================================================================
+// api.cu -- the C ABI (include/gslm_b200.h): orchestration of the stages, one function per
+// entry point of the reference binding (DGR/rasterize_points.cu) plus the cached CG path.
+// No device memory is allocated here; no torch types anywhere.
+// =============================================================================
+#include "gslm_common.cuh"
+#include <cstring>
+
+using namespace gslm;
+
+static TangentPtrs make_tangents(const GslmGaussians* gt, const GslmCameraTangent* ct) {
+    TangentPtrs t;
+    memset(&t, 0, sizeof(t));
+    if (gt) {
+        t.means3D = gt->means3D; t.opacities = gt->opacities; t.scales = gt->scales; t.rotations = gt->rotations;
+        t.cov3D_precomp = gt->cov3D_precomp; t.shs = gt->shs; t.colors_precomp = gt->colors_precomp;
+    }
+    if (ct) {
+        t.viewmatrix = ct->viewmatrix; t.projmatrix = ct->projmatrix; t.campos = ct->campos;
+        t.tan_fovx = ct->tan_fovx; t.tan_fovy = ct->tan_fovy; t.scale_modifier = ct->scale_modifier;
+    }
+    return t;
+}
+
+static int check_inputs(const GslmGaussians* g, const GslmCamera* cam) {
+    if (!g || !cam) { set_error("null argument"); return 1; }
+    if (g->P < 0 || cam->width <= 0 || cam->height <= 0) { set_error("bad sizes"); return 1; }
+    if (g->P > 0) {
+        if (!g->means3D || !g->opacities) { set_error("means3D / opacities missing"); return 1; }
+        // rasterizer_impl.cu:285-288 / __init__.py:322-326
+        if (!g->shs && !g->colors_precomp) { set_error("For non-RGB, provide precomputed Gaussian colors!"); return 1; }
+        if (!g->cov3D_precomp && (!g->scales || !g->rotations)) {
+            set_error("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
+            return 1;
+        }
+        if (g->shs && !g->colors_precomp) {
+            const int need = (g->sh_degree + 1) * (g->sh_degree + 1);
+            if (g->sh_degree < 0 || g->sh_degree > 3 || g->M < need) { set_error("sh_degree / M mismatch"); return 1; }
+        }
+    }
+    if (!cam->bg || !cam->viewmatrix || !cam->projmatrix) { set_error("camera pointers missing"); return 1; }
+    return 0;
+}
+
+static int debug_sync(const GslmCamera* cam, cudaStream_t s, const char* what) {
+    if (cam->debug) {   // auxiliary.h:262-269 CHECK_CUDA
+        cudaError_t e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) { set_error("%s: %s", what, cudaGetErrorString(e)); return 1; }
+    }
+    return 0;
+}
+
+extern "C" {
+
+const char* gslm_last_error(void) { return last_error(); }
+int32_t gslm_abi_version(void) { return 1; }
+
+size_t gslm_geom_bytes(int32_t P) { return carve_geom(nullptr, P).total; }
+size_t gslm_image_bytes(int32_t width, int32_t height) { return carve_image(nullptr, width, height).total; }
+size_t gslm_binning_bytes(int64_t R) { return carve_binning(nullptr, R).total; }
+size_t gslm_backward_scratch_bytes(int64_t R) { return align_up((size_t)R * REC_F4 * sizeof(float4)) + 128; }
+size_t gslm_jvp_scratch_bytes(int32_t P) { return align_up((size_t)P * REC_F4 * sizeof(float4)) + 128; }
+size_t gslm_jtjv_scratch_bytes(int32_t P, int64_t R) {
+    return gslm_jvp_scratch_bytes(P) + gslm_backward_scratch_bytes(R);
+}
+
+int32_t gslm_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                          uint8_t* present, void* stream) {
+    (void)projmatrix;
+    if (P > 0 && (!means3D || !viewmatrix || !present)) { set_error("null argument"); return 1; }
+    return launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
+}
+
+int32_t gslm_forward(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn alloc, void* alloc_ctx,
+                     float* out_color, float* out_invdepth, int32_t* radii, int32_t* num_rendered, void* stream) {
+    if (check_inputs(g, cam)) return 1;
+    if (!alloc || !out_color || !num_rendered || (g->P > 0 && !radii)) { set_error("null argument"); return 1; }
+    cudaStream_t s = (cudaStream_t)stream;
+    const int P = g->P, W = cam->width, H = cam->height;
+    void* gbuf = alloc(alloc_ctx, GSLM_BUF_GEOM, gslm_geom_bytes(P));
+    void* ibuf = alloc(alloc_ctx, GSLM_BUF_IMAGE, gslm_image_bytes(W, H));
+    if (!gbuf || !ibuf) { set_error("allocator returned null"); return 1; }
+    GeomView gv = carve_geom(gbuf, P);
+    ImageView iv = carve_image(ibuf, W, H);
+    uint32_t R = 0;
+    if (P > 0) {
+        if (launch_preprocess(*g, *cam, gv, radii, s)) return 1;
+        if (debug_sync(cam, s, "preprocess")) return 1;
+        if (run_scan(gv, P, s)) return 1;
+        // rasterizer_impl.cu:325 -- the one host synchronisation of the uncached path
+        GSLM_CUDA_OK(cudaMemcpyAsync(&R, gv.point_offsets + (P - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        GSLM_CUDA_OK(cudaStreamSynchronize(s));
+    }
+    *num_rendered = (int32_t)R;
+    void* bbuf = alloc(alloc_ctx, GSLM_BUF_BINNING, gslm_binning_bytes(R));
+    if (!bbuf) { set_error("allocator returned null"); return 1; }
+    BinningView bv = carve_binning(bbuf, R);
+    const float* features = g->colors_precomp ? g->colors_precomp : gv.rgb;
+    if (run_binning(gv, radii, bv, iv, P, W, H, R, features, s)) return 1;
+    if (debug_sync(cam, s, "binning")) return 1;
+    if (launch_blend_fwd(bv, iv, W, H, cam->bg, out_color, out_invdepth, s)) return 1;
+    return debug_sync(cam, s, "render");
+}
+
+int32_t gslm_jvp_cached(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam, const int32_t* radii,
+                        const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
+                        int32_t num_rendered, void* scratch, float* out_color_tangent, float* out_invdepth_tangent,
+                        void* stream) {
+    if (check_inputs(g, cam)) return 1;
+    if (!out_color_tangent || !image_buffer || !binning_buffer || !scratch) { set_error("null argument"); return 1; }
+    cudaStream_t s = (cudaStream_t)stream;
+    ImageView iv = carve_image(const_cast<void*>(image_buffer), cam->width, cam->height);
+    BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_rendered);
+    float4* tgeom = reinterpret_cast<float4*>(align_up((size_t)scratch));
+    TangentPtrs t = make_tangents(gt, nullptr);
+    if (launch_preprocess_tangent(*g, t, *cam, radii, tgeom, s)) return 1;
+    if (launch_blend_jvp(bv, iv, cam->width, cam->height, tgeom, cam->bg, nullptr, out_color_tangent,
+                         out_invdepth_tangent, s)) return 1;
+    (void)geom_buffer;
+    return debug_sync(cam, s, "jvp_cached");
+}
+
+int32_t gslm_forward_jvp(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam,
+                         const GslmCameraTangent* camt, GslmAllocFn alloc, void* alloc_ctx, float* out_color,
+                         float* out_invdepth, int32_t* radii, float* out_color_tangent, float* out_invdepth_tangent,
+                         int32_t* num_rendered, void* stream) {
+    // rasterizer_jvp_impl.h:125-325 runs primal and tangent in one pass and then shrinks its
+    // buffers to the primal layout; here the primal pass IS the plain forward, followed by the
+    // tangent stages on the state it left behind.
+    struct Capture { GslmAllocFn fn; void* ctx; void* p[3]; } cap = {alloc, alloc_ctx, {nullptr, nullptr, nullptr}};
+    auto hook = [](void* c, int32_t which, size_t bytes) -> void* {
+        Capture* k = (Capture*)c;
+        void* r = k->fn(k->ctx, which, bytes);
+        if (which >= 0 && which < 3) k->p[which] = r;
+        return r;
+    };
+    if (!out_color_tangent) { set_error("null argument"); return 1; }
+    if (gslm_forward(g, cam, hook, &cap, out_color, out_invdepth, radii, num_rendered, stream)) return 1;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int P = g->P, W = cam->width, H = cam->height;
+    ImageView iv = carve_image(cap.p[GSLM_BUF_IMAGE], W, H);
+    BinningView bv = carve_binning(cap.p[GSLM_BUF_BINNING], *num_rendered);
+    // the tangent geometry (48 B per Gaussian) borrows the dead tail of the binning buffer when it
+    // fits, i.e. keys_unsorted (8 B per instance) -- otherwise a 4th allocation (which = 1 again
+    // would clobber the live buffer, so ask for geometry-class scratch with which = -1)
+    float4* tgeom = nullptr;
+    const size_t need = gslm_jvp_scratch_bytes(P);
+    const size_t dead = (size_t)((char*)bv.sort_temp + bv.sort_temp_bytes - (char*)bv.keys_unsorted);
+    if (dead >= need) tgeom = reinterpret_cast<float4*>(bv.keys_unsorted);
+    else {
+        void* extra = alloc(alloc_ctx, -1, need);
+        if (!extra) { set_error("allocator returned null"); return 1; }
+        tgeom = reinterpret_cast<float4*>(align_up((size_t)extra));
+    }
+    TangentPtrs t = make_tangents(gt, camt);
+    if (launch_preprocess_tangent(*g, t, *cam, radii, tgeom, s)) return 1;
+    if (launch_blend_jvp(bv, iv, W, H, tgeom, cam->bg, camt ? camt->bg : nullptr, out_color_tangent,
+                         out_invdepth_tangent, s)) return 1;
+    return debug_sync(cam, s, "forward_jvp");
+}
+
+int32_t gslm_backward(const GslmGaussians* g, const GslmCamera* cam, const int32_t* radii, const void* geom_buffer,
+                      const void* binning_buffer, const void* image_buffer, int32_t num_rendered,
+                      const float* dL_dcolor, const float* dL_dinvdepth, void* scratch, GslmGrads* grads,
+                      void* stream) {
+    if (check_inputs(g, cam)) return 1;
+    if (!grads || !dL_dcolor || !geom_buffer || !binning_buffer || !image_buffer || !scratch) {
+        set_error("null argument");
+        return 1;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    const int P = g->P, W = cam->width, H = cam->height;
+    if (P == 0) return 0;
+    GeomView gv = carve_geom(const_cast<void*>(geom_buffer), P);
+    ImageView iv = carve_image(const_cast<void*>(image_buffer), W, H);
+    BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_rendered);
+    float4* inst = reinterpret_cast<float4*>(align_up((size_t)scratch));
+    if (num_rendered > 0)
+        if (launch_blend_bwd(bv, iv, W, H, cam->bg, dL_dcolor, dL_dinvdepth, inst, s)) return 1;
+    if (debug_sync(cam, s, "render bwd")) return 1;
+    if (launch_preprocess_bwd(*g, *cam, radii, gv, bv, inst, dL_dinvdepth != nullptr, *grads, s)) return 1;
+    return debug_sync(cam, s, "preprocess bwd");
+}
+
+int32_t gslm_jtjv(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam, const int32_t* radii,
+                  const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
+                  int32_t num_rendered, const float* weight, void* scratch, GslmGrads* grads, float* out_vJJv,
+                  void* stream) {
+    if (check_inputs(g, cam)) return 1;
+    if (!grads || !geom_buffer || !binning_buffer || !image_buffer || !scratch) { set_error("null argument"); return 1; }
+    cudaStream_t s = (cudaStream_t)stream;
+    const int P = g->P, W = cam->width, H = cam->height;
+    if (P == 0) return 0;
+    GeomView gv = carve_geom(const_cast<void*>(geom_buffer), P);
+    ImageView iv = carve_image(const_cast<void*>(image_buffer), W, H);
+    BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_rendered);
+    float4* tgeom = reinterpret_cast<float4*>(align_up((size_t)scratch));
+    float4* inst = reinterpret_cast<float4*>((char*)tgeom + gslm_jvp_scratch_bytes(P) - 128);
+    inst = reinterpret_cast<float4*>(align_up((size_t)inst));
+    TangentPtrs t = make_tangents(gt, nullptr);
+    if (launch_preprocess_tangent(*g, t, *cam, radii, tgeom, s)) return 1;
+    if (num_rendered > 0)
+        if (launch_blend_jtjv(bv, iv, W, H, cam->bg, tgeom, weight, inst, out_vJJv, s)) return 1;
+    if (launch_preprocess_bwd(*g, *cam, radii, gv, bv, inst, false, *grads, s)) return 1;
+    return debug_sync(cam, s, "jtjv");
+}
+
+int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_rendered, const void* geom_buffer,
+                         const void* binning_buffer, const void* image_buffer, GslmBufferView* out) {
+    if (!out) { set_error("null argument"); return 1; }
+    memset(out, 0, sizeof(*out));
+    if (geom_buffer) {
+        GeomView gv = carve_geom(const_cast<void*>(geom_buffer), P);
+        out->tiles_touched = gv.tiles_touched; out->point_offsets = gv.point_offsets; out->depths = gv.depths;
+        out->means2D = reinterpret_cast<const float*>(gv.means2D);
+        out->conic_opacity = reinterpret_cast<const float*>(gv.conic_opacity);
+        out->rgb = gv.rgb; out->cov3D = gv.cov3D; out->clamped = gv.clamped;
+    }
+    if (binning_buffer) {
+        BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_rendered);
+        out->point_list = bv.point_list; out->keys_sorted = bv.keys_sorted;
+    }
+    if (image_buffer) {
+        ImageView iv = carve_image(const_cast<void*>(image_buffer), width, height);
+        out->ranges = reinterpret_cast<const uint32_t*>(iv.ranges); out->n_contrib = iv.n_contrib; out->final_T = iv.final_T;
+    }
+    return 0;
+}
+
+}  // extern "C"

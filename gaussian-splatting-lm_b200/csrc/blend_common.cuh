@@ -1,0 +1,139 @@
+// =============================================================================
+// blend_common.cuh -- building blocks of the tile kernels (a9, a11, a13, fused J^T J v).
+//
+// One CTA = one 16x16 tile, one thread = one pixel (as DGR/cuda_rasterizer/forward.cu:278-402).
+// What is different from the reference:
+//  * a tile's instances are contiguous 48-byte records (binning.cu), staged 256 at a time
+//    by ONE cp.async.bulk (TMA bulk copy, SASS UBLKCP) per batch into a 2-stage shared-memory
+//    ring guarded by mbarriers -- no per-thread gathers, colour / depth never fetched from
+//    global per hit (forward.cu:377,380);
+//  * alpha is evaluated by ONE rounding-exact instruction sequence (eval_alpha) shared by
+//    the primal, tangent and adjoint sweeps, so all three agree on every hit / skip
+//    decision whatever the surrounding code's FMA contraction;
+//  * the adjoint sweep pre-reduces its ten partials with a 12-shuffle recursive-halving
+//    warp reduction, merges warps in shared memory and writes ONE record per
+//    (tile, Gaussian) instance -- no global atomics (the reference does ten atomicAdd per
+//    (pixel, Gaussian) hit, backward.cu:593-635).
+// =============================================================================
+#pragma once
+#include "gslm_common.cuh"
+
+namespace gslm {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) {}
+}
+// TMA bulk copy global -> shared, completion signalled on an mbarrier (bytes % 16 == 0).
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// Two-stage ring of record batches for one tile. All threads keep an identical copy of the
+// phase bits; thread 0 issues.
+struct RecordRing {
+    float4* buf;       // [2][BATCH * REC_F4]
+    uint64_t* bar;     // [2]
+    const float4* src; // records of this tile (global)
+    int total;         // instances in the tile's range
+    uint32_t phase;    // bit s = parity of the next completion of stage s
+
+    __device__ __forceinline__ float4* stage(int s) const { return buf + s * (BATCH * REC_F4); }
+    __device__ __forceinline__ int batch_size(int b) const { return min(BATCH, total - b * BATCH); }
+    __device__ __forceinline__ void issue(int b, int s) const {   // one thread
+        uint32_t bytes = (uint32_t)batch_size(b) * (REC_F4 * 16);
+        mbar_arrive_expect_tx(&bar[s], bytes);
+        bulk_g2s(stage(s), src + (size_t)b * BATCH * REC_F4, bytes, &bar[s]);
+    }
+    __device__ __forceinline__ void wait(int s) {
+        mbar_wait(&bar[s], (phase >> s) & 1u);
+        phase ^= (1u << s);
+    }
+};
+
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// forward.cu:354-369 / backward.cu:561-569: power, G = exp(power), alpha = min(0.99, o G) and the
+// two skip tests. Explicitly rounded so that every sweep reproduces the same bits.
+// q0 = (x, y, conic.x, conic.y), q1 = (conic.z, opacity, ., .)
+__device__ __forceinline__ bool eval_alpha(const float4& q0, const float4& q1, float pxf, float pyf, float& dx,
+                                           float& dy, float& G, float& alpha) {
+    dx = __fsub_rn(q0.x, pxf);
+    dy = __fsub_rn(q0.y, pyf);
+    float t = __fmul_rn(__fmul_rn(q0.z, dx), dx);
+    t = __fmaf_rn(__fmul_rn(q1.x, dy), dy, t);
+    const float v = __fmul_rn(__fmul_rn(q0.w, dx), dy);
+    const float power = __fmaf_rn(-0.5f, t, -v);
+    if (power > 0.0f) return false;
+    G = ex2_approx(__fmul_rn(power, 1.4426950408889634f));
+    alpha = fminf(0.99f, __fmul_rn(q1.y, G));
+    return alpha >= (1.0f / 255.0f);
+}
+
+// Recursive-halving reduction of 10 values over a warp: 12 SHFL instead of 50.
+// On return lane l holds in `out` the warp total of value slot10(l) (or garbage-free 0 for
+// pad lanes); lanes with an odd index duplicate their even neighbour.
+__device__ __forceinline__ int slot10(int lane) {
+    const int b4 = (lane >> 4) & 1, b3 = (lane >> 3) & 1, b2 = (lane >> 2) & 1, b1 = (lane >> 1) & 1;
+    int sub;                       // index within a group of five: {0,1,2 | 3,4,pad}
+    if (!b3) sub = b2 ? (b1 ? -1 : 2) : b1;
+    else sub = b2 ? -1 : 3 + b1;
+    if (sub < 0 || (lane & 1)) return -1;
+    return b4 * 5 + sub;
+}
+__device__ __forceinline__ float xhalf(float lo, float hi, bool up, int mask) {
+    const float send = up ? lo : hi;
+    const float keep = up ? hi : lo;
+    return keep + __shfl_xor_sync(0xffffffffu, send, mask);
+}
+__device__ __forceinline__ float warp_reduce10(const float (&v)[10], int lane) {
+    const bool u4 = lane & 16, u3 = lane & 8, u2 = lane & 4, u1 = lane & 2;
+    float a0 = xhalf(v[0], v[5], u4, 16), a1 = xhalf(v[1], v[6], u4, 16), a2 = xhalf(v[2], v[7], u4, 16),
+          a3 = xhalf(v[3], v[8], u4, 16), a4 = xhalf(v[4], v[9], u4, 16);
+    float b0 = xhalf(a0, a3, u3, 8), b1 = xhalf(a1, a4, u3, 8), b2 = xhalf(a2, 0.f, u3, 8);
+    float c0 = xhalf(b0, b2, u2, 4), c1 = xhalf(b1, 0.f, u2, 4);
+    float d = xhalf(c0, c1, u1, 2);
+    d += __shfl_xor_sync(0xffffffffu, d, 1);
+    return d;
+}
+
+constexpr int ACC_STRIDE = 11;   // 10 partials + 1 pad word: conflict-free column reads
+
+}  // namespace gslm

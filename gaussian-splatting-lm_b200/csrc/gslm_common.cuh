@@ -1,0 +1,111 @@
+// =============================================================================
+// gslm_common.cuh -- shared declarations of the sm_100a rasterizer library.
+//
+// Buffer layouts replace GeometryState / ImageState / BinningState of the reference
+// (DGR/cuda_rasterizer/rasterizer_impl.h:29-43, rasterizer_impl.cu:155-235); the
+// layout is internal, only its total size crosses the C ABI.
+// =============================================================================
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/gslm_b200.h"
+
+namespace gslm {
+
+constexpr int TILE_X = 16, TILE_Y = 16;          // DGR/cuda_rasterizer/config.h:17-19
+constexpr int TILE_PIX = TILE_X * TILE_Y;        // 256 threads per tile CTA, one pixel each
+constexpr int BATCH = 256;                       // instances staged in shared memory per round
+constexpr int REC_F4 = 3;                        // one instance record = 3 x float4 = 48 bytes
+
+// Instance record (one per (tile, Gaussian) pair, stored in sorted order so that a
+// tile's batch is ONE contiguous 12 KB block that a single cp.async.bulk can stage):
+//   q0 = (x, y, conic.x, conic.y)   q1 = (conic.z, opacity, r, g)   q2 = (b, 1/depth, id bits, 0)
+// The per-Gaussian tangent record and the per-instance gradient record use the same
+// slot order: (xy | conic xyz | opacity | rgb | invdepth).
+
+inline __host__ __device__ size_t align_up(size_t x, size_t a = 128) { return (x + a - 1) / a * a; }
+
+struct GeomView {   // per-Gaussian state, SoA
+    float* depths;            // [P]
+    float2* means2D;          // [P]
+    float4* conic_opacity;    // [P]
+    float* rgb;               // [3P]
+    float* cov3D;             // [6P]
+    uint8_t* clamped;         // [P] bit c = channel c clamped (forward.cu:66-72)
+    uint32_t* tiles_touched;  // [P]
+    uint32_t* point_offsets;  // [P] inclusive scan
+    uint32_t* num_rendered;   // [1] device copy of R (tail of the scan)
+    char* scan_temp;
+    size_t scan_temp_bytes;
+    size_t total;
+};
+struct ImageView {  // per-pixel / per-tile state
+    float* final_T;           // [N]
+    uint32_t* n_contrib;      // [N]
+    uint2* ranges;            // [T]
+    uint32_t* tile_max_contrib;  // [T] max n_contrib over the tile's pixels (bounds the JVP / VJP sweeps)
+    size_t total;
+};
+struct BinningView {  // per-instance state
+    uint64_t* keys_unsorted;  // [R]
+    uint64_t* keys_sorted;    // [R]
+    uint32_t* vals_unsorted;  // [R]
+    uint32_t* point_list;     // [R] sorted Gaussian ids
+    uint32_t* inv_perm;       // [R] Gaussian-major slot -> sorted position
+    float4* records;          // [3R]
+    char* sort_temp;
+    size_t sort_temp_bytes;
+    size_t total;
+};
+
+size_t scan_temp_bytes(int P);
+size_t sort_temp_bytes(int64_t R);
+GeomView carve_geom(void* base, int P);
+ImageView carve_image(void* base, int W, int H);
+BinningView carve_binning(void* base, int64_t R);
+
+void set_error(const char* fmt, ...);
+const char* last_error();
+
+#define GSLM_CUDA_OK(expr)                                                                   \
+    do {                                                                                     \
+        cudaError_t e__ = (expr);                                                            \
+        if (e__ != cudaSuccess) {                                                            \
+            gslm::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+            return 1;                                                                        \
+        }                                                                                    \
+    } while (0)
+
+// ---- stage launchers (each one = one reference stage; see the .cu that defines it) ----
+struct TangentPtrs {   // tangent inputs of the forward-mode preprocess; any pointer may be null
+    const float *means3D, *opacities, *scales, *rotations, *cov3D_precomp, *shs, *colors_precomp;
+    const float *viewmatrix, *projmatrix, *campos;
+    float tan_fovx, tan_fovy, scale_modifier;
+};
+
+// preprocess.cu
+int launch_preprocess(const GslmGaussians& g, const GslmCamera& cam, const GeomView& gv, int32_t* radii,
+                      cudaStream_t s);
+// writes the per-Gaussian tangent record tgeom[3P] for Gaussians with radii > 0 (zeros otherwise)
+int launch_preprocess_tangent(const GslmGaussians& g, const TangentPtrs& t, const GslmCamera& cam,
+                              const int32_t* radii, float4* tgeom, cudaStream_t s);
+int launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present, cudaStream_t s);
+int launch_preprocess_bwd(const GslmGaussians& g, const GslmCamera& cam, const int32_t* radii, const GeomView& gv,
+                          const BinningView& bv, const float4* inst_grads, bool has_invdepth_grad,
+                          const GslmGrads& grads, cudaStream_t s);
+// binning.cu
+int run_scan(const GeomView& gv, int P, cudaStream_t s);
+int run_binning(const GeomView& gv, const int32_t* radii, const BinningView& bv, const ImageView& iv, int P, int W,
+                int H, int64_t R, const float* features, cudaStream_t s);
+// blend.cu
+int launch_blend_fwd(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg, float* out_color,
+                     float* out_invdepth, cudaStream_t s);
+int launch_blend_jvp(const BinningView& bv, const ImageView& iv, int W, int H, const float4* tgeom, const float* bg,
+                     const float* bg_tangent, float* out_color_t, float* out_invdepth_t, cudaStream_t s);
+int launch_blend_bwd(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg,
+                     const float* dL_dcolor, const float* dL_dinvdepth, float4* inst_grads, cudaStream_t s);
+int launch_blend_jtjv(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg,
+                      const float4* tgeom, const float* weight, float4* inst_grads, float* out_vJJv, cudaStream_t s);
+
+}  // namespace gslm

@@ -1,0 +1,359 @@
+"""ctypes binding of libgslm_b200.so (include/gslm_b200.h) with the call signatures of the
+reference extension module `diff_gaussian_rasterization._C`
+(DGR/ext.cpp:15-20, DGR/rasterize_points.cu).  Host plumbing only: torch supplies device
+memory and the current stream; every kernel lives in the shared library.
+
+There is NO fallback: if the library is missing or a tensor is not a CUDA tensor the call
+raises.
+"""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(os.path.dirname(_HERE), "libgslm_b200.so")
+_lib = None
+
+
+class GslmGaussians(C.Structure):
+    _fields_ = [("P", C.c_int32), ("sh_degree", C.c_int32), ("M", C.c_int32), ("scale_modifier", C.c_float),
+                ("means3D", C.c_void_p), ("opacities", C.c_void_p), ("scales", C.c_void_p), ("rotations", C.c_void_p),
+                ("cov3D_precomp", C.c_void_p), ("shs", C.c_void_p), ("colors_precomp", C.c_void_p)]
+
+
+class GslmCamera(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("tan_fovx", C.c_float), ("tan_fovy", C.c_float),
+                ("bg", C.c_void_p), ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("campos", C.c_void_p),
+                ("prefiltered", C.c_int32), ("antialiasing", C.c_int32), ("debug", C.c_int32)]
+
+
+class GslmCameraTangent(C.Structure):
+    _fields_ = [("tan_fovx", C.c_float), ("tan_fovy", C.c_float), ("scale_modifier", C.c_float),
+                ("bg", C.c_void_p), ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("campos", C.c_void_p)]
+
+
+class GslmGrads(C.Structure):
+    _fields_ = [("dL_dmeans2D", C.c_void_p), ("dL_dcolors", C.c_void_p), ("dL_dopacity", C.c_void_p),
+                ("dL_dmeans3D", C.c_void_p), ("dL_dcov3D", C.c_void_p), ("dL_dsh", C.c_void_p),
+                ("dL_dscales", C.c_void_p), ("dL_drotations", C.c_void_p), ("accumulate", C.c_int32)]
+
+
+class GslmBufferView(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("point_list", "keys_sorted", "ranges", "n_contrib", "final_T",
+                                          "tiles_touched", "point_offsets", "depths", "means2D", "conic_opacity",
+                                          "rgb", "cov3D", "clamped")]
+
+
+ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_int32, C.c_size_t)
+
+EXPORTS = ("gslm_last_error", "gslm_abi_version", "gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes",
+           "gslm_mark_visible", "gslm_forward", "gslm_forward_jvp", "gslm_backward_scratch_bytes", "gslm_backward",
+           "gslm_jvp_scratch_bytes", "gslm_jvp_cached", "gslm_jtjv_scratch_bytes", "gslm_jtjv", "gslm_buffer_view")
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise RuntimeError(f"{_LIB_PATH} not built: run `python __graft_entry__.py build` "
+                               "(there is no CPU or PyTorch fallback for the rasterizer)")
+        L = C.CDLL(_LIB_PATH)
+        L.gslm_last_error.restype = C.c_char_p
+        for n in ("gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_backward_scratch_bytes",
+                  "gslm_jvp_scratch_bytes", "gslm_jtjv_scratch_bytes"):
+            getattr(L, n).restype = C.c_size_t
+        L.gslm_geom_bytes.argtypes = [C.c_int32]
+        L.gslm_image_bytes.argtypes = [C.c_int32, C.c_int32]
+        L.gslm_binning_bytes.argtypes = [C.c_int64]
+        L.gslm_backward_scratch_bytes.argtypes = [C.c_int64]
+        L.gslm_jvp_scratch_bytes.argtypes = [C.c_int32]
+        L.gslm_jtjv_scratch_bytes.argtypes = [C.c_int32, C.c_int64]
+        vp = C.c_void_p
+        L.gslm_mark_visible.argtypes = [C.c_int32, vp, vp, vp, vp, vp]
+        L.gslm_forward.argtypes = [vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp]
+        L.gslm_forward_jvp.argtypes = [vp, vp, vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp, vp, vp]
+        L.gslm_backward.argtypes = [vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
+        L.gslm_jvp_cached.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp]
+        L.gslm_jtjv.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
+        L.gslm_buffer_view.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, vp, vp, vp, vp]
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise RuntimeError("gslm_b200: " + lib().gslm_last_error().decode())
+
+
+def _ptr(t):
+    """Device pointer of a float32/int32/uint8 CUDA tensor, None for empty / None."""
+    if t is None or (isinstance(t, torch.Tensor) and t.numel() == 0):
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("gslm_b200: tensors must live on a CUDA device (no CPU path)")
+    return t.data_ptr()
+
+
+def _f32(t):
+    if t is None:
+        return None
+    if not isinstance(t, torch.Tensor):
+        return t
+    if t.numel() == 0:
+        return t
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+class _Alloc:
+    """The three opaque scratch tensors (geomBuffer, binningBuffer, imgBuffer) are torch uint8 tensors
+    created through this callback -- the resizeFunctional of DGR/rasterize_points.cu:28-34."""
+
+    def __init__(self, device):
+        self.device = device
+        self.bufs = {}
+        self.cb = ALLOC_FN(self._alloc)
+
+    def _alloc(self, _ctx, which, nbytes):
+        t = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=self.device)
+        self.bufs[int(which)] = t
+        return t.data_ptr()
+
+    def get(self, which):
+        t = self.bufs.get(which)
+        return t if t is not None else torch.empty(0, dtype=torch.uint8, device=self.device)
+
+
+def _gaussians(means3D, colors_precomp, opacities, scales, rotations, scale_modifier, cov3D_precomp, sh, degree):
+    keep = [_f32(means3D), _f32(colors_precomp), _f32(opacities), _f32(scales), _f32(rotations), _f32(cov3D_precomp),
+            _f32(sh)]
+    m, cp, op, sc, ro, cov, shs = keep
+    if m.dim() != 2 or m.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")   # rasterize_points.cu:59-61
+    g = GslmGaussians()
+    g.P = m.shape[0]
+    g.sh_degree = int(degree)
+    g.M = int(shs.shape[1]) if (shs is not None and shs.numel() != 0) else 0
+    g.scale_modifier = float(scale_modifier)
+    g.means3D, g.opacities, g.scales, g.rotations = _ptr(m), _ptr(op), _ptr(sc), _ptr(ro)
+    g.cov3D_precomp, g.shs, g.colors_precomp = _ptr(cov), _ptr(shs), _ptr(cp)
+    return g, keep
+
+
+def _tangent_gaussians(means3D, colors_precomp, opacities, scales, rotations, cov3D_precomp, sh):
+    keep = [_f32(means3D), _f32(colors_precomp), _f32(opacities), _f32(scales), _f32(rotations), _f32(cov3D_precomp),
+            _f32(sh)]
+    m, cp, op, sc, ro, cov, shs = keep
+    g = GslmGaussians()
+    g.means3D, g.opacities, g.scales, g.rotations = _ptr(m), _ptr(op), _ptr(sc), _ptr(ro)
+    g.cov3D_precomp, g.shs, g.colors_precomp = _ptr(cov), _ptr(shs), _ptr(cp)
+    return g, keep
+
+
+def _camera(bg, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, campos, prefiltered, antialiasing, debug):
+    keep = [_f32(bg), _f32(viewmatrix), _f32(projmatrix), _f32(campos)]
+    c = GslmCamera()
+    c.width, c.height = int(W), int(H)
+    c.tan_fovx, c.tan_fovy = float(tan_fovx), float(tan_fovy)
+    c.bg, c.viewmatrix, c.projmatrix, c.campos = [_ptr(k) for k in keep]
+    c.prefiltered, c.antialiasing, c.debug = int(bool(prefiltered)), int(bool(antialiasing)), int(bool(debug))
+    return c, keep
+
+
+def _as_float(x):
+    return float(x.item()) if isinstance(x, torch.Tensor) else float(x)
+
+
+# ---------------------------------------------------------------------------------------
+# the four functions of the reference module (DGR/ext.cpp:15-20)
+# ---------------------------------------------------------------------------------------
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                        viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                        prefiltered, antialiasing, debug):
+    """DGR/rasterize_points.cu:36-141 -> (num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepth)"""
+    L = lib()
+    dev = means3D.device
+    g, k1 = _gaussians(means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, sh, degree)
+    cam, k2 = _camera(background, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, campos,
+                      prefiltered, antialiasing, debug)
+    P, H, W = g.P, int(image_height), int(image_width)
+    out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+    out_invdepth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+    radii = torch.zeros((P,), dtype=torch.int32, device=dev)
+    if P == 0:   # rasterize_points.cu:105
+        out_color.zero_(); out_invdepth.zero_()
+        e = torch.empty(0, dtype=torch.uint8, device=dev)
+        return 0, out_color, radii, e, e.clone(), e.clone(), out_invdepth
+    al = _Alloc(dev)
+    n = C.c_int32(0)
+    _check(L.gslm_forward(C.addressof(g), C.addressof(cam), al.cb, None, out_color.data_ptr(),
+                          out_invdepth.data_ptr(), radii.data_ptr(), C.addressof(n), _stream()))
+    return int(n.value), out_color, radii, al.get(0), al.get(1), al.get(2), out_invdepth
+
+
+def rasterize_gaussians_jvp(background, background_grad, means3D, means3D_grad, colors, colors_grad, opacity,
+                            opacity_grad, scales, scales_grad, rotations, rotations_grad, scale_modifier,
+                            scale_modifier_grad, cov3D_precomp, cov3D_precomp_grad, viewmatrix, viewmatrix_grad,
+                            projmatrix, projmatrix_grad, tan_fovx, tan_fovx_grad, tan_fovy, tan_fovy_grad,
+                            image_height, image_width, sh, sh_grad, degree, campos, campos_grad, prefiltered,
+                            antialiasing, debug):
+    """DGR/rasterize_points.cu:143-298 -> 9-tuple (the 7 above + color_grad, invdepth_grad)"""
+    L = lib()
+    dev = means3D.device
+    g, k1 = _gaussians(means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, sh, degree)
+    gt, k3 = _tangent_gaussians(means3D_grad, colors_grad, opacity_grad, scales_grad, rotations_grad,
+                                cov3D_precomp_grad, sh_grad)
+    cam, k2 = _camera(background, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, campos,
+                      prefiltered, antialiasing, debug)
+    k4 = [_f32(background_grad), _f32(viewmatrix_grad), _f32(projmatrix_grad), _f32(campos_grad)]
+    ct = GslmCameraTangent()
+    ct.tan_fovx, ct.tan_fovy = _as_float(tan_fovx_grad), _as_float(tan_fovy_grad)
+    ct.scale_modifier = _as_float(scale_modifier_grad)
+    ct.bg, ct.viewmatrix, ct.projmatrix, ct.campos = [_ptr(k) for k in k4]
+    P, H, W = g.P, int(image_height), int(image_width)
+    out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+    out_invdepth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+    out_color_t = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+    out_invdepth_t = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+    radii = torch.zeros((P,), dtype=torch.int32, device=dev)
+    if P == 0:
+        for t in (out_color, out_invdepth, out_color_t, out_invdepth_t):
+            t.zero_()
+        e = torch.empty(0, dtype=torch.uint8, device=dev)
+        return 0, out_color, radii, e, e.clone(), e.clone(), out_invdepth, out_color_t, out_invdepth_t
+    al = _Alloc(dev)
+    n = C.c_int32(0)
+    _check(L.gslm_forward_jvp(C.addressof(g), C.addressof(gt), C.addressof(cam), C.addressof(ct), al.cb, None,
+                              out_color.data_ptr(), out_invdepth.data_ptr(), radii.data_ptr(),
+                              out_color_t.data_ptr(), out_invdepth_t.data_ptr(), C.addressof(n), _stream()))
+    return (int(n.value), out_color, radii, al.get(0), al.get(1), al.get(2), out_invdepth, out_color_t,
+            out_invdepth_t)
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, opacities, scales, rotations, scale_modifier,
+                                 cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color,
+                                 dL_dout_invdepth, sh, degree, campos, geomBuffer, R, binningBuffer, imageBuffer,
+                                 antialiasing, debug, accumulate_into=None):
+    """DGR/rasterize_points.cu:300-399 -> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
+    dL_dscales, dL_drotations).  `accumulate_into` (optional 8-tuple) adds into existing tensors instead."""
+    L = lib()
+    dev = means3D.device
+    g, k1 = _gaussians(means3D, colors, opacities, scales, rotations, scale_modifier, cov3D_precomp, sh, degree)
+    H, W = int(dL_dout_color.shape[-2]), int(dL_dout_color.shape[-1])
+    cam, k2 = _camera(background, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, campos, False, antialiasing, debug)
+    P, M = g.P, g.M
+    if accumulate_into is None:
+        # overwrite mode: the kernel writes every element (zeros for culled Gaussians), so no memset
+        # of the eight tensors is needed (the reference zero-fills ten, rasterize_points.cu:339-348)
+        z = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
+        outs = (z(P, 3), z(P, 3), z(P, 1), z(P, 3), z(P, 6), z(P, M, 3), z(P, 3), z(P, 4))
+    else:
+        outs = accumulate_into
+    if P == 0:
+        return outs
+    dcol = _f32(dL_dout_color)
+    dinv = _f32(dL_dout_invdepth) if (dL_dout_invdepth is not None and dL_dout_invdepth.numel() != 0) else None
+    gr = GslmGrads()
+    (gr.dL_dmeans2D, gr.dL_dcolors, gr.dL_dopacity, gr.dL_dmeans3D, gr.dL_dcov3D, gr.dL_dsh, gr.dL_dscales,
+     gr.dL_drotations) = [_ptr(o) for o in outs]
+    gr.accumulate = 0 if accumulate_into is None else 1
+    scratch = torch.empty(L.gslm_backward_scratch_bytes(int(R)), dtype=torch.uint8, device=dev)
+    _check(L.gslm_backward(C.addressof(g), C.addressof(cam), _ptr(radii), _ptr(geomBuffer), _ptr(binningBuffer),
+                           _ptr(imageBuffer), int(R), _ptr(dcol), _ptr(dinv), scratch.data_ptr(), C.addressof(gr),
+                           _stream()))
+    return outs
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """DGR/rasterize_points.cu:401-420"""
+    m = _f32(means3D)
+    P = m.shape[0]
+    present = torch.zeros((P,), dtype=torch.bool, device=m.device)
+    if P:
+        v, p = _f32(viewmatrix), _f32(projmatrix)
+        _check(lib().gslm_mark_visible(P, _ptr(m), _ptr(v), _ptr(p), present.data_ptr(), _stream()))
+    return present
+
+
+# ---------------------------------------------------------------------------------------
+# additive: linearisation-cached entry points (used by solver.solver_functions)
+# ---------------------------------------------------------------------------------------
+def jvp_cached(gauss_args, tangent_args, cam_args, radii, geomBuffer, R, binningBuffer, imageBuffer,
+               want_invdepth=False):
+    """J v for a linearised view. gauss_args = (means3D, colors, opacity, scales, rotations, scale_modifier,
+    cov3D_precomp, sh, degree); tangent_args = (means3D_t, colors_t, opacity_t, scales_t, rotations_t, cov3D_t,
+    sh_t); cam_args = (bg, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, campos, antialiasing, debug)."""
+    L = lib()
+    g, k1 = _gaussians(*gauss_args)
+    gt, k3 = _tangent_gaussians(*tangent_args)
+    bg, vm, pm, tfx, tfy, H, W, campos, aa, dbg = cam_args
+    cam, k2 = _camera(bg, vm, pm, tfx, tfy, H, W, campos, False, aa, dbg)
+    dev = k1[0].device
+    out_t = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+    out_d = torch.empty((1, H, W), dtype=torch.float32, device=dev) if want_invdepth else None
+    scratch = torch.empty(L.gslm_jvp_scratch_bytes(g.P), dtype=torch.uint8, device=dev)
+    _check(L.gslm_jvp_cached(C.addressof(g), C.addressof(gt), C.addressof(cam), _ptr(radii), _ptr(geomBuffer),
+                             _ptr(binningBuffer), _ptr(imageBuffer), int(R), scratch.data_ptr(), out_t.data_ptr(),
+                             _ptr(out_d), _stream()))
+    return out_t, out_d
+
+
+def jtjv(gauss_args, tangent_args, cam_args, radii, geomBuffer, R, binningBuffer, imageBuffer, weight, outs,
+         out_vJJv=None, scratch=None):
+    """outs (8-tuple like rasterize_gaussians_backward, entries may be None) += J^T diag(weight) J v."""
+    L = lib()
+    g, k1 = _gaussians(*gauss_args)
+    gt, k3 = _tangent_gaussians(*tangent_args)
+    bg, vm, pm, tfx, tfy, H, W, campos, aa, dbg = cam_args
+    cam, k2 = _camera(bg, vm, pm, tfx, tfy, H, W, campos, False, aa, dbg)
+    dev = k1[0].device
+    w = _f32(weight)
+    need = L.gslm_jtjv_scratch_bytes(g.P, int(R))
+    if scratch is None or scratch.numel() < need:
+        scratch = torch.empty(need, dtype=torch.uint8, device=dev)
+    gr = GslmGrads()
+    (gr.dL_dmeans2D, gr.dL_dcolors, gr.dL_dopacity, gr.dL_dmeans3D, gr.dL_dcov3D, gr.dL_dsh, gr.dL_dscales,
+     gr.dL_drotations) = [_ptr(o) for o in outs]
+    gr.accumulate = 1
+    _check(L.gslm_jtjv(C.addressof(g), C.addressof(gt), C.addressof(cam), _ptr(radii), _ptr(geomBuffer),
+                       _ptr(binningBuffer), _ptr(imageBuffer), int(R), _ptr(w), scratch.data_ptr(),
+                       C.addressof(gr), _ptr(out_vJJv), _stream()))
+    return scratch
+
+
+def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer):
+    """Test helper: torch views of the integer state inside the opaque buffers (bit-exactness checks)."""
+    v = GslmBufferView()
+    _check(lib().gslm_buffer_view(int(P), int(W), int(H), int(R), _ptr(geomBuffer), _ptr(binningBuffer),
+                                  _ptr(imageBuffer), C.addressof(v)))
+
+    def view(buf, ptr, nbytes, dtype, shape):
+        off = ptr - buf.data_ptr()
+        return buf[off:off + nbytes].view(dtype).view(shape)
+
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    N = W * H
+    out = {}
+    if binningBuffer is not None and binningBuffer.numel() and R > 0:
+        out["point_list"] = view(binningBuffer, v.point_list, 4 * R, torch.int32, (R,))
+        out["keys_sorted"] = view(binningBuffer, v.keys_sorted, 8 * R, torch.int64, (R,))
+    if imageBuffer is not None and imageBuffer.numel():
+        out["ranges"] = view(imageBuffer, v.ranges, 8 * T, torch.int32, (T, 2))
+        out["n_contrib"] = view(imageBuffer, v.n_contrib, 4 * N, torch.int32, (H, W))
+        out["final_T"] = view(imageBuffer, v.final_T, 4 * N, torch.float32, (H, W))
+    if geomBuffer is not None and geomBuffer.numel():
+        out["tiles_touched"] = view(geomBuffer, v.tiles_touched, 4 * P, torch.int32, (P,))
+        out["point_offsets"] = view(geomBuffer, v.point_offsets, 4 * P, torch.int32, (P,))
+        out["depths"] = view(geomBuffer, v.depths, 4 * P, torch.float32, (P,))
+        out["means2D"] = view(geomBuffer, v.means2D, 8 * P, torch.float32, (P, 2))
+        out["conic_opacity"] = view(geomBuffer, v.conic_opacity, 16 * P, torch.float32, (P, 4))
+        out["rgb"] = view(geomBuffer, v.rgb, 12 * P, torch.float32, (P, 3))
+        out["cov3D"] = view(geomBuffer, v.cov3D, 24 * P, torch.float32, (P, 6))
+        out["clamped"] = view(geomBuffer, v.clamped, P, torch.uint8, (P,))
+    return out

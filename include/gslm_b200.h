@@ -1,0 +1,176 @@
+/* =============================================================================
+ * gslm_b200.h -- C ABI of the B200-native Gaussian-splatting LM hot path.
+ *
+ * Drop-in boundary for the reference's torch extension `diff_gaussian_rasterization._C`
+ * (submodules/diff-gaussian-rasterization, "DGR" below).  Plain pointers and sizes
+ * only; every pointer is a DEVICE pointer unless stated; nothing here owns device
+ * memory: outputs are caller-allocated, scratch comes from the caller's allocator
+ * callback (mirrors resizeFunctional, DGR/rasterize_points.cu:28-34).
+ *
+ * All functions return 0 on success, non-zero on failure; gslm_last_error() gives the
+ * message (thread-local).  Kernels are launched on `stream` (a cudaStream_t passed as
+ * void*); the only host synchronisation is the 4-byte read-back of num_rendered inside
+ * gslm_forward / gslm_forward_jvp (the reference has the same one,
+ * DGR/cuda_rasterizer/rasterizer_impl.cu:325) plus a full sync when camera.debug != 0
+ * (DGR/cuda_rasterizer/auxiliary.h:262-269).
+ * ========================================================================== */
+#ifndef GSLM_B200_H
+#define GSLM_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Gaussian parameters as the reference binding receives them
+ * (DGR/rasterize_points.cu:36-57): activations already applied by the caller. */
+typedef struct GslmGaussians {
+    int32_t P;                   /* number of Gaussians                                   */
+    int32_t sh_degree;           /* active SH degree D (0..3)                              */
+    int32_t M;                   /* SH coefficients stored per channel (sh.size(1)), 0 if none */
+    float scale_modifier;
+    const float* means3D;        /* [P,3]                                                 */
+    const float* opacities;      /* [P]                                                   */
+    const float* scales;         /* [P,3]   or NULL when cov3D_precomp is given           */
+    const float* rotations;      /* [P,4]   (r,x,y,z), NOT normalised by the kernels      */
+    const float* cov3D_precomp;  /* [P,6]   or NULL                                       */
+    const float* shs;            /* [P,M,3] or NULL when colors_precomp is given          */
+    const float* colors_precomp; /* [P,3]   or NULL                                       */
+} GslmGaussians;
+
+/* One camera = the per-view part of GaussianRasterizationSettings
+ * (DGR/diff_gaussian_rasterization/__init__.py:287-300). Matrices are the 16 floats
+ * of the transposed (row-vector) torch tensors, i.e. maths element (i,j) at [i + 4 j]. */
+typedef struct GslmCamera {
+    int32_t width, height;
+    float tan_fovx, tan_fovy;
+    const float* bg;             /* [3]  */
+    const float* viewmatrix;     /* [16] */
+    const float* projmatrix;     /* [16] */
+    const float* campos;         /* [3]  */
+    int32_t prefiltered, antialiasing, debug;
+} GslmCamera;
+
+/* Tangents of the camera-side inputs for the forward-mode entry points
+ * (the `_grad` partners of DGR/rasterize_points.cu:143-180).  NULL / 0 => zero tangent. */
+typedef struct GslmCameraTangent {
+    float tan_fovx, tan_fovy, scale_modifier;
+    const float* bg;
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* campos;
+} GslmCameraTangent;
+
+/* Gradient sinks = the 8-tuple returned by RasterizeGaussiansBackwardCUDA
+ * (DGR/rasterize_points.cu:300-399).  Any pointer may be NULL (not wanted).
+ * accumulate != 0: add into the buffers (batched multi-view sum, replaces the Python
+ * `+=` loop of DGR/diff_gaussian_rasterization/batch_render.py:330-346);
+ * accumulate == 0: every element of every non-NULL buffer is overwritten. */
+typedef struct GslmGrads {
+    float* dL_dmeans2D;   /* [P,3] */
+    float* dL_dcolors;    /* [P,3]   (only meaningful with colors_precomp) */
+    float* dL_dopacity;   /* [P]   */
+    float* dL_dmeans3D;   /* [P,3] */
+    float* dL_dcov3D;     /* [P,6] */
+    float* dL_dsh;        /* [P,M,3] */
+    float* dL_dscales;    /* [P,3] */
+    float* dL_drotations; /* [P,4] */
+    int32_t accumulate;
+} GslmGrads;
+
+/* Scratch allocator: must return a device pointer to at least `bytes` bytes, 128-byte
+ * aligned, that stays valid until the caller frees it.  `which`: 0 geometry, 1 binning,
+ * 2 image buffer -- the three opaque buffers of the reference
+ * (geomBuffer / binningBuffer / imgBuffer, DGR/rasterize_points.cu:80-88). */
+typedef void* (*GslmAllocFn)(void* ctx, int32_t which, size_t bytes);
+enum { GSLM_BUF_GEOM = 0, GSLM_BUF_BINNING = 1, GSLM_BUF_IMAGE = 2 };
+
+const char* gslm_last_error(void);
+int32_t gslm_abi_version(void);
+
+/* Buffer sizes (bytes) -- replaces required<GeometryState/ImageState/BinningState>
+ * (DGR/cuda_rasterizer/rasterizer_impl.h:29-43). */
+size_t gslm_geom_bytes(int32_t P);
+size_t gslm_image_bytes(int32_t width, int32_t height);
+size_t gslm_binning_bytes(int64_t num_rendered);
+
+/* Replaces _C.mark_visible (DGR/rasterize_points.cu:401-420). present: uint8 [P]. */
+int32_t gslm_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                          uint8_t* present, void* stream);
+
+/* Replaces _C.rasterize_gaussians (DGR/rasterize_points.cu:36-141;
+ * CudaRasterizer::Rasterizer::forward, DGR/cuda_rasterizer/rasterizer_impl.cu:239-391).
+ * out_color [3,H,W], out_invdepth [1,H,W], radii int32 [P], *num_rendered host int. */
+int32_t gslm_forward(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn alloc, void* alloc_ctx,
+                     float* out_color, float* out_invdepth, int32_t* radii, int32_t* num_rendered, void* stream);
+
+/* Replaces _C.rasterize_gaussians_jvp (DGR/rasterize_points.cu:143-298; forwardJvp,
+ * DGR/cuda_rasterizer/rasterizer_jvp_impl.h:125-325).  `gt` holds the tangent pointers in
+ * the same fields as `g` (NULL => zero tangent; P/sh_degree/M/scale_modifier ignored,
+ * the scale_modifier tangent travels in camt).  The buffers it leaves behind are
+ * accepted by gslm_backward, like the reference's. */
+int32_t gslm_forward_jvp(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam,
+                         const GslmCameraTangent* camt, GslmAllocFn alloc, void* alloc_ctx, float* out_color,
+                         float* out_invdepth, int32_t* radii, float* out_color_tangent, float* out_invdepth_tangent,
+                         int32_t* num_rendered, void* stream);
+
+/* Replaces _C.rasterize_gaussians_backward (DGR/rasterize_points.cu:300-399;
+ * Rasterizer::backward, DGR/cuda_rasterizer/rasterizer_impl.cu:395-500).
+ * dL_dinvdepth may be NULL.  `scratch` = gslm_backward_scratch_bytes(num_rendered) bytes. */
+size_t gslm_backward_scratch_bytes(int64_t num_rendered);
+int32_t gslm_backward(const GslmGaussians* g, const GslmCamera* cam, const int32_t* radii, const void* geom_buffer,
+                      const void* binning_buffer, const void* image_buffer, int32_t num_rendered,
+                      const float* dL_dcolor, const float* dL_dinvdepth, void* scratch, GslmGrads* grads,
+                      void* stream);
+
+/* ---- additive entry points: the linearisation-cached LM / CG path -------------------
+ * A "linearised view" is the triple of buffers left by gslm_forward for one camera at the
+ * current parameters.  The functions below reuse it, so a CG iteration costs no
+ * preprocess-primal / scan / sort / ranges work and no host synchronisation. */
+
+/* J v for one linearised view: image tangent [3,H,W] (+ optional invdepth tangent [1,H,W])
+ * for Gaussian-parameter tangents `gt` (camera tangents are zero on this path,
+ * DGR/diff_gaussian_rasterization/utils.py:18-19). scratch: gslm_jvp_scratch_bytes(P). */
+size_t gslm_jvp_scratch_bytes(int32_t P);
+int32_t gslm_jvp_cached(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam, const int32_t* radii,
+                        const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
+                        int32_t num_rendered, void* scratch, float* out_color_tangent, float* out_invdepth_tangent,
+                        void* stream);
+
+/* Fused Gauss-Newton product for one linearised view, J never materialised:
+ *   grads (+)= J^T diag(w) J v      with per-pixel weight image `weight` [3,H,W]
+ * (w = residual multiplicity x clamp/alpha mask squared; solver/batch_training_loss.py:10-31,
+ * gaussian_renderer/batch_render.py:118), NULL => w = 1.
+ * out_vJJv (device float[1], may be NULL) accumulates v^T J^T W J v = sum w * (Jv)^2, the
+ * p^T A p that CG needs (solver/conjugate_gradient.py:28), for free.
+ * scratch: gslm_jtjv_scratch_bytes(P, num_rendered). */
+size_t gslm_jtjv_scratch_bytes(int32_t P, int64_t num_rendered);
+int32_t gslm_jtjv(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam, const int32_t* radii,
+                  const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
+                  int32_t num_rendered, const float* weight, void* scratch, GslmGrads* grads, float* out_vJJv,
+                  void* stream);
+
+/* Introspection for tests (bit-exact binning checks): device pointers INTO the buffers. */
+typedef struct GslmBufferView {
+    const uint32_t* point_list;   /* [R] sorted Gaussian ids   (rasterizer.h BinningState::point_list) */
+    const uint64_t* keys_sorted;  /* [R] tile<<32 | depth bits                                          */
+    const uint32_t* ranges;       /* [T,2] per-tile [start,end) (ImageState::ranges)                    */
+    const uint32_t* n_contrib;    /* [H*W]                                                              */
+    const float* final_T;         /* [H*W]                                                              */
+    const uint32_t* tiles_touched;/* [P]                                                                */
+    const uint32_t* point_offsets;/* [P] inclusive scan                                                 */
+    const float* depths;          /* [P]                                                                */
+    const float* means2D;         /* [P,2]                                                              */
+    const float* conic_opacity;   /* [P,4]                                                              */
+    const float* rgb;             /* [P,3]                                                              */
+    const float* cov3D;           /* [P,6]                                                              */
+    const uint8_t* clamped;       /* [P] bit c set <=> channel c clamped                                */
+} GslmBufferView;
+int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_rendered, const void* geom_buffer,
+                         const void* binning_buffer, const void* image_buffer, GslmBufferView* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSLM_B200_H */
