@@ -1,0 +1,87 @@
+"""CPU: the C-ABI library loads and exports every symbol include/gslm_b200.h declares; size queries (host-only
+functions) behave; the Python surface has the reference's names and raises the reference's exceptions.
+No compute call is made (no GPU here)."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "gaussian-splatting-lm_b200", "libgslm_b200.so")
+HEADER = os.path.join(ROOT, "include", "gslm_b200.h")
+
+
+def _declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(gslm_[a-z0-9_]+)\s*\(", src)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if not os.path.exists(LIB):
+        import __graft_entry__
+        __graft_entry__.build()
+    return ctypes.CDLL(LIB)
+
+
+def test_every_declared_symbol_is_exported(lib):
+    names = _declared_symbols()
+    assert len(names) >= 15
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/gslm_b200.h but not exported"
+
+
+def test_binding_lists_the_same_symbols():
+    from diff_gaussian_rasterization import _C
+    assert sorted(_C.EXPORTS) == _declared_symbols()
+
+
+def test_size_queries(lib):
+    for n in ("gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_backward_scratch_bytes",
+              "gslm_jvp_scratch_bytes", "gslm_jtjv_scratch_bytes", "gslm_linearize_bytes"):
+        if hasattr(lib, n):
+            getattr(lib, n).restype = ctypes.c_size_t
+    assert lib.gslm_abi_version() >= 1
+    g0, g1 = lib.gslm_geom_bytes(ctypes.c_int32(0)), lib.gslm_geom_bytes(ctypes.c_int32(1000))
+    assert g1 > g0 and g1 % 128 == 0
+    # per-pixel state: final_T + n_contrib = 8 B / pixel (+ per-tile ranges)
+    i = lib.gslm_image_bytes(ctypes.c_int32(1920), ctypes.c_int32(1080))
+    assert 8 * 1920 * 1080 <= i <= 9 * 1920 * 1080
+    b0, b1 = lib.gslm_binning_bytes(ctypes.c_int64(0)), lib.gslm_binning_bytes(ctypes.c_int64(1 << 20))
+    assert b1 > b0 and b1 >= (1 << 20) * (48 + 4 + 8)
+    assert lib.gslm_backward_scratch_bytes(ctypes.c_int64(1000)) >= 1000 * 40
+
+
+def test_python_surface_names_and_errors():
+    import diff_gaussian_rasterization as dgr
+    fields = dgr.GaussianRasterizationSettings._fields
+    # DGR/diff_gaussian_rasterization/__init__.py:287-300
+    assert fields == ("image_height", "image_width", "tanfovx", "tanfovy", "bg", "scale_modifier", "viewmatrix",
+                      "projmatrix", "sh_degree", "campos", "prefiltered", "debug", "antialiasing")
+    rs = dgr.GaussianRasterizationSettings(8, 8, 1.0, 1.0, torch.zeros(3), 1.0, torch.eye(4), torch.eye(4), 0,
+                                           torch.zeros(3), False, False, False)
+    r = dgr.GaussianRasterizer(rs)
+    m = torch.zeros(4, 3)
+    with pytest.raises(Exception, match="SHs or precomputed colors"):
+        r(m, m, torch.zeros(4, 1), shs=None, colors_precomp=None, scales=m, rotations=torch.zeros(4, 4))
+    with pytest.raises(Exception, match="scale/rotation pair or precomputed 3D covariance"):
+        r(m, m, torch.zeros(4, 1), colors_precomp=m, scales=m, rotations=torch.zeros(4, 4),
+          cov3D_precomp=torch.zeros(4, 6))
+    # no CPU path: host tensors are refused loudly
+    with pytest.raises(RuntimeError, match="CUDA"):
+        r(m, m, torch.zeros(4, 1), colors_precomp=m, scales=m, rotations=torch.zeros(4, 4))
+
+
+def test_utils_tangent_helpers():
+    import torch.autograd.forward_ad as fwAD
+    from diff_gaussian_rasterization.utils import get_tangent, has_tangent
+    x = torch.ones(3)
+    assert not has_tangent(x) and not has_tangent(1.0)
+    assert get_tangent(2.0) == 0.0 and torch.equal(get_tangent(x), torch.zeros(3))
+    with fwAD.dual_level():
+        d = fwAD.make_dual(x, 2 * x)
+        assert has_tangent(d) and has_tangent([x, d])
+        assert torch.equal(get_tangent(d), 2 * x)
