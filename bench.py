@@ -1,0 +1,316 @@
+#!/usr/bin/env python
+"""bench.py -- the headline benchmark of the LM hot path: J^T J v CG matvecs/s.
+
+    python bench.py --gpus N --steps K --warmup W [--config C|B|A] [--views V] [--impl reference]
+
+A "step" = one Gauss-Newton product J^T J v over ALL views of the workload (config C of BASELINE.json by default:
+1M random Gaussians, 64 views at 1920x1080, SH degree 3) through the solver-facing call
+LinearSolverFunctions.normal_matvec -- per view: tangent preprocess, the fused tangent->adjoint tile kernel,
+the per-Gaussian adjoint kernel; then (N > 1) ONE NCCL allreduce of the packed 59 P-float result.  The
+linearisation (forward render, sort, records) is done once before the timed region, exactly as in an LM step
+where one linearisation serves the whole CG solve; its cost is reported separately (`linearize_ms`).
+Views are sharded round-robin over ranks (strong scaling: the total work is fixed).
+
+value  : matvecs/s with v already resident in HBM (device-timed with CUDA events, max over ranks).
+e2e    : the same call with v in pinned HOST memory and the result read back to the host every step.
+roofline: the dominant kernel (k_blend_jtjv) timed live per launch through the library's stage timers in a
+         separate pass of the same K steps (the timers add two event records per kernel, so they stay out of the
+         headline region); algorithmic bytes per launch as DESIGN.md defines them.
+cpu_baseline / --impl reference: the CPU oracle (a port: the reference has NO CPU implementation of this path and
+         its CUDA JVP cannot be built) on the box's host cores on a bounded sample of the views.
+"""
+import argparse
+import functools
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+from types import SimpleNamespace
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (os.path.join(ROOT, "gaussian-splatting-lm_b200"),):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "J^T J v CG matvecs/s"
+UNIT = "matvecs/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="C", choices=["A", "B", "C", "D"])
+    ap.add_argument("--views", type=int, default=0, help="override the number of views (0 = the config's)")
+    ap.add_argument("--points", type=int, default=0, help="override the number of Gaussians")
+    ap.add_argument("--sh-degree", type=int, default=3)
+    ap.add_argument("--mask-xyz", action="store_true", help="zero the xyz tangent like train_jvp.py:221-227")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample-views", type=int, default=0, help="views in the CPU sample (0 = auto)")
+    return ap.parse_args()
+
+
+def workload_name(a, P, V, W, H):
+    return f"config {a.config}: {P} Gaussians x {V} views at {W}x{H}, SH degree {a.sh_degree}, J^T J v (disable_ssim residual)"
+
+
+# --------------------------------------------------------------------------------------- CPU arm
+def cpu_jtjv_views(g, cams, tangent, views):
+    """CPU oracle: J^T (2 m^2 (J v)) for the given views; returns seconds taken (bench.py's cpu_baseline leg is one
+    of the two places allowed to execute oracle/)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import gs_oracle as o
+    import scene_synth as ss
+    t0 = time.perf_counter()
+    for i in views:
+        c = ss.camera_dict(cams[i])
+        st = o.render_forward(g, c, tangents=tangent)          # primal + J v in one sweep (forwardJvp)
+        m = ((st["color"] >= 0) & (st["color"] <= 1)).astype(np.float32)
+        o.render_backward(g, c, st, 2.0 * m * m * st["t_color"])
+    return time.perf_counter() - t0, o.num_threads()
+
+
+def cpu_sample_size(a, P, V):
+    if a.cpu_sample_views:
+        return min(a.cpu_sample_views, V)
+    # ~6 s per 1080p view of 1M Gaussians on 8 cores; aim at 10-30 s of CPU work
+    per_view = 6.0 * (P / 1e6) + 0.05
+    return int(max(1, min(V, round(15.0 / per_view))))
+
+
+def run_reference(a):
+    """--impl reference: the reference's own implementation of the path on the host cores.  The reference has no
+    CPU path and its JVP kernels cannot be compiled (float_grad.h missing), so this is the oracle PORT."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import scene_synth as ss
+    g, cams = ss.make_config(a.config, sh_degree=a.sh_degree, views=a.views or None, P=a.points or None)
+    P, V = g["means3D"].shape[0], len(cams)
+    W, H = cams[0].image_width, cams[0].image_height
+    tangent = ss.random_tangent(g, seed=2001, mask_xyz=a.mask_xyz)
+    n = cpu_sample_size(a, P, V)
+    times = []
+    for s in range(a.warmup + a.steps):
+        views = [(s * n + j) % V for j in range(n)]
+        dt, cores = cpu_jtjv_views(g, cams, tangent, views)
+        if s >= a.warmup:
+            times.append(dt)
+        if sum(times) > 150:      # keep the whole run within a few minutes
+            break
+    per_view = sum(times) / (len(times) * n)
+    value = 1.0 / (per_view * V)
+    sample = f"{n} of {V} views per step, {len(times)} timed steps; per-view time x {V} views = one matvec"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": len(times),
+        "warmup": a.warmup, "ms_per_step": per_view * V * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(a, P, V, W, H)},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+# --------------------------------------------------------------------------------------- clocks
+class ClockSampler(threading.Thread):
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                      str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(self.rows)}
+
+
+# --------------------------------------------------------------------------------------- GPU arm
+def main():
+    a = parse()
+    if a.impl == "reference":
+        return run_reference(a)
+    import torch
+    import torch.distributed as dist
+    import scene_synth as ss
+    from diff_gaussian_rasterization import _C
+    from scene.gaussian_model import GaussianModel
+    from solver.batch_training_loss import batch_training_loss
+    from solver.gaussian_model_state import GaussianModelState
+    from solver.solver_functions import LinearSolverFunctions
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback for the product path)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _C.lib()
+
+    g, cams_np = ss.make_config(a.config, sh_degree=a.sh_degree, views=a.views or None, P=a.points or None)
+    P, V = g["means3D"].shape[0], len(cams_np)
+    W, H = cams_np[0].image_width, cams_np[0].image_height
+    model = GaussianModel.from_activated(g, device=dev, num_cameras=V, requires_grad=False)
+    cams = [ss.torch_camera(c, dev, uid=i) for i, c in enumerate(cams_np)]
+    pipe = SimpleNamespace(debug=False, antialiasing=False, compute_cov3D_python=False, convert_SHs_python=False)
+    loss_func = functools.partial(batch_training_loss, iteration=1, opt=SimpleNamespace(lambda_dssim=0.2), pipe=pipe,
+                                  bg=torch.zeros(3, device=dev), train_test_exp=False,
+                                  depth_l1_weight=lambda it: 0.0, disable_ssim=True)
+    F = LinearSolverFunctions(loss_func, model, cams, batch_size=1)
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- linearisation (once per LM step; untimed for the headline, reported) ----
+    sync_all()
+    t0 = time.perf_counter()
+    F.evaluate_loss()
+    sync_all()
+    linearize_ms = (time.perf_counter() - t0) * 1e3
+    R_total = sum(vc.R for vc in F._views)
+    R_reach, pix = 0, 0
+    for vc in F._views:
+        bv = _C.buffer_view(P, vc.W, vc.H, vc.R, vc.geom, vc.binning, vc.img)
+        ln = (bv["ranges"][:, 1] - bv["ranges"][:, 0]).to(torch.int64)
+        R_reach += int(torch.minimum(ln, bv["tile_max_contrib"].to(torch.int64)).sum())
+        pix += vc.W * vc.H
+
+    tan = ss.random_tangent(g, seed=2001, mask_xyz=a.mask_xyz)
+    v = GaussianModelState.from_gaussians(model)
+    shs_t = torch.from_numpy(tan["shs"]).to(dev)
+    v.xyz_grad.copy_(torch.from_numpy(tan["means3D"]).to(dev))
+    v.features_dc_grad.copy_(shs_t[:, :1]); v.features_rest_grad.copy_(shs_t[:, 1:])
+    v.scaling_grad.copy_(torch.from_numpy(tan["scales"]).to(dev))
+    v.rotation_grad.copy_(torch.from_numpy(tan["rotations"]).to(dev))
+    v.opacity_grad.copy_(torch.from_numpy(tan["opacities"]).to(dev))
+    del shs_t
+
+    def timed(fn, steps):
+        """CUDA-event time of `steps` calls on the current stream, max over ranks (ms per step)."""
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1) / steps], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        sync_all()
+        return float(ms)
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    # ---- device-resident headline ----
+    step = lambda: F.normal_matvec(v)
+    for _ in range(a.warmup):
+        step()
+    if sampler:
+        sampler.start()
+    ms_step = timed(step, a.steps)
+
+    # ---- end to end: v from pinned host memory, result back to the host, every step ----
+    n_flat = v.length
+    v_host = torch.empty(n_flat, dtype=torch.float32).pin_memory()
+    v_host.copy_(v.packed().cpu())
+    out_host = torch.empty(n_flat, dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        v.packed().copy_(v_host, non_blocking=True)
+        out = F.normal_matvec(v)
+        out_host.copy_(out.packed(), non_blocking=True)
+
+    for _ in range(max(1, a.warmup // 2)):
+        e2e_step()
+    ms_e2e = timed(e2e_step, a.steps)
+    if sampler:
+        sampler.stop_flag = True
+
+    # ---- live per-kernel durations (separate pass of the same steps, stage timers on) ----
+    _C.timing_enable(True)
+    _C.timing_collect()
+    for _ in range(a.steps):
+        step()
+    stages = _C.timing_collect()
+    _C.timing_enable(False)
+    launches_per_step = sum(c for _, c in stages.values()) // a.steps
+    jt_ms, jt_n = stages["blend_jtjv"]
+    peaks = {}
+    pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(pk):
+        peaks = json.load(open(pk))
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    # algorithmic bytes of one k_blend_jtjv launch (DESIGN.md "kernels"): per REACHED instance 48 B primal record
+    # + 4 B id + 48 B gathered tangent record + 48 B gradient record out; per pixel n_contrib + final_T + 3 weights
+    n_local = max(len(F._views), 1)
+    alg_bytes = (R_reach * (48 + 4 + 48 + 48) + pix * (4 + 4 + 12)) / n_local
+    dur_s = (jt_ms / max(jt_n, 1)) * 1e-3
+    achieved = alg_bytes / dur_s / 1e9 if dur_s > 0 else 0.0
+    stage_share = {k: round(ms / a.steps, 4) for k, (ms, c) in stages.items() if c}
+
+    result = {
+        "metric": METRIC, "value": 1e3 / ms_step, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": workload_name(a, P, V, W, H), "views_per_rank": len(F._views),
+                   "instances_total_rank0": R_total, "instances_reached_rank0": R_reach,
+                   "l2_policy": "inputs larger than L2 (per-view records + gradients >> 126 MB)",
+                   "linearize_ms": round(linearize_ms, 2), "mask_xyz": bool(a.mask_xyz)},
+        "e2e": {"value": 1e3 / ms_e2e, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": 4 * n_flat,
+                "d2h_bytes_per_step": 4 * n_flat},
+        "gpu_launches": int(launches_per_step) * a.steps,
+        "roofline": {"kernel": "k_blend_jtjv", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": achieved / hbm_peak, "traffic": None,
+                     "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s",
+                     "launch_ms": dur_s * 1e3, "alg_bytes_per_launch": alg_bytes},
+        "stage_ms_per_step": stage_share,
+    }
+    if sampler:
+        sampler.join(timeout=2)
+        result["clocks"] = sampler.summary()
+    if rank == 0 and not a.no_cpu_baseline and world == 1:
+        n = cpu_sample_size(a, P, V)
+        dt, cores = cpu_jtjv_views(g, cams_np, tan, list(range(n)))
+        result["cpu_baseline"] = {"value": 1.0 / (dt / n * V), "unit": UNIT, "cores": cores, "kind": "port",
+                                  "sample": f"{n} of {V} views (oracle fwd+JVP then VJP), per-view time x {V}"}
+    elif rank == 0:
+        result["cpu_baseline"] = None
+    if rank == 0:
+        print(json.dumps(result))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -58,6 +58,7 @@ int32_t gslm_abi_version(void) { return 1; }
 size_t gslm_geom_bytes(int32_t P) { return carve_geom(nullptr, P).total; }
 size_t gslm_image_bytes(int32_t width, int32_t height) { return carve_image(nullptr, width, height).total; }
 size_t gslm_binning_bytes(int64_t R) { return carve_binning(nullptr, R).total; }
+size_t gslm_binning_temp_bytes(int64_t R) { return carve_binning_temp(nullptr, R).total; }
 size_t gslm_backward_scratch_bytes(int64_t R) { return align_up((size_t)R * REC_F4 * sizeof(float4)) + 128; }
 size_t gslm_jvp_scratch_bytes(int32_t P) { return align_up((size_t)P * REC_F4 * sizeof(float4)) + 128; }
 size_t gslm_jtjv_scratch_bytes(int32_t P, int64_t R) {
@@ -93,10 +94,12 @@ int32_t gslm_forward(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn 
     }
     *num_rendered = (int32_t)R;
     void* bbuf = alloc(alloc_ctx, GSLM_BUF_BINNING, gslm_binning_bytes(R));
-    if (!bbuf) { set_error("allocator returned null"); return 1; }
+    void* tbuf = alloc(alloc_ctx, GSLM_BUF_BINNING_TEMP, gslm_binning_temp_bytes(R));
+    if (!bbuf || !tbuf) { set_error("allocator returned null"); return 1; }
     BinningView bv = carve_binning(bbuf, R);
+    BinningTemp bt = carve_binning_temp(tbuf, R);
     const float* features = g->colors_precomp ? g->colors_precomp : gv.rgb;
-    if (run_binning(gv, radii, bv, iv, P, W, H, R, features, s)) return 1;
+    if (run_binning(gv, radii, bv, bt, iv, P, W, H, R, features, s)) return 1;
     if (debug_sync(cam, s, "binning")) return 1;
     if (launch_blend_fwd(bv, iv, W, H, cam->bg, out_color, out_invdepth, s)) return 1;
     return debug_sync(cam, s, "render");
@@ -127,11 +130,11 @@ int32_t gslm_forward_jvp(const GslmGaussians* g, const GslmGaussians* gt, const 
     // rasterizer_jvp_impl.h:125-325 runs primal and tangent in one pass and then shrinks its
     // buffers to the primal layout; here the primal pass IS the plain forward, followed by the
     // tangent stages on the state it left behind.
-    struct Capture { GslmAllocFn fn; void* ctx; void* p[3]; } cap = {alloc, alloc_ctx, {nullptr, nullptr, nullptr}};
+    struct Capture { GslmAllocFn fn; void* ctx; void* p[4]; } cap = {alloc, alloc_ctx, {nullptr, nullptr, nullptr, nullptr}};
     auto hook = [](void* c, int32_t which, size_t bytes) -> void* {
         Capture* k = (Capture*)c;
         void* r = k->fn(k->ctx, which, bytes);
-        if (which >= 0 && which < 3) k->p[which] = r;
+        if (which >= 0 && which < 4) k->p[which] = r;
         return r;
     };
     if (!out_color_tangent) { set_error("null argument"); return 1; }
@@ -140,13 +143,12 @@ int32_t gslm_forward_jvp(const GslmGaussians* g, const GslmGaussians* gt, const 
     const int P = g->P, W = cam->width, H = cam->height;
     ImageView iv = carve_image(cap.p[GSLM_BUF_IMAGE], W, H);
     BinningView bv = carve_binning(cap.p[GSLM_BUF_BINNING], *num_rendered);
-    // the tangent geometry (48 B per Gaussian) borrows the dead tail of the binning buffer when it
-    // fits, i.e. keys_unsorted (8 B per instance) -- otherwise a 4th allocation (which = 1 again
-    // would clobber the live buffer, so ask for geometry-class scratch with which = -1)
+    // the tangent geometry (48 B per Gaussian) borrows the binning TEMP buffer, which is dead once the
+    // forward pass has returned, when it fits; otherwise one more scratch allocation (which = -1)
     float4* tgeom = nullptr;
     const size_t need = gslm_jvp_scratch_bytes(P);
-    const size_t dead = (size_t)((char*)bv.sort_temp + bv.sort_temp_bytes - (char*)bv.keys_unsorted);
-    if (dead >= need) tgeom = reinterpret_cast<float4*>(bv.keys_unsorted);
+    if (cap.p[GSLM_BUF_BINNING_TEMP] && gslm_binning_temp_bytes(*num_rendered) >= need)
+        tgeom = reinterpret_cast<float4*>(cap.p[GSLM_BUF_BINNING_TEMP]);
     else {
         void* extra = alloc(alloc_ctx, -1, need);
         if (!extra) { set_error("allocator returned null"); return 1; }
@@ -206,7 +208,8 @@ int32_t gslm_jtjv(const GslmGaussians* g, const GslmGaussians* gt, const GslmCam
 }
 
 int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_rendered, const void* geom_buffer,
-                         const void* binning_buffer, const void* image_buffer, GslmBufferView* out) {
+                         const void* binning_buffer, const void* image_buffer, const void* binning_temp_buffer,
+                         GslmBufferView* out) {
     if (!out) { set_error("null argument"); return 1; }
     memset(out, 0, sizeof(*out));
     if (geom_buffer) {
@@ -218,11 +221,13 @@ int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_r
     }
     if (binning_buffer) {
         BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_rendered);
-        out->point_list = bv.point_list; out->keys_sorted = bv.keys_sorted;
+        out->point_list = bv.point_list;
     }
+    if (binning_temp_buffer) out->keys_sorted = carve_binning_temp(const_cast<void*>(binning_temp_buffer), num_rendered).keys_sorted;
     if (image_buffer) {
         ImageView iv = carve_image(const_cast<void*>(image_buffer), width, height);
         out->ranges = reinterpret_cast<const uint32_t*>(iv.ranges); out->n_contrib = iv.n_contrib; out->final_T = iv.final_T;
+        out->tile_max_contrib = iv.tile_max_contrib;
     }
     return 0;
 }

@@ -89,12 +89,17 @@ BinningView carve_binning(void* base, int64_t R) {
     BinningView v;
     char* p = reinterpret_cast<char*>(base);
     size_t n = (size_t)R;
-    // long-lived part first (what the cached CG path keeps reading) ...
     v.records = take<float4>(p, REC_F4 * n);
     v.point_list = take<uint32_t>(p, n);
     v.inv_perm = take<uint32_t>(p, n);
+    v.total = (size_t)(p - reinterpret_cast<char*>(base));
+    return v;
+}
+BinningTemp carve_binning_temp(void* base, int64_t R) {
+    BinningTemp v;
+    char* p = reinterpret_cast<char*>(base);
+    size_t n = (size_t)R;
     v.keys_sorted = take<uint64_t>(p, n);
-    // ... then the part that is dead once the forward pass returns
     v.keys_unsorted = take<uint64_t>(p, n);
     v.vals_unsorted = take<uint32_t>(p, n);
     v.sort_temp_bytes = sort_temp_bytes(R);
@@ -111,6 +116,7 @@ int run_scan(const GeomView& gv, int P, cudaStream_t s) {
         return 1;
     }
     size_t have = gv.scan_temp_bytes;
+    StageScope ts(ST_SCAN, s);
     GSLM_CUDA_OK(cub::DeviceScan::InclusiveSum(gv.scan_temp, have, gv.tiles_touched, gv.point_offsets, P, s));
     return 0;
 }
@@ -188,29 +194,36 @@ k_gather_records(uint32_t L, const uint64_t* __restrict__ keys, const uint32_t* 
     inv_perm[base + (uint32_t)((ty - y0) * (x1 - x0) + (tx - x0))] = k;
 }
 
-int run_binning(const GeomView& gv, const int32_t* radii, const BinningView& bv, const ImageView& iv, int P, int W,
-                int H, int64_t R, const float* features, cudaStream_t s) {
+int run_binning(const GeomView& gv, const int32_t* radii, const BinningView& bv, const BinningTemp& bt,
+                const ImageView& iv, int P, int W, int H, int64_t R, const float* features, cudaStream_t s) {
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     GSLM_CUDA_OK(cudaMemsetAsync(iv.ranges, 0, sizeof(uint2) * (size_t)gx * gy, s));
     if (R == 0 || P == 0) return 0;
+    stage_begin(ST_KEYS, s);
     k_duplicate_keys<<<(P + 255) / 256, 256, 0, s>>>(P, gv.means2D, gv.depths, gv.point_offsets, radii, gx, gy,
-                                                     bv.keys_unsorted, bv.vals_unsorted);
+                                                     bt.keys_unsorted, bt.vals_unsorted);
+    stage_end(ST_KEYS, s);
     GSLM_CUDA_OK(cudaGetLastError());
     const int bit = (int)higher_msb((uint32_t)(gx * gy));
     size_t need = 0;
-    GSLM_CUDA_OK(cub::DeviceRadixSort::SortPairs(nullptr, need, bv.keys_unsorted, bv.keys_sorted, bv.vals_unsorted,
+    GSLM_CUDA_OK(cub::DeviceRadixSort::SortPairs(nullptr, need, bt.keys_unsorted, bt.keys_sorted, bt.vals_unsorted,
                                                  bv.point_list, (int)R, 0, 32 + bit, s));
-    if (need > bv.sort_temp_bytes) {
-        set_error("sort temp storage too small: need %zu have %zu", need, bv.sort_temp_bytes);
+    if (need > bt.sort_temp_bytes) {
+        set_error("sort temp storage too small: need %zu have %zu", need, bt.sort_temp_bytes);
         return 1;
     }
-    size_t have = bv.sort_temp_bytes;
-    GSLM_CUDA_OK(cub::DeviceRadixSort::SortPairs(bv.sort_temp, have, bv.keys_unsorted, bv.keys_sorted,
-                                                 bv.vals_unsorted, bv.point_list, (int)R, 0, 32 + bit, s));
+    size_t have = bt.sort_temp_bytes;
+    stage_begin(ST_SORT, s);
+    GSLM_CUDA_OK(cub::DeviceRadixSort::SortPairs(bt.sort_temp, have, bt.keys_unsorted, bt.keys_sorted,
+                                                 bt.vals_unsorted, bv.point_list, (int)R, 0, 32 + bit, s));
+    stage_end(ST_SORT, s);
     const uint32_t L = (uint32_t)R;
-    k_tile_ranges<<<(L + 255) / 256, 256, 0, s>>>(L, bv.keys_sorted, iv.ranges);
+    stage_begin(ST_RANGES, s);
+    k_tile_ranges<<<(L + 255) / 256, 256, 0, s>>>(L, bt.keys_sorted, iv.ranges);
+    stage_end(ST_RANGES, s);
     GSLM_CUDA_OK(cudaGetLastError());
-    k_gather_records<<<(L + 255) / 256, 256, 0, s>>>(L, bv.keys_sorted, bv.point_list, gv.means2D, gv.conic_opacity,
+    StageScope ts(ST_GATHER, s);
+    k_gather_records<<<(L + 255) / 256, 256, 0, s>>>(L, bt.keys_sorted, bv.point_list, gv.means2D, gv.conic_opacity,
                                                      features, gv.depths, gv.point_offsets, radii, gx, gy, bv.records,
                                                      bv.inv_perm);
     GSLM_CUDA_OK(cudaGetLastError());

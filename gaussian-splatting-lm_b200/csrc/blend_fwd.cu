@@ -100,6 +100,7 @@ int launch_blend_fwd(const BinningView& bv, const ImageView& iv, int W, int H, c
                      float* out_invdepth, cudaStream_t s) {
     const int tiles = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
     if (tiles == 0) return 0;
+    StageScope ts(ST_BLEND_FWD, s);
     k_blend_fwd<<<tiles, TILE_PIX, 0, s>>>(iv.ranges, bv.records, W, H, bg, iv.final_T, iv.n_contrib,
                                           iv.tile_max_contrib, out_color, out_invdepth);
     GSLM_CUDA_OK(cudaGetLastError());

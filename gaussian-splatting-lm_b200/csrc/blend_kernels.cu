@@ -156,6 +156,7 @@ int launch_blend_jvp(const BinningView& bv, const ImageView& iv, int W, int H, c
         GSLM_CUDA_OK(cudaFuncSetAttribute(k_blend_jvp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr = true;
     }
+    StageScope ts(ST_BLEND_JVP, s);
     k_blend_jvp<<<tiles, TILE_PIX, smem, s>>>(iv.ranges, iv.tile_max_contrib, bv.records, bv.point_list, iv.n_contrib,
                                               tgeom, W, H, bg, bg_tangent, out_color_t, out_invdepth_t);
     GSLM_CUDA_OK(cudaGetLastError());
@@ -167,6 +168,7 @@ int launch_blend_bwd(const BinningView& bv, const ImageView& iv, int W, int H, c
     const int tiles = tiles_of(W, H);
     if (tiles == 0) return 0;
     const size_t smem = SMEM_RING + SMEM_ACC;
+    StageScope ts(ST_BLEND_BWD, s);
     k_blend_bwd<<<tiles, TILE_PIX, smem, s>>>(iv.ranges, iv.tile_max_contrib, bv.records, iv.n_contrib, iv.final_T, W,
                                               H, bg, dL_dcolor, dL_dinvdepth, inst_grads);
     GSLM_CUDA_OK(cudaGetLastError());
@@ -183,6 +185,7 @@ int launch_blend_jtjv(const BinningView& bv, const ImageView& iv, int W, int H, 
         GSLM_CUDA_OK(cudaFuncSetAttribute(k_blend_jtjv, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr = true;
     }
+    StageScope ts(ST_BLEND_JTJV, s);
     k_blend_jtjv<<<tiles, TILE_PIX, smem, s>>>(iv.ranges, iv.tile_max_contrib, bv.records, bv.point_list, iv.n_contrib,
                                                iv.final_T, tgeom, W, H, bg, weight, inst_grads, out_vJJv);
     GSLM_CUDA_OK(cudaGetLastError());

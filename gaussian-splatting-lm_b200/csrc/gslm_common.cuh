@@ -47,13 +47,16 @@ struct ImageView {  // per-pixel / per-tile state
     uint32_t* tile_max_contrib;  // [T] max n_contrib over the tile's pixels (bounds the JVP / VJP sweeps)
     size_t total;
 };
-struct BinningView {  // per-instance state
-    uint64_t* keys_unsorted;  // [R]
-    uint64_t* keys_sorted;    // [R]
-    uint32_t* vals_unsorted;  // [R]
+struct BinningView {  // per-instance state that outlives the forward pass (56 B / instance)
+    float4* records;          // [3R]
     uint32_t* point_list;     // [R] sorted Gaussian ids
     uint32_t* inv_perm;       // [R] Gaussian-major slot -> sorted position
-    float4* records;          // [3R]
+    size_t total;
+};
+struct BinningTemp {  // per-instance state that is dead once the forward pass returns (32 B / instance)
+    uint64_t* keys_sorted;    // [R]
+    uint64_t* keys_unsorted;  // [R]
+    uint32_t* vals_unsorted;  // [R]
     char* sort_temp;
     size_t sort_temp_bytes;
     size_t total;
@@ -64,6 +67,7 @@ size_t sort_temp_bytes(int64_t R);
 GeomView carve_geom(void* base, int P);
 ImageView carve_image(void* base, int W, int H);
 BinningView carve_binning(void* base, int64_t R);
+BinningTemp carve_binning_temp(void* base, int64_t R);
 
 void set_error(const char* fmt, ...);
 const char* last_error();
@@ -76,6 +80,17 @@ const char* last_error();
             return 1;                                                                        \
         }                                                                                    \
     } while (0)
+
+// ---- optional per-stage device timing (gslm_timing_*; used by bench.py for the live roofline numbers) ----
+enum Stage { ST_PREPROCESS = 0, ST_SCAN, ST_KEYS, ST_SORT, ST_RANGES, ST_GATHER, ST_BLEND_FWD, ST_PRE_TANGENT,
+             ST_BLEND_JVP, ST_BLEND_BWD, ST_BLEND_JTJV, ST_PRE_BWD, ST_COUNT };
+void stage_begin(int stage, cudaStream_t s);   // no-ops unless timing is enabled
+void stage_end(int stage, cudaStream_t s);
+struct StageScope {
+    int st; cudaStream_t s;
+    StageScope(int st_, cudaStream_t s_) : st(st_), s(s_) { stage_begin(st, s); }
+    ~StageScope() { stage_end(st, s); }
+};
 
 // ---- stage launchers (each one = one reference stage; see the .cu that defines it) ----
 struct TangentPtrs {   // tangent inputs of the forward-mode preprocess; any pointer may be null
@@ -96,8 +111,8 @@ int launch_preprocess_bwd(const GslmGaussians& g, const GslmCamera& cam, const i
                           const GslmGrads& grads, cudaStream_t s);
 // binning.cu
 int run_scan(const GeomView& gv, int P, cudaStream_t s);
-int run_binning(const GeomView& gv, const int32_t* radii, const BinningView& bv, const ImageView& iv, int P, int W,
-                int H, int64_t R, const float* features, cudaStream_t s);
+int run_binning(const GeomView& gv, const int32_t* radii, const BinningView& bv, const BinningTemp& bt,
+                const ImageView& iv, int P, int W, int H, int64_t R, const float* features, cudaStream_t s);
 // blend.cu
 int launch_blend_fwd(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg, float* out_color,
                      float* out_invdepth, cudaStream_t s);

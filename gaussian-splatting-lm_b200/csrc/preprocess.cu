@@ -131,6 +131,7 @@ int launch_preprocess(const GslmGaussians& g, const GslmCamera& cam, const GeomV
     a.cov3D_precomp = g.cov3D_precomp; a.shs = g.shs; a.colors_precomp = g.colors_precomp;
     a.viewmatrix = cam.viewmatrix; a.projmatrix = cam.projmatrix; a.campos = cam.campos;
     if (g.P == 0) return 0;
+    StageScope ts(ST_PREPROCESS, s);
     k_preprocess<<<(g.P + 255) / 256, 256, 0, s>>>(a, gv, radii);
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
@@ -224,6 +225,7 @@ int launch_preprocess_tangent(const GslmGaussians& g, const TangentPtrs& t, cons
     a.focal_x_t = -a.p.focal_x / cam.tan_fovx * t.tan_fovx;
     a.focal_y_t = -a.p.focal_y / cam.tan_fovy * t.tan_fovy;
     if (g.P == 0) return 0;
+    StageScope ts(ST_PRE_TANGENT, s);
     bool camt = t.viewmatrix || t.projmatrix || t.campos || t.tan_fovx != 0.f || t.tan_fovy != 0.f ||
                 t.scale_modifier != 0.f;
     if (camt) k_preprocess_tangent<true><<<(g.P + 255) / 256, 256, 0, s>>>(a, radii, tgeom);

@@ -306,6 +306,7 @@ int launch_preprocess_bwd(const GslmGaussians& g, const GslmCamera& cam, const i
     a.radii = radii; a.clamped = gv.clamped; a.point_offsets = gv.point_offsets; a.inv_perm = bv.inv_perm;
     a.inst_grads = inst_grads; a.g = grads;
     int grid = (g.P + 127) / 128;
+    StageScope ts(ST_PRE_BWD, s);
     if (grads.accumulate) k_preprocess_bwd<true><<<grid, 128, 0, s>>>(a);
     else k_preprocess_bwd<false><<<grid, 128, 0, s>>>(a);
     GSLM_CUDA_OK(cudaGetLastError());

@@ -42,14 +42,15 @@ class GslmGrads(C.Structure):
 class GslmBufferView(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("point_list", "keys_sorted", "ranges", "n_contrib", "final_T",
                                           "tiles_touched", "point_offsets", "depths", "means2D", "conic_opacity",
-                                          "rgb", "cov3D", "clamped")]
+                                          "rgb", "cov3D", "clamped", "tile_max_contrib")]
 
 
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_int32, C.c_size_t)
 
-EXPORTS = ("gslm_last_error", "gslm_abi_version", "gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes",
+EXPORTS = ("gslm_last_error", "gslm_abi_version", "gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_binning_temp_bytes",
            "gslm_mark_visible", "gslm_forward", "gslm_forward_jvp", "gslm_backward_scratch_bytes", "gslm_backward",
-           "gslm_jvp_scratch_bytes", "gslm_jvp_cached", "gslm_jtjv_scratch_bytes", "gslm_jtjv", "gslm_buffer_view")
+           "gslm_jvp_scratch_bytes", "gslm_jvp_cached", "gslm_jtjv_scratch_bytes", "gslm_jtjv", "gslm_buffer_view", "gslm_timing_num_stages",
+           "gslm_timing_stage_name", "gslm_timing_enable", "gslm_timing_collect")
 
 
 def lib():
@@ -60,12 +61,14 @@ def lib():
                                "(there is no CPU or PyTorch fallback for the rasterizer)")
         L = C.CDLL(_LIB_PATH)
         L.gslm_last_error.restype = C.c_char_p
-        for n in ("gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_backward_scratch_bytes",
+        for n in ("gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_binning_temp_bytes",
+                  "gslm_backward_scratch_bytes",
                   "gslm_jvp_scratch_bytes", "gslm_jtjv_scratch_bytes"):
             getattr(L, n).restype = C.c_size_t
         L.gslm_geom_bytes.argtypes = [C.c_int32]
         L.gslm_image_bytes.argtypes = [C.c_int32, C.c_int32]
         L.gslm_binning_bytes.argtypes = [C.c_int64]
+        L.gslm_binning_temp_bytes.argtypes = [C.c_int64]
         L.gslm_backward_scratch_bytes.argtypes = [C.c_int64]
         L.gslm_jvp_scratch_bytes.argtypes = [C.c_int32]
         L.gslm_jtjv_scratch_bytes.argtypes = [C.c_int32, C.c_int64]
@@ -76,7 +79,9 @@ def lib():
         L.gslm_backward.argtypes = [vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
         L.gslm_jvp_cached.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp]
         L.gslm_jtjv.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
-        L.gslm_buffer_view.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, vp, vp, vp, vp]
+        L.gslm_buffer_view.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, vp, vp, vp, vp, vp]
+        L.gslm_timing_stage_name.restype = C.c_char_p
+        L.gslm_timing_collect.argtypes = [vp, vp]
         _lib = L
     return _lib
 
@@ -128,6 +133,16 @@ class _Alloc:
     def get(self, which):
         t = self.bufs.get(which)
         return t if t is not None else torch.empty(0, dtype=torch.uint8, device=self.device)
+
+
+KEEP_SORT_SCRATCH = False     # tests: keep the sort scratch (sorted keys) of the last forward call alive
+LAST_SORT_SCRATCH = None
+
+
+def _after_forward(al):
+    global LAST_SORT_SCRATCH
+    if KEEP_SORT_SCRATCH:
+        LAST_SORT_SCRATCH = al.bufs.get(3)
 
 
 def _gaussians(means3D, colors_precomp, opacities, scales, rotations, scale_modifier, cov3D_precomp, sh, degree):
@@ -194,6 +209,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     n = C.c_int32(0)
     _check(L.gslm_forward(C.addressof(g), C.addressof(cam), al.cb, None, out_color.data_ptr(),
                           out_invdepth.data_ptr(), radii.data_ptr(), C.addressof(n), _stream()))
+    _after_forward(al)
     return int(n.value), out_color, radii, al.get(0), al.get(1), al.get(2), out_invdepth
 
 
@@ -232,6 +248,7 @@ def rasterize_gaussians_jvp(background, background_grad, means3D, means3D_grad, 
     _check(L.gslm_forward_jvp(C.addressof(g), C.addressof(gt), C.addressof(cam), C.addressof(ct), al.cb, None,
                               out_color.data_ptr(), out_invdepth.data_ptr(), radii.data_ptr(),
                               out_color_t.data_ptr(), out_invdepth_t.data_ptr(), C.addressof(n), _stream()))
+    _after_forward(al)
     return (int(n.value), out_color, radii, al.get(0), al.get(1), al.get(2), out_invdepth, out_color_t,
             out_invdepth_t)
 
@@ -327,11 +344,12 @@ def jtjv(gauss_args, tangent_args, cam_args, radii, geomBuffer, R, binningBuffer
     return scratch
 
 
-def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer):
-    """Test helper: torch views of the integer state inside the opaque buffers (bit-exactness checks)."""
+def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer, sortScratch=None):
+    """Test helper: torch views of the integer state inside the opaque buffers (bit-exactness checks).
+    sortScratch (the which = 3 allocation of the forward call, see KEEP_SORT_SCRATCH) adds `keys_sorted`."""
     v = GslmBufferView()
     _check(lib().gslm_buffer_view(int(P), int(W), int(H), int(R), _ptr(geomBuffer), _ptr(binningBuffer),
-                                  _ptr(imageBuffer), C.addressof(v)))
+                                  _ptr(imageBuffer), _ptr(sortScratch), C.addressof(v)))
 
     def view(buf, ptr, nbytes, dtype, shape):
         off = ptr - buf.data_ptr()
@@ -342,11 +360,13 @@ def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer):
     out = {}
     if binningBuffer is not None and binningBuffer.numel() and R > 0:
         out["point_list"] = view(binningBuffer, v.point_list, 4 * R, torch.int32, (R,))
-        out["keys_sorted"] = view(binningBuffer, v.keys_sorted, 8 * R, torch.int64, (R,))
+    if sortScratch is not None and sortScratch.numel() and R > 0:
+        out["keys_sorted"] = view(sortScratch, v.keys_sorted, 8 * R, torch.int64, (R,))
     if imageBuffer is not None and imageBuffer.numel():
         out["ranges"] = view(imageBuffer, v.ranges, 8 * T, torch.int32, (T, 2))
         out["n_contrib"] = view(imageBuffer, v.n_contrib, 4 * N, torch.int32, (H, W))
         out["final_T"] = view(imageBuffer, v.final_T, 4 * N, torch.float32, (H, W))
+        out["tile_max_contrib"] = view(imageBuffer, v.tile_max_contrib, 4 * T, torch.int32, (T,))
     if geomBuffer is not None and geomBuffer.numel():
         out["tiles_touched"] = view(geomBuffer, v.tiles_touched, 4 * P, torch.int32, (P,))
         out["point_offsets"] = view(geomBuffer, v.point_offsets, 4 * P, torch.int32, (P,))
@@ -357,3 +377,17 @@ def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer):
         out["cov3D"] = view(geomBuffer, v.cov3D, 24 * P, torch.float32, (P, 6))
         out["clamped"] = view(geomBuffer, v.clamped, P, torch.uint8, (P,))
     return out
+
+
+def timing_enable(on=True):
+    lib().gslm_timing_enable(1 if on else 0)
+
+
+def timing_collect():
+    """{stage name: (total ms, launches)} since the previous collect; synchronises the device."""
+    L = lib()
+    n = L.gslm_timing_num_stages()
+    ms = (C.c_float * n)()
+    cnt = (C.c_int32 * n)()
+    _check(L.gslm_timing_collect(C.addressof(ms), C.addressof(cnt)))
+    return {L.gslm_timing_stage_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n)}

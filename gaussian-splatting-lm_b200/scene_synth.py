@@ -153,3 +153,20 @@ def camera_dict(cam, bg=(0.0, 0.0, 0.0), antialiasing=False):
             "tan_fovy": math.tan(cam.FoVy * 0.5), "viewmatrix": cam.world_view_transform.reshape(16),
             "projmatrix": cam.full_proj_transform.reshape(16), "campos": cam.camera_center,
             "bg": np.asarray(bg, np.float32), "antialiasing": bool(antialiasing)}
+
+
+def torch_camera(cam, device="cuda", original_image=None, alpha_mask=None, uid=0):
+    """Camera namespace with torch tensors on `device` and the attributes the solver reads from the reference's
+    scene.cameras.Camera: image sizes, FoV, the three matrices/centre, original_image [3,H,W], alpha_mask, depth flags."""
+    import torch
+    H, W = cam.image_height, cam.image_width
+    if original_image is None:
+        original_image = torch.zeros(3, H, W, device=device)      # gt = 0 (SURVEY.md 8d)
+    return SimpleNamespace(
+        image_width=W, image_height=H, FoVx=cam.FoVx, FoVy=cam.FoVy, znear=cam.znear, zfar=cam.zfar, uid=uid,
+        image_name=f"synth_{uid:04d}",
+        world_view_transform=torch.from_numpy(cam.world_view_transform).to(device),
+        projection_matrix=torch.from_numpy(cam.projection_matrix).to(device),
+        full_proj_transform=torch.from_numpy(cam.full_proj_transform).to(device),
+        camera_center=torch.from_numpy(cam.camera_center).to(device),
+        original_image=original_image, alpha_mask=alpha_mask, depth_reliable=False, invdepthmap=None)

@@ -1,0 +1,344 @@
+"""LinearSolverFunctions: the callables CG / CGLS consume (reference solver/solver_functions.py:15-138) --
+matvec = J v, matvec_T = J^T u, dot, saxpy, evaluate_loss, get_initial_solution -- plus the additive
+normal_matvec = J^T J v (+ D v) that plugs into conjugate_gradient(matvec=...).
+
+Two execution modes with identical results:
+
+generic  (any loss_func): exactly the reference's composition -- forward-mode AD through loss_func for J v,
+         loss.backward for J^T u; the rasterizer kernels run underneath via autograd.Function.{jvp,backward}.
+cached   (loss_func is a functools.partial of solver.batch_training_loss.batch_training_loss with
+         disable_ssim=True, the configuration the LM driver uses, train_jvp.py:212): the linearisation point is
+         fixed for the whole CG solve, so evaluate_loss() keeps, per view, the sorted instance records, tile
+         ranges, final_T / n_contrib and the pixel weights; every later matvec / matvec_T / normal_matvec then
+         costs only the tangent-preprocess, one tile kernel and the per-Gaussian adjoint kernel per view: no
+         preprocess, no scan / sort, no host synchronisation.
+         normal_matvec uses the fused tangent->adjoint tile kernel, so J v is never written to HBM.
+
+Multi-GPU (torch.distributed initialised, one process per GPU): views are sharded over ranks, parameters and
+parameter-space vectors are replicated, and each normal_matvec / matvec_T ends with ONE allreduce(sum) of the
+packed 59 P-float result; residual-space dots allreduce one scalar.
+"""
+import functools
+import math
+
+import torch
+import torch.autograd.forward_ad as fwAD
+
+from diff_gaussian_rasterization import _C
+from solver.batch_training_loss import batch_training_loss, gather_targets
+from solver.gaussian_model_state import (GaussianModelDampMatrix, GaussianModelParamGroupMask,
+                                         GaussianModelSplatMask, GaussianModelState)
+from solver.loss_image_state import BatchLossImageState, MultiBatchLossImageState
+
+
+def _dist():
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        return dist
+    return None
+
+
+class _ViewCache:
+    """Linearisation state of one view (everything a CG iteration needs, all device-resident)."""
+    __slots__ = ("cam", "H", "W", "R", "radii", "geom", "binning", "img", "weight", "mask", "residual", "cam_args")
+
+
+class LinearSolverFunctions:
+
+    def __init__(self, loss_func, gaussians, viewpoint_cams, batch_size=-1, param_mask=None, splat_mask=None,
+                 cached=None, shard_views=True):
+        self.loss_func = loss_func
+        self.gaussians = gaussians
+        self.all_cams = list(viewpoint_cams)
+        d = _dist() if shard_views else None
+        self.dist = d
+        # data-parallel axis: views.  rank r owns views r, r + world, ... (round robin keeps per-rank R balanced
+        # for rigs whose neighbouring cameras see similar content)
+        self.viewpoint_cams = self.all_cams[d.get_rank()::d.get_world_size()] if d else self.all_cams
+        self.B = len(self.viewpoint_cams)
+        self.batch_size = max(self.B, 1) if batch_size < 0 else batch_size
+        self.batch_stats = {}
+        self.param_mask = param_mask
+        self.splat_mask = splat_mask
+        legal = (isinstance(loss_func, functools.partial) and loss_func.func is batch_training_loss
+                 and bool(loss_func.keywords.get("disable_ssim", False))
+                 and not loss_func.keywords.get("train_test_exp", False)
+                 and not getattr(loss_func.keywords.get("pipe"), "compute_cov3D_python", False)
+                 and not getattr(loss_func.keywords.get("pipe"), "convert_SHs_python", False))
+        if cached and not legal:
+            raise ValueError("cached=True needs loss_func = partial(batch_training_loss, ..., disable_ssim=True)")
+        self.cached = legal if cached is None else bool(cached)
+        self._views = None
+        self._scratch = None
+
+    # ------------------------------------------------------------------ reference API
+    def get_initial_solution(self):
+        return GaussianModelState.from_gaussians(self.gaussians, param_mask=self.param_mask,
+                                                 splat_mask=self.splat_mask)
+
+    def _batches(self):
+        for start in range(0, self.B, self.batch_size):
+            yield start, min(start + self.batch_size, self.B)
+
+    def evaluate_loss(self, with_batch_stats=False, with_grad=False):
+        """r(theta) at the current parameters; in cached mode this is also the linearisation pass."""
+        if self.cached and not with_grad and not with_batch_stats:
+            self.linearize()
+            return self.loss
+        batch_stats = {} if with_batch_stats else None
+        with torch.enable_grad() if with_grad else torch.no_grad():
+            losses = []
+            for start, end in self._batches():
+                loss = self.loss_func(gaussians=self.gaussians, viewpoint_cams=self.viewpoint_cams[start:end],
+                                      batch_stats=batch_stats)
+                losses.append(loss)
+                if with_batch_stats:
+                    for k, v in batch_stats.items():
+                        if start == 0:
+                            self.batch_stats[k] = [v]
+                        else:
+                            self.batch_stats[k].append(v)
+            self.loss = MultiBatchLossImageState(losses)
+        return self.loss
+
+    def _scalar(self, t):
+        if self.dist and isinstance(t, torch.Tensor):
+            t = t.clone()
+            self.dist.all_reduce(t)
+        return t
+
+    @property
+    def loss_scalar(self):
+        return self._scalar(self.loss.loss_scalar)
+
+    @property
+    def Ll1_scalar(self):
+        return self._scalar(self.loss.Ll1_scalar)
+
+    @property
+    def depth_loss_scalar(self):
+        return self._scalar(self.loss.Ll1depth_scalar)
+
+    @property
+    def get_batch_stats(self):
+        return self.batch_stats
+
+    def matvec(self, v):
+        assert isinstance(v, GaussianModelState), "v must be an instance of GaussianModelState"
+        if self.cached:
+            return self._matvec_cached(v)
+        with torch.no_grad(), fwAD.dual_level(), self.gaussians.make_dual(v):
+            tangents = []
+            for start, end in self._batches():
+                loss_dual = self.loss_func(gaussians=self.gaussians, viewpoint_cams=self.viewpoint_cams[start:end])
+                tangents.append(loss_dual.unpack_dual()[1])
+            return MultiBatchLossImageState(tangents)
+
+    def matvec_T(self, vs):
+        assert isinstance(vs, MultiBatchLossImageState), "vs must be an instance of MultiBatchLossImageState"
+        if self.cached:
+            return self._matvec_T_cached(vs)
+        with torch.enable_grad():
+            self.gaussians.zero_grad()
+            for idx, (start, end) in enumerate(self._batches()):
+                loss_batch = self.loss_func(gaussians=self.gaussians, viewpoint_cams=self.viewpoint_cams[start:end])
+                loss_batch.backward(vs.batch_losses[idx], retain_graph=True)
+        g = self.gaussians
+        for name in ("_xyz", "_features_dc", "_features_rest", "_scaling", "_rotation", "_opacity"):
+            grad = getattr(g, name).grad
+            assert grad is None or not torch.isnan(grad).any(), f"NaN detected in gaussians.{name}.grad"
+        out = GaussianModelState.from_gaussians_grad(g, param_mask=None, splat_mask=None)
+        if self.dist:
+            self.dist.all_reduce(out.packed())
+        return GaussianModelState(*out.tensors(), param_mask=self.param_mask, splat_mask=self.splat_mask,
+                                  _flat=out.flat)
+
+    def dot(self, v1, v2, damp=1.0):
+        s = v1.dot(v2, damp)
+        if self.dist and isinstance(v1, (MultiBatchLossImageState, BatchLossImageState)):
+            t = torch.tensor([s], dtype=torch.float64, device=self.gaussians._xyz.device)
+            self.dist.all_reduce(t)
+            s = t.item()
+        return s
+
+    def saxpy(self, a, x, y):
+        return a * x + y
+
+    # ------------------------------------------------------------------ cached mode
+    def _kw(self, name, default=None):
+        return self.loss_func.keywords.get(name, default)
+
+    def _activated(self):
+        """Kernel inputs at the linearisation point + what the activation JVP / VJP need."""
+        g = self.gaussians
+        with torch.no_grad():
+            raw_rot = g._rotation.detach()
+            norm = raw_rot.norm(dim=1, keepdim=True).clamp_min(1e-12)   # F.normalize eps
+            act = {"means3D": g._xyz.detach().contiguous(), "opacities": torch.sigmoid(g._opacity.detach()),
+                   "scales": torch.exp(g._scaling.detach()), "rotations": raw_rot / norm, "rot_norm": norm,
+                   "shs": torch.cat((g._features_dc.detach(), g._features_rest.detach()), dim=1).contiguous(),
+                   "sh_degree": int(g.active_sh_degree)}
+        return act
+
+    def _gauss_args(self):
+        a = self._act
+        e = self._empty
+        return (a["means3D"], e, a["opacities"], a["scales"], a["rotations"], 1.0, e, a["shs"], a["sh_degree"])
+
+    def linearize(self):
+        """Forward-render every local view once; keep per-view caches, residuals and pixel weights."""
+        pipe, bg = self._kw("pipe"), self._kw("bg")
+        dev = self.gaussians._xyz.device
+        self._empty = torch.empty(0, device=dev)
+        self._act = a = self._activated()
+        self._views = []
+        losses = []
+        for start, end in self._batches():
+            cams = self.viewpoint_cams[start:end]
+            Hm, Wm = max(c.image_height for c in cams), max(c.image_width for c in cams)
+            resid = torch.zeros((len(cams), 3, Hm, Wm), dtype=torch.float32, device=dev)
+            gt, masks = gather_targets(cams, resid)
+            for i, cam in enumerate(cams):
+                H, W = int(cam.image_height), int(cam.image_width)
+                vc = _ViewCache()
+                vc.cam, vc.H, vc.W = cam, H, W
+                tfx, tfy = math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5)
+                (vc.R, color, vc.radii, vc.geom, vc.binning, vc.img, _) = _C.rasterize_gaussians(
+                    bg, a["means3D"], self._empty, a["opacities"], a["scales"], a["rotations"], 1.0, self._empty,
+                    cam.world_view_transform, cam.full_proj_transform, tfx, tfy, H, W, a["shs"], a["sh_degree"],
+                    cam.camera_center, False, pipe.antialiasing, pipe.debug)
+                vc.cam_args = (bg, cam.world_view_transform, cam.full_proj_transform, tfx, tfy, H, W,
+                               cam.camera_center, pipe.antialiasing, pipe.debug)
+                # d clamp(x,0,1)/dx as torch defines it (inclusive bounds) times the alpha mask
+                m = ((color >= 0) & (color <= 1)).to(torch.float32)
+                if masks is not None:
+                    m = m * masks[i, :, :H, :W]
+                    resid[i, :, :H, :W] = color.clamp(0, 1) * masks[i, :, :H, :W] - gt[i, :, :H, :W]
+                else:
+                    resid[i, :, :H, :W] = color.clamp(0, 1) - gt[i, :, :H, :W]
+                vc.mask = m
+                vc.weight = 2.0 * m * m      # two aliased residual blocks => multiplicity 2 (batch_training_loss.py:15-17)
+                self._views.append(vc)
+            depth_block = torch.zeros((0,), dtype=torch.float32, device=dev)
+            sizes = [(c.image_height, c.image_width) for c in cams]
+            losses.append(BatchLossImageState(resid, resid, depth_block, sizes, False))
+        self.loss = MultiBatchLossImageState(losses)
+        return self.loss
+
+    def _tangent_inputs(self, v):
+        """Activation JVP: raw-parameter tangent -> tangents of the kernel inputs (scene/gaussian_model.py:192-220)."""
+        a = self._act
+        q = a["rotations"]
+        vr = v.rotation_grad
+        t_rot = (vr - q * (q * vr).sum(dim=1, keepdim=True)) / a["rot_norm"]
+        o = a["opacities"]
+        return (v.xyz_grad.contiguous(), None, o * (1.0 - o) * v.opacity_grad, a["scales"] * v.scaling_grad, t_rot,
+                None, torch.cat((v.features_dc_grad, v.features_rest_grad), dim=1))
+
+    def _act_accumulators(self):
+        """Packed activated-space gradient buffer [means3D | shs | scales | rotations | opacity] (59 P floats:
+        the allreduce payload) and the 8-tuple of sinks the kernels write into."""
+        a = self._act
+        P, M = a["means3D"].shape[0], a["shs"].shape[1]
+        flat = torch.zeros(P * (3 + 3 * M + 3 + 4 + 1), dtype=torch.float32, device=a["means3D"].device)
+        off = 0
+        views = {}
+        for name, shape in (("means3D", (P, 3)), ("shs", (P, M, 3)), ("scales", (P, 3)), ("rotations", (P, 4)),
+                            ("opacities", (P, 1))):
+            n = 1
+            for d in shape:
+                n *= d
+            views[name] = flat[off:off + n].view(shape)
+            off += n
+        sinks = (None, None, views["opacities"], views["means3D"], None, views["shs"], views["scales"],
+                 views["rotations"])
+        return flat, views, sinks
+
+    def _to_state(self, views, extra=None):
+        """Activation VJP: activated-space gradients -> raw-parameter GaussianModelState (masked)."""
+        a = self._act
+        g = self.gaussians
+        out = GaussianModelState.from_gaussians(g)
+        out.xyz_grad.copy_(views["means3D"])
+        out.features_dc_grad.copy_(views["shs"][:, :1])
+        out.features_rest_grad.copy_(views["shs"][:, 1:])
+        torch.mul(a["scales"], views["scales"], out=out.scaling_grad)
+        q, gr = a["rotations"], views["rotations"]
+        out.rotation_grad.copy_((gr - q * (q * gr).sum(dim=1, keepdim=True)) / a["rot_norm"])
+        o = a["opacities"]
+        torch.mul(o * (1.0 - o), views["opacities"], out=out.opacity_grad)
+        if extra is not None:
+            out.packed().add_(extra)
+        return GaussianModelState(*out.tensors(), param_mask=self.param_mask, splat_mask=self.splat_mask,
+                                  _flat=out.flat)
+
+    def _require_linearized(self):
+        if self._views is None:
+            self.linearize()
+
+    def _matvec_cached(self, v):
+        self._require_linearized()
+        targs = self._tangent_inputs(v)
+        gargs = self._gauss_args()
+        out, k = [], 0
+        for start, end in self._batches():
+            cams = self.viewpoint_cams[start:end]
+            Hm, Wm = max(c.image_height for c in cams), max(c.image_width for c in cams)
+            t = torch.zeros((len(cams), 3, Hm, Wm), dtype=torch.float32, device=v.xyz_grad.device)
+            for i in range(len(cams)):
+                vc = self._views[k]
+                k += 1
+                jv, _ = _C.jvp_cached(gargs, targs, vc.cam_args, vc.radii, vc.geom, vc.R, vc.binning, vc.img)
+                t[i, :, :vc.H, :vc.W] = jv * vc.mask
+            depth_block = torch.zeros((0,), dtype=torch.float32, device=t.device)
+            out.append(BatchLossImageState(t, t, depth_block, [(c.image_height, c.image_width) for c in cams], False))
+        return MultiBatchLossImageState(out)
+
+    def _matvec_T_cached(self, vs):
+        self._require_linearized()
+        flat, views, sinks = self._act_accumulators()
+        a = self._act
+        k = 0
+        for idx, (start, end) in enumerate(self._batches()):
+            u = vs.batch_losses[idx]
+            cot = u.Ll1_per_pixel + u.ssim_loss_per_pixel     # J^T of the two aliased blocks
+            for i in range(end - start):
+                vc = self._views[k]
+                k += 1
+                g = cot[i, :, :vc.H, :vc.W] * vc.mask
+                bg, vm, pm, tfx, tfy, H, W, campos, aa, dbg = vc.cam_args
+                _C.rasterize_gaussians_backward(bg, a["means3D"], vc.radii, self._empty, a["opacities"], a["scales"],
+                                                a["rotations"], 1.0, self._empty, vm, pm, tfx, tfy, g, None, a["shs"],
+                                                a["sh_degree"], campos, vc.geom, vc.R, vc.binning, vc.img, aa, dbg,
+                                                accumulate_into=sinks)
+        if self.dist:
+            self.dist.all_reduce(flat)
+        return self._to_state(views)
+
+    def normal_matvec(self, v, damp=None, return_quad=False):
+        """J^T J v (+ damp * v): the Gauss-Newton product CG needs, one fused tile kernel per view.
+        damp: None, a float (lambda: adds lambda v) or a GaussianModelDampMatrix (adds D v).
+        return_quad=True also returns v^T J^T J v as a 0-dim device tensor (CG's p^T A p without a second pass)."""
+        assert isinstance(v, GaussianModelState), "v must be an instance of GaussianModelState"
+        if not self.cached:
+            out = self.matvec_T(self.matvec(v))
+            if damp is not None:
+                out = out + v * damp
+            return (out, None) if return_quad else out
+        self._require_linearized()
+        targs = self._tangent_inputs(v)
+        gargs = self._gauss_args()
+        flat, views, sinks = self._act_accumulators()
+        quad = torch.zeros(1, dtype=torch.float32, device=flat.device) if return_quad else None
+        for vc in self._views:
+            self._scratch = _C.jtjv(gargs, targs, vc.cam_args, vc.radii, vc.geom, vc.R, vc.binning, vc.img, vc.weight,
+                                    sinks, out_vJJv=quad, scratch=self._scratch)
+        if self.dist:
+            self.dist.all_reduce(flat)
+            if quad is not None:
+                self.dist.all_reduce(quad)
+        extra = None
+        if damp is not None:
+            extra = (v * damp).packed()
+        out = self._to_state(views, extra)
+        return (out, quad) if return_quad else out

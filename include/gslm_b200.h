@@ -82,9 +82,12 @@ typedef struct GslmGrads {
 /* Scratch allocator: must return a device pointer to at least `bytes` bytes, 128-byte
  * aligned, that stays valid until the caller frees it.  `which`: 0 geometry, 1 binning,
  * 2 image buffer -- the three opaque buffers of the reference
- * (geomBuffer / binningBuffer / imgBuffer, DGR/rasterize_points.cu:80-88). */
+ * (geomBuffer / binningBuffer / imgBuffer, DGR/rasterize_points.cu:80-88) -- 3 = sort scratch
+ * (keys + radix-sort temporaries, 32 B / instance) that may be freed or reused as soon as the
+ * call returns (the reference trims the same data off its binning buffer after the forward pass,
+ * rasterizer_impl.cu:383-388), -1 = anonymous scratch for the duration of the call. */
 typedef void* (*GslmAllocFn)(void* ctx, int32_t which, size_t bytes);
-enum { GSLM_BUF_GEOM = 0, GSLM_BUF_BINNING = 1, GSLM_BUF_IMAGE = 2 };
+enum { GSLM_BUF_GEOM = 0, GSLM_BUF_BINNING = 1, GSLM_BUF_IMAGE = 2, GSLM_BUF_BINNING_TEMP = 3 };
 
 const char* gslm_last_error(void);
 int32_t gslm_abi_version(void);
@@ -94,6 +97,7 @@ int32_t gslm_abi_version(void);
 size_t gslm_geom_bytes(int32_t P);
 size_t gslm_image_bytes(int32_t width, int32_t height);
 size_t gslm_binning_bytes(int64_t num_rendered);
+size_t gslm_binning_temp_bytes(int64_t num_rendered);
 
 /* Replaces _C.mark_visible (DGR/rasterize_points.cu:401-420). present: uint8 [P]. */
 int32_t gslm_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
@@ -151,10 +155,19 @@ int32_t gslm_jtjv(const GslmGaussians* g, const GslmGaussians* gt, const GslmCam
                   int32_t num_rendered, const float* weight, void* scratch, GslmGrads* grads, float* out_vJJv,
                   void* stream);
 
+/* ---- optional per-stage device timing (no reference counterpart; bench.py's live roofline numbers) ----
+ * When enabled, each stage brackets its kernels with a cudaEvent pair on the launching stream.
+ * gslm_timing_collect synchronises the device and returns, per stage, the summed elapsed milliseconds and the
+ * number of launches since the previous collect (arrays of gslm_timing_num_stages() entries). */
+int32_t gslm_timing_num_stages(void);
+const char* gslm_timing_stage_name(int32_t stage);
+void gslm_timing_enable(int32_t on);
+int32_t gslm_timing_collect(float* ms, int32_t* counts);
+
 /* Introspection for tests (bit-exact binning checks): device pointers INTO the buffers. */
 typedef struct GslmBufferView {
     const uint32_t* point_list;   /* [R] sorted Gaussian ids   (rasterizer.h BinningState::point_list) */
-    const uint64_t* keys_sorted;  /* [R] tile<<32 | depth bits                                          */
+    const uint64_t* keys_sorted;  /* [R] tile<<32 | depth bits (lives in the sort scratch; NULL without it) */
     const uint32_t* ranges;       /* [T,2] per-tile [start,end) (ImageState::ranges)                    */
     const uint32_t* n_contrib;    /* [H*W]                                                              */
     const float* final_T;         /* [H*W]                                                              */
@@ -166,9 +179,11 @@ typedef struct GslmBufferView {
     const float* rgb;             /* [P,3]                                                              */
     const float* cov3D;           /* [P,6]                                                              */
     const uint8_t* clamped;       /* [P] bit c set <=> channel c clamped                                */
+    const uint32_t* tile_max_contrib; /* [T] max n_contrib over the tile: instances the cached sweeps visit */
 } GslmBufferView;
 int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_rendered, const void* geom_buffer,
-                         const void* binning_buffer, const void* image_buffer, GslmBufferView* out);
+                         const void* binning_buffer, const void* image_buffer, const void* binning_temp_buffer,
+                         GslmBufferView* out);
 
 #ifdef __cplusplus
 }

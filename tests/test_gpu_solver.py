@@ -1,0 +1,154 @@
+"""GPU tests of the solver-facing path (run with -m gpu): batch_render == per-view render, the cached
+(linearisation-reusing, fused) mode of LinearSolverFunctions == the generic autograd / forward-AD mode (which is
+the reference's own composition), adjoint identity, and a CG solve on the fused J^T J v."""
+import functools
+from types import SimpleNamespace
+
+import numpy as np
+import pytest
+import torch
+
+import scene_synth as ss
+import helpers as h
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(P=4000, V=4, W=128, H=96, deg=2, seed=3, masks=True):
+    from scene.gaussian_model import GaussianModel
+    from solver.batch_training_loss import batch_training_loss
+    g = ss.make_gaussians(P, sh_degree=deg, seed=seed, scale_mult=0.8)
+    g["rotations"] = (g["rotations"] * 1.7).astype(np.float32)       # raw quaternions are NOT unit: exercises normalize
+    model = GaussianModel.from_activated(g, device="cuda", num_cameras=V)
+    gen = torch.Generator(device="cpu").manual_seed(seed)
+    cams = []
+    for i, c in enumerate(ss.hemisphere_rig(V, W, H)):
+        gt = torch.rand(3, H, W, generator=gen).cuda()
+        am = (torch.rand(1, H, W, generator=gen) > 0.2).float().cuda() if (masks and i == 1) else None
+        cams.append(ss.torch_camera(c, "cuda", original_image=gt, alpha_mask=am, uid=i))
+    pipe = SimpleNamespace(debug=False, antialiasing=False, compute_cov3D_python=False, convert_SHs_python=False)
+    opt = SimpleNamespace(lambda_dssim=0.2)
+    bg = torch.tensor([0.0, 0.0, 0.0], device="cuda")
+    loss_func = functools.partial(batch_training_loss, iteration=1, opt=opt, pipe=pipe, bg=bg, train_test_exp=False,
+                                  depth_l1_weight=lambda it: 0.0, disable_ssim=True)
+    return model, cams, loss_func, pipe, bg
+
+
+def _rand_state(model, seed):
+    from solver.gaussian_model_state import GaussianModelState
+    s = GaussianModelState.from_gaussians(model)
+    s.packed().copy_(torch.randn(s.length, generator=torch.Generator().manual_seed(seed)).cuda())
+    s.exposure_grad.zero_()
+    return s
+
+
+def test_batch_render_equals_per_view_render():
+    """tests/test_batch_render.py:82-89 of the reference: render/depth allclose(atol=1e-6), radii exact."""
+    from gaussian_renderer import render
+    from gaussian_renderer.batch_render import batch_render
+    model, cams, _, pipe, bg = _setup()
+    with torch.no_grad():
+        pkg = batch_render(cams, model, pipe, bg)
+        singles = [render(c, model, pipe, bg) for c in cams]
+    assert pkg["render"].shape == (len(cams), 3, 96, 128)
+    for i, s in enumerate(singles):
+        assert torch.allclose(pkg["render"][i], s["render"], atol=1e-6)
+        assert torch.allclose(pkg["depth"][i], s["depth"], atol=1e-6)
+    radii = torch.stack([s["radii"] for s in singles])
+    assert torch.equal(pkg["max_radii"], radii.max(dim=0).values)
+    assert torch.equal(pkg["viewcount"], (radii > 0).sum(dim=0))
+    assert torch.equal(pkg["visibility_filter"], (radii.max(dim=0).values > 0).nonzero())
+
+
+def test_batch_gradients_equal_sum_of_single_view_gradients():
+    """tests/test_batch_training_loss.py:104-110 of the reference (atol 1e-5 on grads)."""
+    from gaussian_renderer import render
+    from gaussian_renderer.batch_render import batch_render
+    model, cams, _, pipe, bg = _setup(P=1500)
+    u = torch.randn(len(cams), 3, 96, 128, device="cuda")
+    model.zero_grad()
+    pkg = batch_render(cams, model, pipe, bg)
+    (pkg["render"] * u).sum().backward()
+    names = ("_xyz", "_features_dc", "_features_rest", "_scaling", "_rotation", "_opacity")
+    batch = [getattr(model, n).grad.clone() for n in names]
+    model.zero_grad()
+    for i, c in enumerate(cams):
+        (render(c, model, pipe, bg)["render"] * u[i]).sum().backward()
+    for n, b in zip(names, batch):
+        s = getattr(model, n).grad
+        assert torch.allclose(b, s, atol=1e-5 * max(1.0, float(s.abs().max()))), n
+
+
+def test_cached_mode_equals_generic_mode():
+    from solver.solver_functions import LinearSolverFunctions
+    model, cams, loss_func, pipe, bg = _setup()
+    Fc = LinearSolverFunctions(loss_func, model, cams, batch_size=3)
+    Fg = LinearSolverFunctions(loss_func, model, cams, batch_size=3, cached=False)
+    assert Fc.cached and not Fg.cached
+    Lc, Lg = Fc.evaluate_loss(), Fg.evaluate_loss()
+    assert abs(float(Fc.loss_scalar) - float(Fg.loss_scalar)) <= 1e-5 * float(Fg.loss_scalar)
+    for a, b in zip(Lc.batch_losses, Lg.batch_losses):
+        assert torch.allclose(a.Ll1_per_pixel, b.Ll1_per_pixel, atol=1e-6)
+    v = _rand_state(model, 7)
+    Jc, Jg = Fc.matvec(v), Fg.matvec(v)
+    for a, b in zip(Jc.batch_losses, Jg.batch_losses):
+        assert h.rel_l2(a.Ll1_per_pixel.cpu().numpy(), b.Ll1_per_pixel.cpu().numpy()) < 1e-3
+    u = Jg * 0.5 + Lg * 1.0
+    Tc, Tg = Fc.matvec_T(u), Fg.matvec_T(u)
+    for n, a, b in zip(("xyz", "dc", "rest", "scaling", "rotation", "opacity"), Tc.tensors(), Tg.tensors()):
+        assert h.rel_l2(a.cpu().numpy(), b.cpu().numpy()) < 1e-3, n
+    # fused J^T J v == J^T (J v) of the generic (reference-composition) mode; quad == <Jv, Jv>
+    Nc, quad = Fc.normal_matvec(v, return_quad=True)
+    Ng = Fg.matvec_T(Fg.matvec(v))
+    for n, a, b in zip(("xyz", "dc", "rest", "scaling", "rotation", "opacity"), Nc.tensors(), Ng.tensors()):
+        assert h.rel_l2(a.cpu().numpy(), b.cpu().numpy()) < 1e-3, n
+    q_ref = Fg.dot(Jg, Jg)
+    assert abs(float(quad) - q_ref) <= 1e-3 * abs(q_ref)
+    # damping
+    from solver.gaussian_model_state import GaussianModelDampMatrix
+    D = GaussianModelDampMatrix(5e2, 5e2, 5e2, 5e-2, 5e-2, 1e1, 0.0)
+    Nd = Fc.normal_matvec(v, damp=D)
+    assert h.rel_l2(Nd.packed().cpu().numpy(), (Nc + v * D).packed().cpu().numpy()) < 1e-6
+
+
+def test_adjoint_identity_through_solver_interface():
+    """tests/test_matvec.py of the reference (rel 1e-4), on the cached path, away from the documented non-adjoint
+    quirks (alpha clamp, cov clamp): small extent, capped opacity."""
+    from scene.gaussian_model import GaussianModel
+    from solver.solver_functions import LinearSolverFunctions
+    model, cams, loss_func, pipe, bg = _setup(masks=False)
+    g = ss.make_gaussians(3000, sh_degree=2, seed=11, scale_mult=0.8, extent=0.4)
+    g["opacities"] = np.minimum(g["opacities"], 0.9).astype(np.float32)
+    model = GaussianModel.from_activated(g, device="cuda", num_cameras=len(cams))
+    F = LinearSolverFunctions(loss_func, model, cams)
+    F.evaluate_loss()
+    v = _rand_state(model, 8)
+    Jv = F.matvec(v)
+    u = F.loss * 1.0 + Jv * 0.1
+    lhs, rhs = F.dot(u, Jv), F.dot(F.matvec_T(u), v)
+    assert abs(lhs - rhs) <= 1e-4 * max(abs(lhs), abs(rhs))
+
+
+def test_cg_on_fused_normal_matvec_and_cgls_agree(capsys):
+    """Solve (J^T J + D) s = -J^T r with conjugate_gradient(matvec=normal_matvec) and compare with cgls_damped on
+    (matvec, matvec_T): same Krylov space => same iterate after the same number of steps (rel 1e-3)."""
+    from solver.conjugate_gradient import cgls_damped, conjugate_gradient
+    from solver.gaussian_model_state import GaussianModelDampMatrix, GaussianModelParamGroupMask
+    from solver.solver_functions import LinearSolverFunctions
+    model, cams, loss_func, pipe, bg = _setup(P=2000)
+    pm = GaussianModelParamGroupMask(mask_xyz=True, mask_exposure=True)        # train_jvp.py:221-227
+    D = GaussianModelDampMatrix(5e2, 5e2, 5e2, 5e-2, 5e-2, 1e1, 1.0)
+    F = LinearSolverFunctions(loss_func, model, cams, param_mask=pm)
+    F.evaluate_loss()
+    b = -1 * F.loss
+    rhs = F.matvec_T(b)
+    x0 = F.get_initial_solution()
+    s_cg = conjugate_gradient(lambda p: F.normal_matvec(p, damp=D), lambda x, y: x + y, lambda x, y: x - y,
+                              lambda x, y: F.dot(x, y), lambda a, x: a * x, rhs, x0, max_iter=3, tol=0.0)
+    s_ls = cgls_damped(F.matvec, F.matvec_T, F.dot, F.saxpy, b, x0, damp=D, max_iter=3, restart_iter=3,
+                       recompute_residual=False)
+    capsys.readouterr()
+    assert float(s_cg.xyz_grad.abs().sum()) == 0.0
+    assert h.rel_l2(s_cg.packed().cpu().numpy(), s_ls.packed().cpu().numpy()) < 1e-3
+    lin = F.saxpy(-1.0, F.matvec(s_cg), b)
+    assert F.dot(lin, lin) + F.dot(s_cg, s_cg, D) < F.dot(b, b)
