@@ -45,9 +45,11 @@ size_t scan_temp_bytes(int P) {
     return align_up((size_t)(P / 128 + 1024) * 16 + 4096);
 }
 size_t sort_temp_bytes(int64_t R) {
-    // cub::DeviceRadixSort (non-DoubleBuffer overload) needs one alternate key and value
-    // buffer plus histograms; generous bound, checked against CUB's own answer at run time.
-    return align_up((size_t)R * (sizeof(uint64_t) + sizeof(uint32_t)) + ((size_t)1 << 20));
+    // cub::DeviceRadixSort (non-DoubleBuffer overload) needs one alternate key and value buffer
+    // (12 B / item) plus the onesweep look-back table: 256 counters x 4 B per tile of >= 2048 items
+    // (<= 0.5 B / item; measured 0.18 B / item at R = 19.8 M) plus per-pass histograms.  The bound
+    // is checked against CUB's own answer at run time.
+    return align_up((size_t)R * (sizeof(uint64_t) + sizeof(uint32_t)) + (size_t)R / 2 + ((size_t)1 << 20));
 }
 
 template <class T> static T* take(char*& p, size_t n) {
