@@ -1,0 +1,105 @@
+"""ctypes front-end of oracle/_ref/libgsref.so -- the REFERENCE's own primal / VJP / binning CUDA kernels
+(unmodified forward.cu, backward.cu, rasterizer_impl.cu) built for sm_100a by oracle/Makefile (target `ref`).
+
+TEST INFRASTRUCTURE ONLY: GPU-side parity oracle, bit-exactness oracle for the tile sort / ranges, and the timing
+baseline "kernel to beat".  Only tests/ and bench scripts import it; the product never does.  Needs a GPU and the
+prebuilt library (it cannot be rebuilt on the GPU box: /root/reference does not exist there)."""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+PATH = os.path.join(_HERE, "_ref", "libgsref.so")
+_LIB = None
+
+
+def available():
+    return os.path.exists(PATH)
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = C.CDLL(PATH)
+        _LIB.gsref_last_error.restype = C.c_char_p
+        vp, f, i = C.c_void_p, C.c_float, C.c_int
+        _LIB.gsref_forward.argtypes = [i, i, i, vp, i, i, vp, vp, vp, vp, vp, f, vp, vp, vp, vp, vp, f, f, i, i, vp, vp,
+                                       vp, i]
+        _LIB.gsref_backward.argtypes = [i, i, i, vp, i, i, vp, vp, vp, vp, vp, f, vp, vp, vp, vp, vp, f, f, vp, vp, vp,
+                                        vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i]
+        _LIB.gsref_state.argtypes = [vp] * 8
+    return _LIB
+
+
+def _p(t):
+    return None if t is None or t.numel() == 0 else t.data_ptr()
+
+
+def forward(g, cam, antialiasing=False, scale_modifier=1.0):
+    """g: dict of CUDA tensors (means3D, opacities, scales, rotations, shs, sh_degree[, colors_precomp,
+    cov3D_precomp]); cam: dict(bg, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, H, W).
+    Returns (R, color[3,H,W], invdepth[1,H,W], radii[P])."""
+    L = lib()
+    dev = g["means3D"].device
+    P = g["means3D"].shape[0]
+    shs = g.get("shs")
+    M = shs.shape[1] if shs is not None and shs.numel() else 0
+    H, W = cam["H"], cam["W"]
+    color = torch.zeros(3, H, W, device=dev)
+    invd = torch.zeros(1, H, W, device=dev)
+    radii = torch.zeros(P, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    R = L.gsref_forward(P, int(g.get("sh_degree", 0)), M, _p(cam["bg"]), W, H, _p(g["means3D"]), _p(shs),
+                        _p(g.get("colors_precomp")), _p(g["opacities"]), _p(g.get("scales")), scale_modifier,
+                        _p(g.get("rotations")), _p(g.get("cov3D_precomp")), _p(cam["viewmatrix"]),
+                        _p(cam["projmatrix"]), _p(cam["campos"]), cam["tan_fovx"], cam["tan_fovy"], 0,
+                        int(antialiasing), _p(color), _p(invd), _p(radii), 0)
+    if R < 0:
+        raise RuntimeError("gsref_forward: " + L.gsref_last_error().decode())
+    return R, color, invd, radii
+
+
+def state(P, W, H, R, dev="cuda"):
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    out = {"point_list": torch.zeros(max(R, 1), dtype=torch.int32, device=dev)[:R],
+           "ranges": torch.zeros(T, 2, dtype=torch.int32, device=dev),
+           "n_contrib": torch.zeros(H, W, dtype=torch.int32, device=dev),
+           "final_T": torch.zeros(H, W, device=dev), "tiles_touched": torch.zeros(P, dtype=torch.int32, device=dev),
+           "point_offsets": torch.zeros(P, dtype=torch.int32, device=dev), "depths": torch.zeros(P, device=dev),
+           "means2D": torch.zeros(P, 2, device=dev)}
+    rc = lib().gsref_state(_p(out["point_list"]), _p(out["ranges"]), _p(out["n_contrib"]), _p(out["final_T"]),
+                           _p(out["tiles_touched"]), _p(out["point_offsets"]), _p(out["depths"]), _p(out["means2D"]))
+    if rc:
+        raise RuntimeError("gsref_state: " + lib().gsref_last_error().decode())
+    return out
+
+
+def backward(g, cam, radii, dL_dcolor, dL_dinvdepth=None, antialiasing=False, scale_modifier=1.0):
+    """Gradients of the LAST forward call. Returns the dict of rasterize_points.cu:300-399's 8-tuple."""
+    L = lib()
+    dev = g["means3D"].device
+    P = g["means3D"].shape[0]
+    shs = g.get("shs")
+    M = shs.shape[1] if shs is not None and shs.numel() else 0
+    H, W = cam["H"], cam["W"]
+    z = lambda *s: torch.zeros(s, device=dev)
+    o = {"dL_dmeans2D": z(P, 3), "dL_dconic": z(P, 2, 2), "dL_dopacity": z(P, 1), "dL_dcolors": z(P, 3),
+         "dL_dinvdepth": z(P, 1), "dL_dmeans3D": z(P, 3), "dL_dcov3D": z(P, 6), "dL_dsh": z(P, max(M, 1), 3),
+         "dL_dscales": z(P, 3), "dL_drotations": z(P, 4)}
+    dcol = dL_dcolor.contiguous()
+    dinv = dL_dinvdepth.contiguous() if dL_dinvdepth is not None else None
+    torch.cuda.synchronize()
+    rc = L.gsref_backward(P, int(g.get("sh_degree", 0)), M, _p(cam["bg"]), W, H, _p(g["means3D"]), _p(shs),
+                          _p(g.get("colors_precomp")), _p(g["opacities"]), _p(g.get("scales")), scale_modifier,
+                          _p(g.get("rotations")), _p(g.get("cov3D_precomp")), _p(cam["viewmatrix"]),
+                          _p(cam["projmatrix"]), _p(cam["campos"]), cam["tan_fovx"], cam["tan_fovy"], _p(radii),
+                          _p(dcol), _p(dinv), _p(o["dL_dmeans2D"]), _p(o["dL_dconic"]), _p(o["dL_dopacity"]),
+                          _p(o["dL_dcolors"]), _p(o["dL_dinvdepth"]), _p(o["dL_dmeans3D"]), _p(o["dL_dcov3D"]),
+                          _p(o["dL_dsh"]), _p(o["dL_dscales"]), _p(o["dL_drotations"]), int(antialiasing), 0)
+    if rc:
+        raise RuntimeError("gsref_backward: " + L.gsref_last_error().decode())
+    torch.cuda.synchronize()
+    if M == 0:
+        o["dL_dsh"] = z(P, 0, 3)
+    return o
