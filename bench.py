@@ -197,13 +197,9 @@ def main():
     F.evaluate_loss()
     sync_all()
     linearize_ms = (time.perf_counter() - t0) * 1e3
-    R_total = sum(vc.R for vc in F._views)
-    R_reach, pix = 0, 0
-    for vc in F._views:
-        bv = _C.buffer_view(P, vc.W, vc.H, vc.R, vc.geom, vc.binning, vc.img)
-        ln = (bv["ranges"][:, 1] - bv["ranges"][:, 0]).to(torch.int64)
-        R_reach += int(torch.minimum(ln, bv["tile_max_contrib"].to(torch.int64)).sum())
-        pix += vc.W * vc.H
+    R_total = sum(int(vc.R) for vc in F._views)
+    R_cached = sum(vc.R.cached for vc in F._views)     # instances some pixel blended: what every CG iteration sweeps
+    pix = sum(vc.W * vc.H for vc in F._views)
 
     tan = ss.random_tangent(g, seed=2001, mask_xyz=a.mask_xyz)
     v = GaussianModelState.from_gaussians(model)
@@ -270,10 +266,10 @@ def main():
     if os.path.exists(pk):
         peaks = json.load(open(pk))
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    # algorithmic bytes of one k_blend_jtjv launch (DESIGN.md "kernels"): per REACHED instance 48 B primal record
+    # algorithmic bytes of one k_blend_jtjv launch (DESIGN.md "kernels"): per CACHED instance 48 B primal record
     # + 4 B id + 48 B gathered tangent record + 48 B gradient record out; per pixel n_contrib + final_T + 3 weights
     n_local = max(len(F._views), 1)
-    alg_bytes = (R_reach * (48 + 4 + 48 + 48) + pix * (4 + 4 + 12)) / n_local
+    alg_bytes = (R_cached * (48 + 4 + 48 + 48) + pix * (4 + 4 + 12)) / n_local
     dur_s = (jt_ms / max(jt_n, 1)) * 1e-3
     achieved = alg_bytes / dur_s / 1e9 if dur_s > 0 else 0.0
     stage_share = {k: round(ms / a.steps, 4) for k, (ms, c) in stages.items() if c}
@@ -283,7 +279,7 @@ def main():
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": workload_name(a, P, V, W, H), "views_per_rank": len(F._views),
-                   "instances_total_rank0": R_total, "instances_reached_rank0": R_reach,
+                   "instances_total_rank0": R_total, "instances_cached_rank0": R_cached,
                    "l2_policy": "inputs larger than L2 (per-view records + gradients >> 126 MB)",
                    "linearize_ms": round(linearize_ms, 2), "mask_xyz": bool(a.mask_xyz)},
         "e2e": {"value": 1e3 / ms_e2e, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": 4 * n_flat,

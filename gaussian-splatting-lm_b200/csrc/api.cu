@@ -57,12 +57,12 @@ int32_t gslm_abi_version(void) { return 1; }
 
 size_t gslm_geom_bytes(int32_t P) { return carve_geom(nullptr, P).total; }
 size_t gslm_image_bytes(int32_t width, int32_t height) { return carve_image(nullptr, width, height).total; }
-size_t gslm_binning_bytes(int64_t R) { return carve_binning(nullptr, R).total; }
+size_t gslm_binning_bytes(int64_t Rc) { return carve_binning(nullptr, Rc).total; }
 size_t gslm_binning_temp_bytes(int64_t R) { return carve_binning_temp(nullptr, R).total; }
-size_t gslm_backward_scratch_bytes(int64_t R) { return align_up((size_t)R * REC_F4 * sizeof(float4)) + 128; }
+size_t gslm_backward_scratch_bytes(int64_t Rc) { return align_up((size_t)Rc * REC_F4 * sizeof(float4)) + 128; }
 size_t gslm_jvp_scratch_bytes(int32_t P) { return align_up((size_t)P * REC_F4 * sizeof(float4)) + 128; }
-size_t gslm_jtjv_scratch_bytes(int32_t P, int64_t R) {
-    return gslm_jvp_scratch_bytes(P) + gslm_backward_scratch_bytes(R);
+size_t gslm_jtjv_scratch_bytes(int32_t P, int64_t Rc) {
+    return gslm_jvp_scratch_bytes(P) + gslm_backward_scratch_bytes(Rc);
 }
 
 int32_t gslm_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
@@ -73,63 +73,79 @@ int32_t gslm_mark_visible(int32_t P, const float* means3D, const float* viewmatr
 }
 
 int32_t gslm_forward(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn alloc, void* alloc_ctx,
-                     float* out_color, float* out_invdepth, int32_t* radii, int32_t* num_rendered, void* stream) {
+                     float* out_color, float* out_invdepth, int32_t* radii, int32_t* num_rendered,
+                     int32_t* num_cached, void* stream) {
     if (check_inputs(g, cam)) return 1;
-    if (!alloc || !out_color || !num_rendered || (g->P > 0 && !radii)) { set_error("null argument"); return 1; }
+    if (!alloc || !out_color || !num_rendered || !num_cached || (g->P > 0 && !radii)) {
+        set_error("null argument");
+        return 1;
+    }
     cudaStream_t s = (cudaStream_t)stream;
     const int P = g->P, W = cam->width, H = cam->height;
+    const int T = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
     void* gbuf = alloc(alloc_ctx, GSLM_BUF_GEOM, gslm_geom_bytes(P));
     void* ibuf = alloc(alloc_ctx, GSLM_BUF_IMAGE, gslm_image_bytes(W, H));
     if (!gbuf || !ibuf) { set_error("allocator returned null"); return 1; }
     GeomView gv = carve_geom(gbuf, P);
     ImageView iv = carve_image(ibuf, W, H);
-    uint32_t R = 0;
+    uint32_t R = 0, Rc = 0;
     if (P > 0) {
         if (launch_preprocess(*g, *cam, gv, radii, s)) return 1;
         if (debug_sync(cam, s, "preprocess")) return 1;
         if (run_scan(gv, P, s)) return 1;
-        // rasterizer_impl.cu:325 -- the one host synchronisation of the uncached path
+        // rasterizer_impl.cu:325 -- host synchronisation #1 of the uncached path (sizes the sort scratch)
         GSLM_CUDA_OK(cudaMemcpyAsync(&R, gv.point_offsets + (P - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
         GSLM_CUDA_OK(cudaStreamSynchronize(s));
     }
     *num_rendered = (int32_t)R;
-    void* bbuf = alloc(alloc_ctx, GSLM_BUF_BINNING, gslm_binning_bytes(R));
     void* tbuf = alloc(alloc_ctx, GSLM_BUF_BINNING_TEMP, gslm_binning_temp_bytes(R));
-    if (!bbuf || !tbuf) { set_error("allocator returned null"); return 1; }
-    BinningView bv = carve_binning(bbuf, R);
+    if (!tbuf) { set_error("allocator returned null"); return 1; }
     BinningTemp bt = carve_binning_temp(tbuf, R);
-    const float* features = g->colors_precomp ? g->colors_precomp : gv.rgb;
-    if (run_binning(gv, radii, bv, bt, iv, P, W, H, R, features, s)) return 1;
+    if (run_binning(gv, radii, bt, iv, P, W, H, R, s)) return 1;
     if (debug_sync(cam, s, "binning")) return 1;
-    if (launch_blend_fwd(bv, iv, W, H, cam->bg, out_color, out_invdepth, s)) return 1;
-    return debug_sync(cam, s, "render");
+    const float* features = g->colors_precomp ? g->colors_precomp : gv.rgb;
+    if (launch_blend_fwd(gv, bt, iv, W, H, features, cam->bg, out_color, out_invdepth, s)) return 1;
+    if (debug_sync(cam, s, "render")) return 1;
+    if (run_tile_scan(iv, W, H, s)) return 1;
+    // host synchronisation #2: the compact cache is sized by what the forward pass actually blended
+    GSLM_CUDA_OK(cudaMemcpyAsync(&Rc, iv.cstart + T, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    GSLM_CUDA_OK(cudaStreamSynchronize(s));
+    *num_cached = (int32_t)Rc;
+    void* bbuf = alloc(alloc_ctx, GSLM_BUF_BINNING, gslm_binning_bytes(Rc));
+    if (!bbuf) { set_error("allocator returned null"); return 1; }
+    BinningView bv = carve_binning(bbuf, Rc);
+    if (P > 0 && run_compaction(gv, bv, bt, iv, P, W, H, Rc, s)) return 1;
+    return debug_sync(cam, s, "compaction");
 }
 
 int32_t gslm_jvp_cached(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam, const int32_t* radii,
                         const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
-                        int32_t num_rendered, void* scratch, float* out_color_tangent, float* out_invdepth_tangent,
+                        int32_t num_cached, void* scratch, float* out_color_tangent, float* out_invdepth_tangent,
                         void* stream) {
     if (check_inputs(g, cam)) return 1;
-    if (!out_color_tangent || !image_buffer || !binning_buffer || !scratch) { set_error("null argument"); return 1; }
+    if (!out_color_tangent || !image_buffer || !binning_buffer || !geom_buffer || !scratch) {
+        set_error("null argument");
+        return 1;
+    }
     cudaStream_t s = (cudaStream_t)stream;
+    GeomView gv = carve_geom(const_cast<void*>(geom_buffer), g->P);
     ImageView iv = carve_image(const_cast<void*>(image_buffer), cam->width, cam->height);
-    BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_rendered);
+    BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_cached);
     float4* tgeom = reinterpret_cast<float4*>(align_up((size_t)scratch));
     TangentPtrs t = make_tangents(gt, nullptr);
-    if (launch_preprocess_tangent(*g, t, *cam, radii, tgeom, s)) return 1;
+    if (launch_preprocess_tangent(*g, t, *cam, radii, gv.g_off, tgeom, s)) return 1;
     if (launch_blend_jvp(bv, iv, cam->width, cam->height, tgeom, cam->bg, nullptr, out_color_tangent,
                          out_invdepth_tangent, s)) return 1;
-    (void)geom_buffer;
     return debug_sync(cam, s, "jvp_cached");
 }
 
 int32_t gslm_forward_jvp(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam,
                          const GslmCameraTangent* camt, GslmAllocFn alloc, void* alloc_ctx, float* out_color,
                          float* out_invdepth, int32_t* radii, float* out_color_tangent, float* out_invdepth_tangent,
-                         int32_t* num_rendered, void* stream) {
+                         int32_t* num_rendered, int32_t* num_cached, void* stream) {
     // rasterizer_jvp_impl.h:125-325 runs primal and tangent in one pass and then shrinks its
     // buffers to the primal layout; here the primal pass IS the plain forward, followed by the
-    // tangent stages on the state it left behind.
+    // tangent stages on the compact state it left behind.
     struct Capture { GslmAllocFn fn; void* ctx; void* p[4]; } cap = {alloc, alloc_ctx, {nullptr, nullptr, nullptr, nullptr}};
     auto hook = [](void* c, int32_t which, size_t bytes) -> void* {
         Capture* k = (Capture*)c;
@@ -138,12 +154,13 @@ int32_t gslm_forward_jvp(const GslmGaussians* g, const GslmGaussians* gt, const 
         return r;
     };
     if (!out_color_tangent) { set_error("null argument"); return 1; }
-    if (gslm_forward(g, cam, hook, &cap, out_color, out_invdepth, radii, num_rendered, stream)) return 1;
+    if (gslm_forward(g, cam, hook, &cap, out_color, out_invdepth, radii, num_rendered, num_cached, stream)) return 1;
     cudaStream_t s = (cudaStream_t)stream;
     const int P = g->P, W = cam->width, H = cam->height;
+    GeomView gv = carve_geom(cap.p[GSLM_BUF_GEOM], P);
     ImageView iv = carve_image(cap.p[GSLM_BUF_IMAGE], W, H);
-    BinningView bv = carve_binning(cap.p[GSLM_BUF_BINNING], *num_rendered);
-    // the tangent geometry (48 B per Gaussian) borrows the binning TEMP buffer, which is dead once the
+    BinningView bv = carve_binning(cap.p[GSLM_BUF_BINNING], *num_cached);
+    // the tangent geometry (48 B per Gaussian) borrows the sort scratch, which is dead once the
     // forward pass has returned, when it fits; otherwise one more scratch allocation (which = -1)
     float4* tgeom = nullptr;
     const size_t need = gslm_jvp_scratch_bytes(P);
@@ -155,14 +172,14 @@ int32_t gslm_forward_jvp(const GslmGaussians* g, const GslmGaussians* gt, const 
         tgeom = reinterpret_cast<float4*>(align_up((size_t)extra));
     }
     TangentPtrs t = make_tangents(gt, camt);
-    if (launch_preprocess_tangent(*g, t, *cam, radii, tgeom, s)) return 1;
+    if (launch_preprocess_tangent(*g, t, *cam, radii, gv.g_off, tgeom, s)) return 1;
     if (launch_blend_jvp(bv, iv, W, H, tgeom, cam->bg, camt ? camt->bg : nullptr, out_color_tangent,
                          out_invdepth_tangent, s)) return 1;
     return debug_sync(cam, s, "forward_jvp");
 }
 
 int32_t gslm_backward(const GslmGaussians* g, const GslmCamera* cam, const int32_t* radii, const void* geom_buffer,
-                      const void* binning_buffer, const void* image_buffer, int32_t num_rendered,
+                      const void* binning_buffer, const void* image_buffer, int32_t num_cached,
                       const float* dL_dcolor, const float* dL_dinvdepth, void* scratch, GslmGrads* grads,
                       void* stream) {
     if (check_inputs(g, cam)) return 1;
@@ -175,9 +192,9 @@ int32_t gslm_backward(const GslmGaussians* g, const GslmCamera* cam, const int32
     if (P == 0) return 0;
     GeomView gv = carve_geom(const_cast<void*>(geom_buffer), P);
     ImageView iv = carve_image(const_cast<void*>(image_buffer), W, H);
-    BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_rendered);
+    BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_cached);
     float4* inst = reinterpret_cast<float4*>(align_up((size_t)scratch));
-    if (num_rendered > 0)
+    if (num_cached > 0)
         if (launch_blend_bwd(bv, iv, W, H, cam->bg, dL_dcolor, dL_dinvdepth, inst, s)) return 1;
     if (debug_sync(cam, s, "render bwd")) return 1;
     if (launch_preprocess_bwd(*g, *cam, radii, gv, bv, inst, dL_dinvdepth != nullptr, *grads, s)) return 1;
@@ -186,7 +203,7 @@ int32_t gslm_backward(const GslmGaussians* g, const GslmCamera* cam, const int32
 
 int32_t gslm_jtjv(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam, const int32_t* radii,
                   const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
-                  int32_t num_rendered, const float* weight, void* scratch, GslmGrads* grads, float* out_vJJv,
+                  int32_t num_cached, const float* weight, void* scratch, GslmGrads* grads, float* out_vJJv,
                   void* stream) {
     if (check_inputs(g, cam)) return 1;
     if (!grads || !geom_buffer || !binning_buffer || !image_buffer || !scratch) { set_error("null argument"); return 1; }
@@ -195,21 +212,21 @@ int32_t gslm_jtjv(const GslmGaussians* g, const GslmGaussians* gt, const GslmCam
     if (P == 0) return 0;
     GeomView gv = carve_geom(const_cast<void*>(geom_buffer), P);
     ImageView iv = carve_image(const_cast<void*>(image_buffer), W, H);
-    BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_rendered);
+    BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_cached);
     float4* tgeom = reinterpret_cast<float4*>(align_up((size_t)scratch));
     float4* inst = reinterpret_cast<float4*>((char*)tgeom + gslm_jvp_scratch_bytes(P) - 128);
     inst = reinterpret_cast<float4*>(align_up((size_t)inst));
     TangentPtrs t = make_tangents(gt, nullptr);
-    if (launch_preprocess_tangent(*g, t, *cam, radii, tgeom, s)) return 1;
-    if (num_rendered > 0)
+    if (launch_preprocess_tangent(*g, t, *cam, radii, gv.g_off, tgeom, s)) return 1;
+    if (num_cached > 0)
         if (launch_blend_jtjv(bv, iv, W, H, cam->bg, tgeom, weight, inst, out_vJJv, s)) return 1;
     if (launch_preprocess_bwd(*g, *cam, radii, gv, bv, inst, false, *grads, s)) return 1;
     return debug_sync(cam, s, "jtjv");
 }
 
-int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_rendered, const void* geom_buffer,
-                         const void* binning_buffer, const void* image_buffer, const void* binning_temp_buffer,
-                         GslmBufferView* out) {
+int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_rendered, int64_t num_cached,
+                         const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
+                         const void* binning_temp_buffer, GslmBufferView* out) {
     if (!out) { set_error("null argument"); return 1; }
     memset(out, 0, sizeof(*out));
     if (geom_buffer) {
@@ -217,17 +234,20 @@ int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_r
         out->tiles_touched = gv.tiles_touched; out->point_offsets = gv.point_offsets; out->depths = gv.depths;
         out->means2D = reinterpret_cast<const float*>(gv.means2D);
         out->conic_opacity = reinterpret_cast<const float*>(gv.conic_opacity);
-        out->rgb = gv.rgb; out->cov3D = gv.cov3D; out->clamped = gv.clamped;
+        out->rgb = gv.rgb; out->cov3D = gv.cov3D; out->clamped = gv.clamped; out->g_off = gv.g_off;
     }
     if (binning_buffer) {
-        BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_rendered);
-        out->point_list = bv.point_list;
+        BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_cached);
+        out->records = reinterpret_cast<const float*>(bv.records); out->cid = bv.cid; out->g_list = bv.g_list;
     }
-    if (binning_temp_buffer) out->keys_sorted = carve_binning_temp(const_cast<void*>(binning_temp_buffer), num_rendered).keys_sorted;
+    if (binning_temp_buffer) {
+        BinningTemp bt = carve_binning_temp(const_cast<void*>(binning_temp_buffer), num_rendered);
+        out->keys_sorted = bt.keys_sorted; out->point_list = bt.point_list;
+    }
     if (image_buffer) {
         ImageView iv = carve_image(const_cast<void*>(image_buffer), width, height);
         out->ranges = reinterpret_cast<const uint32_t*>(iv.ranges); out->n_contrib = iv.n_contrib; out->final_T = iv.final_T;
-        out->tile_max_contrib = iv.tile_max_contrib;
+        out->n_contrib_c = iv.n_contrib_c; out->cstart = iv.cstart;
     }
     return 0;
 }

@@ -1,7 +1,8 @@
 // =============================================================================
 // binning.cu -- tile binning (a8): scan, key generation, tile|depth radix sort, tile
-// ranges; plus the record gather that turns the sorted id list into contiguous 48-byte
-// instance records (what the tile kernels stage with one bulk copy per batch).
+// ranges; plus the compaction that turns the instances the forward pass actually blended
+// into dense 48-byte records in tile|depth order (what the derivative tile kernels stage with
+// one bulk copy per batch) and a per-Gaussian CSR over them (deterministic gradient gather).
 //
 // Reference: DGR/cuda_rasterizer/rasterizer_impl.cu:35-50 (getHigherMsb), :70-111
 // (duplicateWithKeys), :116-138 (identifyTileRanges), :321-364 (orchestration).
@@ -71,6 +72,8 @@ GeomView carve_geom(void* base, int P) {
     v.tiles_touched = take<uint32_t>(p, n);
     v.point_offsets = take<uint32_t>(p, n);
     v.num_rendered = take<uint32_t>(p, 32);
+    v.g_off = take<uint32_t>(p, n + 1);
+    v.g_cursor = take<uint32_t>(p, n);
     v.scan_temp_bytes = scan_temp_bytes(P);
     v.scan_temp = take<char>(p, v.scan_temp_bytes);
     v.total = (size_t)(p - reinterpret_cast<char*>(base));
@@ -82,18 +85,20 @@ ImageView carve_image(void* base, int W, int H) {
     size_t N = (size_t)W * H, T = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
     v.final_T = take<float>(p, N);
     v.n_contrib = take<uint32_t>(p, N);
+    v.n_contrib_c = take<uint32_t>(p, N);
     v.ranges = take<uint2>(p, T);
-    v.tile_max_contrib = take<uint32_t>(p, T);
+    v.ccount = take<uint32_t>(p, T);
+    v.cstart = take<uint32_t>(p, T + 1);
     v.total = (size_t)(p - reinterpret_cast<char*>(base));
     return v;
 }
-BinningView carve_binning(void* base, int64_t R) {
+BinningView carve_binning(void* base, int64_t Rc) {
     BinningView v;
     char* p = reinterpret_cast<char*>(base);
-    size_t n = (size_t)R;
+    size_t n = (size_t)Rc;
     v.records = take<float4>(p, REC_F4 * n);
-    v.point_list = take<uint32_t>(p, n);
-    v.inv_perm = take<uint32_t>(p, n);
+    v.cid = take<uint32_t>(p, n);
+    v.g_list = take<uint32_t>(p, n);
     v.total = (size_t)(p - reinterpret_cast<char*>(base));
     return v;
 }
@@ -104,6 +109,8 @@ BinningTemp carve_binning_temp(void* base, int64_t R) {
     v.keys_sorted = take<uint64_t>(p, n);
     v.keys_unsorted = take<uint64_t>(p, n);
     v.vals_unsorted = take<uint32_t>(p, n);
+    v.point_list = take<uint32_t>(p, n);
+    v.records_tmp = take<float4>(p, REC_F4 * n);
     v.sort_temp_bytes = sort_temp_bytes(R);
     v.sort_temp = take<char>(p, v.sort_temp_bytes);
     v.total = (size_t)(p - reinterpret_cast<char*>(base));
@@ -166,38 +173,8 @@ k_tile_ranges(uint32_t L, const uint64_t* __restrict__ keys, uint2* __restrict__
     if (idx == L - 1) ranges[cur].y = L;
 }
 
-// Gather: sorted position k -> 48-byte instance record, and the inverse permutation
-// (Gaussian-major slot -> k) used by the deterministic gradient gather.
-// slot = offsets[id-1] + (ty - rect.y0) * rect_w + (tx - rect.x0): the position at which
-// k_duplicate_keys emitted this (tile, Gaussian) pair.
-__global__ void __launch_bounds__(256)
-k_gather_records(uint32_t L, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ point_list,
-                 const float2* __restrict__ xy, const float4* __restrict__ conic_opacity,
-                 const float* __restrict__ features, const float* __restrict__ depths,
-                 const uint32_t* __restrict__ offsets, const int32_t* __restrict__ radii, int gx, int gy,
-                 float4* __restrict__ records, uint32_t* __restrict__ inv_perm) {
-    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= L) return;
-    uint32_t id = point_list[k];
-    uint32_t tile = (uint32_t)(keys[k] >> 32);
-    float2 p = __ldg(xy + id);
-    float4 co = __ldg(conic_opacity + id);
-    float r = __ldg(features + 3 * (size_t)id), g = __ldg(features + 3 * (size_t)id + 1),
-          b = __ldg(features + 3 * (size_t)id + 2);
-    float invz = 1.f / __ldg(depths + id);   // forward.cu:380: (1 / depths[id])
-    float4* rec = records + (size_t)REC_F4 * k;
-    rec[0] = make_float4(p.x, p.y, co.x, co.y);
-    rec[1] = make_float4(co.z, co.w, r, g);
-    rec[2] = make_float4(b, invz, __uint_as_float(id), 0.f);
-    int x0, y0, x1, y1;
-    tile_rect(p.x, p.y, __ldg(radii + id), gx, gy, x0, y0, x1, y1);
-    int tx = (int)(tile % (uint32_t)gx), ty = (int)(tile / (uint32_t)gx);
-    uint32_t base = id == 0 ? 0u : __ldg(offsets + id - 1);
-    inv_perm[base + (uint32_t)((ty - y0) * (x1 - x0) + (tx - x0))] = k;
-}
-
-int run_binning(const GeomView& gv, const int32_t* radii, const BinningView& bv, const BinningTemp& bt,
-                const ImageView& iv, int P, int W, int H, int64_t R, const float* features, cudaStream_t s) {
+int run_binning(const GeomView& gv, const int32_t* radii, const BinningTemp& bt, const ImageView& iv, int P, int W,
+                int H, int64_t R, cudaStream_t s) {
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     GSLM_CUDA_OK(cudaMemsetAsync(iv.ranges, 0, sizeof(uint2) * (size_t)gx * gy, s));
     if (R == 0 || P == 0) return 0;
@@ -209,7 +186,7 @@ int run_binning(const GeomView& gv, const int32_t* radii, const BinningView& bv,
     const int bit = (int)higher_msb((uint32_t)(gx * gy));
     size_t need = 0;
     GSLM_CUDA_OK(cub::DeviceRadixSort::SortPairs(nullptr, need, bt.keys_unsorted, bt.keys_sorted, bt.vals_unsorted,
-                                                 bv.point_list, (int)R, 0, 32 + bit, s));
+                                                 bt.point_list, (int)R, 0, 32 + bit, s));
     if (need > bt.sort_temp_bytes) {
         set_error("sort temp storage too small: need %zu have %zu", need, bt.sort_temp_bytes);
         return 1;
@@ -217,18 +194,123 @@ int run_binning(const GeomView& gv, const int32_t* radii, const BinningView& bv,
     size_t have = bt.sort_temp_bytes;
     stage_begin(ST_SORT, s);
     GSLM_CUDA_OK(cub::DeviceRadixSort::SortPairs(bt.sort_temp, have, bt.keys_unsorted, bt.keys_sorted,
-                                                 bt.vals_unsorted, bv.point_list, (int)R, 0, 32 + bit, s));
+                                                 bt.vals_unsorted, bt.point_list, (int)R, 0, 32 + bit, s));
     stage_end(ST_SORT, s);
     const uint32_t L = (uint32_t)R;
-    stage_begin(ST_RANGES, s);
+    StageScope ts(ST_RANGES, s);
     k_tile_ranges<<<(L + 255) / 256, 256, 0, s>>>(L, bt.keys_sorted, iv.ranges);
-    stage_end(ST_RANGES, s);
     GSLM_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// compaction (no reference counterpart): dense compact arrays + per-Gaussian CSR
+// ---------------------------------------------------------------------------------------------
+// exclusive scan of the per-tile compact counts; one CTA (T is a few thousand)
+__global__ void __launch_bounds__(1024) k_scan_tiles(int T, const uint32_t* __restrict__ ccount, uint32_t* __restrict__ cstart) {
+    __shared__ uint32_t s_w[32];
+    __shared__ uint32_t s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < T; base += 1024) {
+        const int i = base + tid;
+        const uint32_t v = i < T ? ccount[i] : 0u;
+        uint32_t x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) s_w[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t w = s_w[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                uint32_t y = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += y;
+            }
+            s_w[lane] = w;
+        }
+        __syncthreads();
+        const uint32_t carry = s_carry;
+        const uint32_t incl = x + (warp ? s_w[warp - 1] : 0u) + carry;
+        if (i < T) cstart[i] = incl - v;
+        __syncthreads();
+        if (tid == 1023) s_carry = incl;
+        __syncthreads();
+    }
+    if (tid == 0) cstart[T] = s_carry;
+}
+
+int run_tile_scan(const ImageView& iv, int W, int H, cudaStream_t s) {
+    const int T = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+    k_scan_tiles<<<1, 1024, 0, s>>>(T, iv.ccount, iv.cstart);
+    GSLM_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+// one CTA per tile: tile-local compact records -> dense positions; ids; per-Gaussian counts
+__global__ void __launch_bounds__(256)
+k_compact_copy(const uint2* __restrict__ ranges, const uint32_t* __restrict__ cstart,
+               const uint32_t* __restrict__ ccount, const float4* __restrict__ src, float4* __restrict__ dst,
+               uint32_t* __restrict__ cid, uint32_t* __restrict__ g_cnt) {
+    const int tile = blockIdx.x;
+    const uint32_t n = ccount[tile];
+    if (n == 0) return;
+    const size_t s0 = (size_t)ranges[tile].x * REC_F4, d0 = (size_t)cstart[tile] * REC_F4;
+    for (uint32_t i = threadIdx.x; i < n * REC_F4; i += blockDim.x) {
+        const float4 q = src[s0 + i];
+        dst[d0 + i] = q;
+        if (i % REC_F4 == 2) {
+            const uint32_t id = __float_as_uint(q.z);
+            cid[cstart[tile] + i / REC_F4] = id;
+            atomicAdd(&g_cnt[id], 1u);
+        }
+    }
+}
+__global__ void __launch_bounds__(256)
+k_fill_glist(uint32_t Rc, const uint32_t* __restrict__ cid, uint32_t* __restrict__ g_cursor, uint32_t* __restrict__ g_list) {
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= Rc) return;
+    g_list[atomicAdd(&g_cursor[cid[c]], 1u)] = c;
+}
+// atomics hand out slots in arbitrary order: sort every Gaussian's (short) list so that the
+// gradient gather always sums in the same order => deterministic gradients
+__global__ void __launch_bounds__(256)
+k_sort_glist(int P, const uint32_t* __restrict__ g_off, uint32_t* __restrict__ g_list) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const uint32_t b = g_off[i], e = g_off[i + 1];
+    for (uint32_t k = b + 1; k < e; k++) {
+        const uint32_t x = g_list[k];
+        uint32_t j = k;
+        while (j > b && g_list[j - 1] > x) { g_list[j] = g_list[j - 1]; j--; }
+        g_list[j] = x;
+    }
+}
+
+int run_compaction(const GeomView& gv, const BinningView& bv, const BinningTemp& bt, const ImageView& iv, int P,
+                   int W, int H, int64_t Rc, cudaStream_t s) {
+    const int T = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
     StageScope ts(ST_GATHER, s);
-    k_gather_records<<<(L + 255) / 256, 256, 0, s>>>(L, bt.keys_sorted, bv.point_list, gv.means2D, gv.conic_opacity,
-                                                     features, gv.depths, gv.point_offsets, radii, gx, gy, bv.records,
-                                                     bv.inv_perm);
-    GSLM_CUDA_OK(cudaGetLastError());
+    GSLM_CUDA_OK(cudaMemsetAsync(gv.g_cursor, 0, sizeof(uint32_t) * (size_t)P, s));
+    GSLM_CUDA_OK(cudaMemsetAsync(gv.g_off, 0, sizeof(uint32_t), s));
+    if (Rc > 0) {
+        k_compact_copy<<<T, 256, 0, s>>>(iv.ranges, iv.cstart, iv.ccount, bt.records_tmp, bv.records, bv.cid, gv.g_cursor);
+        GSLM_CUDA_OK(cudaGetLastError());
+    }
+    // g_off[1..P] = inclusive scan of the counts (the forward pass's scan scratch is free again)
+    size_t have = gv.scan_temp_bytes;
+    GSLM_CUDA_OK(cub::DeviceScan::InclusiveSum(gv.scan_temp, have, gv.g_cursor, gv.g_off + 1, P, s));
+    if (Rc > 0) {
+        GSLM_CUDA_OK(cudaMemcpyAsync(gv.g_cursor, gv.g_off, sizeof(uint32_t) * (size_t)P, cudaMemcpyDeviceToDevice, s));
+        k_fill_glist<<<(unsigned)((Rc + 255) / 256), 256, 0, s>>>((uint32_t)Rc, bv.cid, gv.g_cursor, bv.g_list);
+        GSLM_CUDA_OK(cudaGetLastError());
+        k_sort_glist<<<(P + 255) / 256, 256, 0, s>>>(P, gv.g_off, bv.g_list);
+        GSLM_CUDA_OK(cudaGetLastError());
+    }
     return 0;
 }
 

@@ -1,15 +1,16 @@
 // =============================================================================
 // blend_common.cuh -- building blocks of the tile kernels (a9, a11, a13, fused J^T J v).
 //
-// One CTA = one 16x16 tile, one thread = one pixel (as DGR/cuda_rasterizer/forward.cu:278-402).
+// One CTA = one 16x16 tile (as DGR/cuda_rasterizer/forward.cu:278-402); the primal kernel maps one thread to one
+// pixel, the derivative kernels one thread to a vertical pair of pixels (128 threads per tile).
 // What is different from the reference:
 //  * a tile's instances are contiguous 48-byte records (binning.cu), staged 256 at a time
 //    by ONE cp.async.bulk (TMA bulk copy, SASS UBLKCP) per batch into a 2-stage shared-memory
 //    ring guarded by mbarriers -- no per-thread gathers, colour / depth never fetched from
 //    global per hit (forward.cu:377,380);
-//  * alpha is evaluated by ONE rounding-exact instruction sequence (eval_alpha) shared by
-//    the primal, tangent and adjoint sweeps, so all three agree on every hit / skip
-//    decision whatever the surrounding code's FMA contraction;
+//  * alpha is evaluated by ONE rounding-exact instruction sequence (alpha_column / alpha_pixel)
+//    shared by the primal, tangent and adjoint sweeps, so all three agree on every hit / skip
+//    decision whatever the surrounding code's FMA contraction or pixel-to-thread mapping;
 //  * the adjoint sweep pre-reduces its ten partials with a 12-shuffle recursive-halving
 //    warp reduction, merges warps in shared memory and writes ONE record per
 //    (tile, Gaussian) instance -- no global atomics (the reference does ten atomicAdd per
@@ -62,21 +63,23 @@ template <int N> __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
+constexpr int DBATCH = 128;   // instances per staged batch in the derivative kernels (6 KB of records)
+
 // Two-stage ring of record batches for one tile. All threads keep an identical copy of the
 // phase bits; thread 0 issues.
 struct RecordRing {
-    float4* buf;       // [2][BATCH * REC_F4]
+    float4* buf;       // [2][DBATCH * REC_F4]
     uint64_t* bar;     // [2]
     const float4* src; // records of this tile (global)
     int total;         // instances in the tile's range
     uint32_t phase;    // bit s = parity of the next completion of stage s
 
-    __device__ __forceinline__ float4* stage(int s) const { return buf + s * (BATCH * REC_F4); }
-    __device__ __forceinline__ int batch_size(int b) const { return min(BATCH, total - b * BATCH); }
+    __device__ __forceinline__ float4* stage(int s) const { return buf + s * (DBATCH * REC_F4); }
+    __device__ __forceinline__ int batch_size(int b) const { return min(DBATCH, total - b * DBATCH); }
     __device__ __forceinline__ void issue(int b, int s) const {   // one thread
         uint32_t bytes = (uint32_t)batch_size(b) * (REC_F4 * 16);
         mbar_arrive_expect_tx(&bar[s], bytes);
-        bulk_g2s(stage(s), src + (size_t)b * BATCH * REC_F4, bytes, &bar[s]);
+        bulk_g2s(stage(s), src + (size_t)b * DBATCH * REC_F4, bytes, &bar[s]);
     }
     __device__ __forceinline__ void wait(int s) {
         mbar_wait(&bar[s], (phase >> s) & 1u);
@@ -90,21 +93,34 @@ __device__ __forceinline__ float ex2_approx(float x) {
     return y;
 }
 
-// forward.cu:354-369 / backward.cu:561-569: power, G = exp(power), alpha = min(0.99, o G) and the
-// two skip tests. Explicitly rounded so that every sweep reproduces the same bits.
-// q0 = (x, y, conic.x, conic.y), q1 = (conic.z, opacity, ., .)
-__device__ __forceinline__ bool eval_alpha(const float4& q0, const float4& q1, float pxf, float pyf, float& dx,
-                                           float& dy, float& G, float& alpha) {
+// forward.cu:354-369 / backward.cu:561-569: power, G = exp(power), alpha = min(0.99, o G) and the two
+// skip tests, q0 = (x, y, conic.x, conic.y), q1 = (conic.z, opacity, ., .).
+// The image is a DISCONTINUOUS function of alpha at the 1/255 and T < 1e-4 thresholds, so the roundings follow
+// the reference's own instruction sequence (nvcc's contraction of forward.cu:358:
+// power = fma(-0.5, fma(C dy, dy, (A dx) dx), -((B dx) dy)), exp = ex2(power log2e)); a cheaper reassociation flips
+// enough threshold decisions to move isolated pixels by 1e-3.  It is split in a part shared by the pixels of one
+// image column (alpha_column: dx, e = (A dx) dx, f = B dx) and a per-pixel part (alpha_pixel), and every
+// operation is explicitly rounded so that the primal, tangent and adjoint sweeps -- whatever their
+// pixel-to-thread mapping -- reproduce the same bits and therefore the same hit / skip decisions.
+__device__ __forceinline__ void alpha_column(const float4& q0, float pxf, float& dx, float& e, float& f) {
     dx = __fsub_rn(q0.x, pxf);
+    e = __fmul_rn(__fmul_rn(q0.z, dx), dx);
+    f = __fmul_rn(q0.w, dx);
+}
+__device__ __forceinline__ bool alpha_pixel(const float4& q0, const float4& q1, float e, float f, float pyf, float& dy,
+                                            float& G, float& alpha) {
     dy = __fsub_rn(q0.y, pyf);
-    float t = __fmul_rn(__fmul_rn(q0.z, dx), dx);
-    t = __fmaf_rn(__fmul_rn(q1.x, dy), dy, t);
-    const float v = __fmul_rn(__fmul_rn(q0.w, dx), dy);
-    const float power = __fmaf_rn(-0.5f, t, -v);
+    const float t = __fmaf_rn(__fmul_rn(q1.x, dy), dy, e);
+    const float power = __fmaf_rn(-0.5f, t, -__fmul_rn(f, dy));
     if (power > 0.0f) return false;
     G = ex2_approx(__fmul_rn(power, 1.4426950408889634f));
     alpha = fminf(0.99f, __fmul_rn(q1.y, G));
     return alpha >= (1.0f / 255.0f);
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
 }
 
 // Recursive-halving reduction of 10 values over a warp: 12 SHFL instead of 50.

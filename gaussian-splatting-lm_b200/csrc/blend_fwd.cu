@@ -1,108 +1,169 @@
 // =============================================================================
-// blend_fwd.cu -- primal tile sweep (a9): front-to-back alpha blending.
+// blend_fwd.cu -- primal tile sweep (a9): front-to-back alpha blending, plus the flagging that
+// builds the compact linearisation cache.
 // Reference: DGR/cuda_rasterizer/forward.cu:278-402 (renderCUDA).
 //   C = sum c_i a_i T_i + T bg,  D = sum a_i T_i / z_i,  a_i = min(0.99, o_i exp(power_i));
 //   skip if power > 0 or a < 1/255; a pixel stops when T (1 - a) < 1e-4 (that Gaussian is
 //   not blended); the CTA stops when all 256 pixels have stopped.
-// Writes final_T, n_contrib (ImageState, rasterizer.h) and the per-tile maximum of
-// n_contrib, which bounds the tangent / adjoint sweeps of the cached CG path.
+// Like the reference, each thread fetches one Gaussian of the current batch through the
+// sorted id list (forward.cu:337-345) -- but it fetches colour and depth too, so the inner
+// loop never touches global memory (the reference reads them per hit, :377,380), and the
+// loads of batch b+1 are in flight while batch b is blended.  The early exit means only
+// ~10 % of the sorted list is ever fetched, which is why the records are NOT pre-gathered.
+//
+// New: every instance that at least one pixel blended is flagged; per batch the flagged
+// records are written, densely and in order, to the tile's slice of a scratch array, and
+// every pixel's n_contrib is also kept in that compact numbering.  binning.cu turns the
+// slices into the dense compact cache that all derivative kernels run on.
+// Writes final_T, n_contrib (ImageState, rasterizer.h), n_contrib_c, ccount.
 // =============================================================================
 #include "blend_common.cuh"
 
 namespace gslm {
 
-__global__ void __launch_bounds__(TILE_PIX)
-k_blend_fwd(const uint2* __restrict__ ranges, const float4* __restrict__ records, int W, int H,
-            const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
-            uint32_t* __restrict__ tile_max_contrib, float* __restrict__ out_color, float* __restrict__ out_invdepth) {
-    __shared__ __align__(128) float4 s_rec[2 * BATCH * REC_F4];
-    __shared__ __align__(8) uint64_t s_bar[2];
-    __shared__ uint32_t s_max;
+struct FwdArgs {
+    const uint2* ranges;
+    const uint32_t* point_list;
+    const float2* xy;
+    const float4* conic_opacity;
+    const float* features;
+    const float* depths;
+    int W, H;
+    const float* bg;
+    float* final_T;
+    uint32_t* n_contrib;
+    uint32_t* n_contrib_c;
+    uint32_t* ccount;
+    float4* records_tmp;
+    float* out_color;
+    float* out_invdepth;
+};
 
-    const int tid = threadIdx.x;
-    const int gx = (W + TILE_X - 1) / TILE_X;
+__global__ void __launch_bounds__(TILE_PIX) k_blend_fwd(FwdArgs a) {
+    __shared__ __align__(16) float4 s_rec[2][BATCH * REC_F4];
+    __shared__ uint32_t s_flag[BATCH];
+    __shared__ uint32_t s_pref[BATCH];     // exclusive prefix of s_flag inside each warp's 32-instance group
+    __shared__ uint32_t s_wsum[TILE_PIX / 32];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int gx = (a.W + TILE_X - 1) / TILE_X;
     const int tile = blockIdx.x;
     const int px = (tile % gx) * TILE_X + (tid & (TILE_X - 1));
     const int py = (tile / gx) * TILE_Y + (tid >> 4);
-    const bool inside = px < W && py < H;
+    const bool inside = px < a.W && py < a.H;
     const float pxf = (float)px, pyf = (float)py;
-    const uint2 range = ranges[tile];
+    const uint2 range = a.ranges[tile];
+    const int total = (int)(range.y - range.x);
+    const int rounds = (total + BATCH - 1) / BATCH;
 
-    RecordRing ring;
-    ring.buf = s_rec; ring.bar = s_bar; ring.src = records + (size_t)range.x * REC_F4;
-    ring.total = (int)(range.y - range.x); ring.phase = 0;
-    const int rounds = (ring.total + BATCH - 1) / BATCH;
-
-    if (tid == 0) {
-        mbar_init(&s_bar[0], 1);
-        mbar_init(&s_bar[1], 1);
-        mbar_fence_init();
-        s_max = 0;
-    }
-    __syncthreads();
-    if (tid == 0 && rounds > 0) ring.issue(0, 0);
+    float4 r0, r1, r2;
+    bool have = false;
+    auto fetch = [&](int b) {
+        const int k = b * BATCH + tid;
+        have = k < total;
+        if (have) {
+            const uint32_t id = __ldg(a.point_list + range.x + k);
+            const float2 p = __ldg(a.xy + id);
+            const float4 co = __ldg(a.conic_opacity + id);
+            const float* f = a.features + 3 * (size_t)id;
+            r0 = make_float4(p.x, p.y, co.x, co.y);
+            r1 = make_float4(co.z, co.w, __ldg(f), __ldg(f + 1));
+            r2 = make_float4(__ldg(f + 2), 1.f / __ldg(a.depths + id), __uint_as_float(id), 0.f);   // forward.cu:380
+        }
+    };
+    if (rounds > 0) fetch(0);
 
     bool done = !inside;
     float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
-    uint32_t contributor = 0, last_contributor = 0;
+    uint32_t last_contributor = 0, last_c = 0;
+    uint32_t run = 0;   // compact instances of this tile so far (uniform over the CTA)
 
-    int b = 0;
-    bool pending = rounds > 0;   // batch b has been issued and not yet waited for
-    for (; b < rounds; b++) {
-        // also the barrier that frees stage (b+1)&1: everybody has finished batch b-1
-        const int num_done = __syncthreads_count(done);
-        if (num_done == TILE_PIX) break;
-        if (tid == 0 && b + 1 < rounds) ring.issue(b + 1, (b + 1) & 1);
-        ring.wait(b & 1);
-        const float4* rec = ring.stage(b & 1);
-        const int n = ring.batch_size(b);
-        for (int j = 0; !done && j < n; j++) {
-            contributor++;
-            const float4 q0 = rec[REC_F4 * j], q1 = rec[REC_F4 * j + 1];
-            float dx, dy, G, alpha;
-            if (!eval_alpha(q0, q1, pxf, pyf, dx, dy, G, alpha)) continue;
-            const float test_T = T * (1.f - alpha);
-            if (test_T < 0.0001f) {
-                done = true;
-                continue;
-            }
-            const float4 q2 = rec[REC_F4 * j + 2];
-            const float w = alpha * T;
-            C0 += q1.z * w;
-            C1 += q1.w * w;
-            C2 += q2.x * w;
-            D += q2.y * w;
-            T = test_T;
-            last_contributor = contributor;
+    for (int b = 0; b < rounds; b++) {
+        // barrier: batch b-1 fully consumed (records, flags, prefixes); also the all-done vote
+        if (__syncthreads_count(done) == TILE_PIX) break;
+        float4* rec = s_rec[b & 1];
+        if (have) {
+            rec[REC_F4 * tid] = r0;
+            rec[REC_F4 * tid + 1] = r1;
+            rec[REC_F4 * tid + 2] = r2;
         }
-        pending = false;
-        if (b + 1 < rounds) pending = true;
+        s_flag[tid] = 0;
+        if (b + 1 < rounds) fetch(b + 1);   // in flight during the blend loop below
+        __syncthreads();
+        const int n = min(BATCH, total - b * BATCH);
+        int last_j = -1;
+        for (int j = 0; j < n; j++) {
+            if ((j & 7) == 0 && __all_sync(0xffffffffu, done)) break;
+            bool blended = false;
+            if (!done) {
+                const float4 q0 = rec[REC_F4 * j], q1 = rec[REC_F4 * j + 1];
+                float dx, e, ff, dy, G, alpha;
+                alpha_column(q0, pxf, dx, e, ff);
+                if (alpha_pixel(q0, q1, e, ff, pyf, dy, G, alpha)) {
+                    const float test_T = T * (1.f - alpha);
+                    if (test_T < 0.0001f) {
+                        done = true;
+                    } else {
+                        const float4 q2 = rec[REC_F4 * j + 2];
+                        const float w = alpha * T;
+                        C0 += q1.z * w;
+                        C1 += q1.w * w;
+                        C2 += q2.x * w;
+                        D += q2.y * w;
+                        T = test_T;
+                        last_contributor = (uint32_t)(b * BATCH + j + 1);
+                        last_j = j;
+                        blended = true;
+                    }
+                }
+            }
+            if (__any_sync(0xffffffffu, blended) && lane == 0) s_flag[j] = 1;   // benign race: every writer stores 1
+        }
+        __syncthreads();
+        // block-wide exclusive prefix over the 256 flags
+        const uint32_t f = s_flag[tid];
+        const uint32_t bal = __ballot_sync(0xffffffffu, f != 0);
+        s_pref[tid] = __popc(bal & ((1u << lane) - 1u));
+        if (lane == 0) s_wsum[warp] = __popc(bal);
+        __syncthreads();
+        uint32_t woff[TILE_PIX / 32 + 1];
+        woff[0] = 0;
+#pragma unroll
+        for (int w = 0; w < TILE_PIX / 32; w++) woff[w + 1] = woff[w] + s_wsum[w];
+        if (f) {
+            float4* dst = a.records_tmp + ((size_t)range.x + run + woff[warp] + s_pref[tid]) * REC_F4;
+            dst[0] = rec[REC_F4 * tid];
+            dst[1] = rec[REC_F4 * tid + 1];
+            dst[2] = rec[REC_F4 * tid + 2];
+        }
+        if (last_j >= 0) last_c = run + woff[last_j >> 5] + s_pref[last_j] + 1;   // the pixel's own last hit is flagged
+        run += woff[TILE_PIX / 32];
     }
-    // never leave the CTA with a bulk copy still in flight into its shared memory
-    if (b < rounds && pending) ring.wait(b & 1);
 
     if (inside) {
-        const size_t pix = (size_t)py * W + px, HW = (size_t)H * W;
-        final_T[pix] = T;
-        n_contrib[pix] = last_contributor;
-        out_color[pix] = C0 + T * bg[0];
-        out_color[HW + pix] = C1 + T * bg[1];
-        out_color[2 * HW + pix] = C2 + T * bg[2];
-        if (out_invdepth) out_invdepth[pix] = D;
+        const size_t pix = (size_t)py * a.W + px, HW = (size_t)a.H * a.W;
+        a.final_T[pix] = T;
+        a.n_contrib[pix] = last_contributor;
+        a.n_contrib_c[pix] = last_c;
+        a.out_color[pix] = C0 + T * a.bg[0];
+        a.out_color[HW + pix] = C1 + T * a.bg[1];
+        a.out_color[2 * HW + pix] = C2 + T * a.bg[2];
+        if (a.out_invdepth) a.out_invdepth[pix] = D;
     }
-    const uint32_t wmax = __reduce_max_sync(0xffffffffu, inside ? last_contributor : 0u);
-    if ((tid & 31) == 0) atomicMax(&s_max, wmax);
-    __syncthreads();
-    if (tid == 0) tile_max_contrib[tile] = s_max;
+    if (tid == 0) a.ccount[tile] = run;
 }
 
-int launch_blend_fwd(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg, float* out_color,
-                     float* out_invdepth, cudaStream_t s) {
+int launch_blend_fwd(const GeomView& gv, const BinningTemp& bt, const ImageView& iv, int W, int H,
+                     const float* features, const float* bg, float* out_color, float* out_invdepth, cudaStream_t s) {
     const int tiles = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
     if (tiles == 0) return 0;
+    FwdArgs a;
+    a.ranges = iv.ranges; a.point_list = bt.point_list; a.xy = gv.means2D; a.conic_opacity = gv.conic_opacity;
+    a.features = features; a.depths = gv.depths; a.W = W; a.H = H; a.bg = bg; a.final_T = iv.final_T;
+    a.n_contrib = iv.n_contrib; a.n_contrib_c = iv.n_contrib_c; a.ccount = iv.ccount; a.records_tmp = bt.records_tmp;
+    a.out_color = out_color; a.out_invdepth = out_invdepth;
     StageScope ts(ST_BLEND_FWD, s);
-    k_blend_fwd<<<tiles, TILE_PIX, 0, s>>>(iv.ranges, bv.records, W, H, bg, iv.final_T, iv.n_contrib,
-                                          iv.tile_max_contrib, out_color, out_invdepth);
+    k_blend_fwd<<<tiles, TILE_PIX, 0, s>>>(a);
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
 }

@@ -18,11 +18,19 @@ constexpr int TILE_PIX = TILE_X * TILE_Y;        // 256 threads per tile CTA, on
 constexpr int BATCH = 256;                       // instances staged in shared memory per round
 constexpr int REC_F4 = 3;                        // one instance record = 3 x float4 = 48 bytes
 
-// Instance record (one per (tile, Gaussian) pair, stored in sorted order so that a
+// Instance record (one per (tile, Gaussian) pair, stored in tile|depth order so that a
 // tile's batch is ONE contiguous 12 KB block that a single cp.async.bulk can stage):
-//   q0 = (x, y, conic.x, conic.y)   q1 = (conic.z, opacity, r, g)   q2 = (b, 1/depth, id bits, 0)
-// The per-Gaussian tangent record and the per-instance gradient record use the same
-// slot order: (xy | conic xyz | opacity | rgb | invdepth).
+//   q0 = (x, y, conic.x, conic.y)   q1 = (conic.z, opacity, r, g)   q2 = (b, 1/depth, id bits, 0).
+// The per-instance gradient record is (dmean2D.xy | dconic xx,xy,yy | dopacity | drgb |
+// dinvdepth); the per-Gaussian tangent record holds the coefficients of the power tangent as a polynomial in
+// (dx, dy): (a1, a2, a3, a4 | a5, opacity_t, r_t, g_t | b_t, invdepth_t, 0, 0), see preprocess.cu.
+//
+// COMPACT CACHE.  Only instances that at least one pixel of their tile actually BLENDED survive
+// the forward pass (k_blend_fwd flags them): instances behind the point where every pixel of
+// the tile has terminated, and instances of the 3-sigma bounding square that no pixel sees with
+// alpha >= 1/255, carry exactly zero tangent / gradient and are dropped.  "Rc" = number of
+// compact instances of a view (about 5 % of R at 1M Gaussians / 1080p); every derivative
+// kernel works on the compact arrays only.
 
 inline __host__ __device__ size_t align_up(size_t x, size_t a = 128) { return (x + a - 1) / a * a; }
 
@@ -36,27 +44,33 @@ struct GeomView {   // per-Gaussian state, SoA
     uint32_t* tiles_touched;  // [P]
     uint32_t* point_offsets;  // [P] inclusive scan
     uint32_t* num_rendered;   // [1] device copy of R (tail of the scan)
+    uint32_t* g_off;          // [P+1] CSR offsets: compact instances of Gaussian i are g_list[g_off[i] .. g_off[i+1])
+    uint32_t* g_cursor;       // [P]   build-time counters / cursors of the CSR
     char* scan_temp;
     size_t scan_temp_bytes;
     size_t total;
 };
 struct ImageView {  // per-pixel / per-tile state
     float* final_T;           // [N]
-    uint32_t* n_contrib;      // [N]
-    uint2* ranges;            // [T]
-    uint32_t* tile_max_contrib;  // [T] max n_contrib over the tile's pixels (bounds the JVP / VJP sweeps)
+    uint32_t* n_contrib;      // [N] last blended position in the FULL tile list (reference numbering, ImageState::n_contrib)
+    uint32_t* n_contrib_c;    // [N] the same in the COMPACT tile list (what the derivative sweeps use)
+    uint2* ranges;            // [T] full-list ranges (ImageState::ranges)
+    uint32_t* ccount;         // [T] compact instances per tile
+    uint32_t* cstart;         // [T+1] exclusive scan of ccount; cstart[T] = Rc
     size_t total;
 };
-struct BinningView {  // per-instance state that outlives the forward pass (56 B / instance)
-    float4* records;          // [3R]
-    uint32_t* point_list;     // [R] sorted Gaussian ids
-    uint32_t* inv_perm;       // [R] Gaussian-major slot -> sorted position
+struct BinningView {  // compact per-instance state that outlives the forward pass (56 B / compact instance)
+    float4* records;          // [3 Rc] compact records, tile|depth order
+    uint32_t* cid;            // [Rc] Gaussian id of each compact instance
+    uint32_t* g_list;         // [Rc] CSR payload: compact positions grouped by Gaussian (ascending within a Gaussian)
     size_t total;
 };
-struct BinningTemp {  // per-instance state that is dead once the forward pass returns (32 B / instance)
+struct BinningTemp {  // per-instance state that is dead once the forward pass returns (84 B / instance)
     uint64_t* keys_sorted;    // [R]
     uint64_t* keys_unsorted;  // [R]
     uint32_t* vals_unsorted;  // [R]
+    uint32_t* point_list;     // [R] sorted Gaussian ids (BinningState::point_list)
+    float4* records_tmp;      // [3R] compact records at tile-local positions (range.x + j), before the global scan
     char* sort_temp;
     size_t sort_temp_bytes;
     size_t total;
@@ -66,7 +80,7 @@ size_t scan_temp_bytes(int P);
 size_t sort_temp_bytes(int64_t R);
 GeomView carve_geom(void* base, int P);
 ImageView carve_image(void* base, int W, int H);
-BinningView carve_binning(void* base, int64_t R);
+BinningView carve_binning(void* base, int64_t Rc);
 BinningTemp carve_binning_temp(void* base, int64_t R);
 
 void set_error(const char* fmt, ...);
@@ -104,18 +118,23 @@ int launch_preprocess(const GslmGaussians& g, const GslmCamera& cam, const GeomV
                       cudaStream_t s);
 // writes the per-Gaussian tangent record tgeom[3P] for Gaussians with radii > 0 (zeros otherwise)
 int launch_preprocess_tangent(const GslmGaussians& g, const TangentPtrs& t, const GslmCamera& cam,
-                              const int32_t* radii, float4* tgeom, cudaStream_t s);
+                              const int32_t* radii, const uint32_t* g_off, float4* tgeom, cudaStream_t s);
 int launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present, cudaStream_t s);
 int launch_preprocess_bwd(const GslmGaussians& g, const GslmCamera& cam, const int32_t* radii, const GeomView& gv,
                           const BinningView& bv, const float4* inst_grads, bool has_invdepth_grad,
                           const GslmGrads& grads, cudaStream_t s);
 // binning.cu
 int run_scan(const GeomView& gv, int P, cudaStream_t s);
-int run_binning(const GeomView& gv, const int32_t* radii, const BinningView& bv, const BinningTemp& bt,
-                const ImageView& iv, int P, int W, int H, int64_t R, const float* features, cudaStream_t s);
+int run_binning(const GeomView& gv, const int32_t* radii, const BinningTemp& bt, const ImageView& iv, int P, int W,
+                int H, int64_t R, cudaStream_t s);
+// after k_blend_fwd: cstart = exclusive scan of ccount (device only)
+int run_tile_scan(const ImageView& iv, int W, int H, cudaStream_t s);
+// tile-local compact records -> dense compact arrays + per-Gaussian CSR
+int run_compaction(const GeomView& gv, const BinningView& bv, const BinningTemp& bt, const ImageView& iv, int P,
+                   int W, int H, int64_t Rc, cudaStream_t s);
 // blend.cu
-int launch_blend_fwd(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg, float* out_color,
-                     float* out_invdepth, cudaStream_t s);
+int launch_blend_fwd(const GeomView& gv, const BinningTemp& bt, const ImageView& iv, int W, int H,
+                     const float* features, const float* bg, float* out_color, float* out_invdepth, cudaStream_t s);
 int launch_blend_jvp(const BinningView& bv, const ImageView& iv, int W, int H, const float4* tgeom, const float* bg,
                      const float* bg_tangent, float* out_color_t, float* out_invdepth_t, cudaStream_t s);
 int launch_blend_bwd(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg,

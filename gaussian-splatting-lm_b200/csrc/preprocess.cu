@@ -152,18 +152,15 @@ __device__ __forceinline__ dualf ldd(const float* p, const float* t, size_t i) {
 
 template <bool CAMT>
 __global__ void __launch_bounds__(256)
-k_preprocess_tangent(PreTanArgs a, const int32_t* __restrict__ radii, float4* __restrict__ tgeom) {
+k_preprocess_tangent(PreTanArgs a, const int32_t* __restrict__ radii, const uint32_t* __restrict__ g_off,
+                     float4* __restrict__ tgeom) {
     __shared__ CamConst sc;
     load_cam(&sc, a.p.viewmatrix, a.p.projmatrix, a.p.campos, a.t.viewmatrix, a.t.projmatrix, a.t.campos);
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= a.p.P) return;
     float4* out = tgeom + (size_t)REC_F4 * idx;
-    if (radii[idx] <= 0) {
-        out[0] = make_float4(0.f, 0.f, 0.f, 0.f);
-        out[1] = make_float4(0.f, 0.f, 0.f, 0.f);
-        out[2] = make_float4(0.f, 0.f, 0.f, 0.f);
-        return;
-    }
+    // only Gaussians with at least one compact instance are ever looked up by the tile sweeps
+    if (radii[idx] <= 0 || g_off[idx] == g_off[idx + 1]) return;
     CamD<CAMT> cam{&sc, a.p.focal_x, a.p.focal_y, a.p.tan_fovx, a.p.tan_fovy,
                    a.focal_x_t, a.focal_y_t, a.t.tan_fovx, a.t.tan_fovy};
     v3<dualf> mean = {ldd(a.p.means3D, a.t.means3D, 3 * (size_t)idx), ldd(a.p.means3D, a.t.means3D, 3 * (size_t)idx + 1),
@@ -204,13 +201,17 @@ k_preprocess_tangent(PreTanArgs a, const int32_t* __restrict__ radii, float4* __
         cb_t = ct ? __ldg(ct + 3 * (size_t)idx + 2) : 0.f;
     }
     dualf invd = 1.f / o.depth;   // forward_impl.h:506: (1 / depth) on duals
-    out[0] = make_float4(o.x.d, o.y.d, o.conx.d, o.cony.d);
-    out[1] = make_float4(o.conz.d, o.opac.d, cr_t, cg_t);
+    // tangent of the exponent, power = -0.5 (A dx^2 + C dy^2) - B dx dy with dx = x - px, as a polynomial in
+    // (dx, dy):  power_t = dx (a3 dx + a5 dy + a1) + dy (a4 dy + a2)   (forward_impl.h:468-476 on duals)
+    const float a1 = -(o.conx.v * o.x.d + o.cony.v * o.y.d);
+    const float a2 = -(o.conz.v * o.y.d + o.cony.v * o.x.d);
+    out[0] = make_float4(a1, a2, -0.5f * o.conx.d, -0.5f * o.conz.d);
+    out[1] = make_float4(-o.cony.d, o.opac.d, cr_t, cg_t);
     out[2] = make_float4(cb_t, invd.d, 0.f, 0.f);
 }
 
 int launch_preprocess_tangent(const GslmGaussians& g, const TangentPtrs& t, const GslmCamera& cam,
-                              const int32_t* radii, float4* tgeom, cudaStream_t s) {
+                              const int32_t* radii, const uint32_t* g_off, float4* tgeom, cudaStream_t s) {
     PreTanArgs a;
     a.p.P = g.P; a.p.D = g.sh_degree; a.p.M = g.M; a.p.W = cam.width; a.p.H = cam.height;
     a.p.scale_modifier = g.scale_modifier; a.p.tan_fovx = cam.tan_fovx; a.p.tan_fovy = cam.tan_fovy;
@@ -228,8 +229,8 @@ int launch_preprocess_tangent(const GslmGaussians& g, const TangentPtrs& t, cons
     StageScope ts(ST_PRE_TANGENT, s);
     bool camt = t.viewmatrix || t.projmatrix || t.campos || t.tan_fovx != 0.f || t.tan_fovy != 0.f ||
                 t.scale_modifier != 0.f;
-    if (camt) k_preprocess_tangent<true><<<(g.P + 255) / 256, 256, 0, s>>>(a, radii, tgeom);
-    else k_preprocess_tangent<false><<<(g.P + 255) / 256, 256, 0, s>>>(a, radii, tgeom);
+    if (camt) k_preprocess_tangent<true><<<(g.P + 255) / 256, 256, 0, s>>>(a, radii, g_off, tgeom);
+    else k_preprocess_tangent<false><<<(g.P + 255) / 256, 256, 0, s>>>(a, radii, g_off, tgeom);
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
 }

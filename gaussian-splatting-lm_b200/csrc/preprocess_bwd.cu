@@ -5,8 +5,8 @@
 // + bwd computeColorFromSH (:23-142) + bwd computeCov3D (:330-393), and the ten float
 // atomicAdd per (pixel, Gaussian) hit of the reference's bwd renderCUDA (:593-635):
 // the tile kernels leave ONE 48-byte partial per (tile, Gaussian) instance in sorted
-// order (coalesced, no atomics); this kernel gathers a Gaussian's instances through
-// inv_perm (Gaussian-major slot -> sorted position) and sums them in a fixed order, so
+// order (coalesced, no atomics); this kernel gathers a Gaussian's compact instances through
+// the CSR (g_off, g_list) built at linearisation time and sums them in a fixed order, so
 // the whole backward pass is deterministic.
 // Quirks of the reference kept on purpose: 1/(det^2 + 1e-7) in the
 // conic adjoint, no quaternion-normalisation Jacobian, the alpha-clamp is not masked.
@@ -24,8 +24,8 @@ struct BwdArgs {
     const float *viewmatrix, *projmatrix, *campos;
     const int32_t* radii;
     const uint8_t* clamped;
-    const uint32_t* point_offsets;
-    const uint32_t* inv_perm;
+    const uint32_t* g_off;
+    const uint32_t* g_list;
     const float4* inst_grads;
     GslmGrads g;
 };
@@ -46,7 +46,9 @@ __global__ void __launch_bounds__(128) k_preprocess_bwd(BwdArgs a) {
     if (idx >= a.P) return;
     const size_t i = idx;
     const int ncoef = a.shs ? a.M : 0;
-    if (a.radii[idx] <= 0) {
+    const uint32_t beg = a.g_off[idx], end = a.g_off[idx + 1];
+    // culled, or visible but blended by no pixel: every gradient is exactly zero
+    if (a.radii[idx] <= 0 || beg == end) {
         if (!ACC) {  // overwrite mode: culled Gaussians get exact zeros
             for (int k = 0; k < 3; k++) { put<false>(a.g.dL_dmeans2D, 3 * i + k, 0.f); put<false>(a.g.dL_dcolors, 3 * i + k, 0.f);
                                           put<false>(a.g.dL_dmeans3D, 3 * i + k, 0.f); put<false>(a.g.dL_dscales, 3 * i + k, 0.f); }
@@ -61,9 +63,8 @@ __global__ void __launch_bounds__(128) k_preprocess_bwd(BwdArgs a) {
     float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
     float2 s2 = make_float2(0.f, 0.f);
     {
-        uint32_t beg = idx == 0 ? 0u : a.point_offsets[idx - 1], end = a.point_offsets[idx];
         for (uint32_t slot = beg; slot < end; slot++) {
-            const float4* r = a.inst_grads + (size_t)REC_F4 * __ldg(a.inv_perm + slot);
+            const float4* r = a.inst_grads + (size_t)REC_F4 * __ldg(a.g_list + slot);
             float4 q0 = __ldg(r), q1 = __ldg(r + 1), q2 = __ldg(r + 2);
             s0.x += q0.x; s0.y += q0.y; s0.z += q0.z; s0.w += q0.w;
             s1.x += q1.x; s1.y += q1.y; s1.z += q1.z; s1.w += q1.w;
@@ -303,7 +304,7 @@ int launch_preprocess_bwd(const GslmGaussians& g, const GslmCamera& cam, const i
     a.cov3D = g.cov3D_precomp ? g.cov3D_precomp : gv.cov3D;
     a.shs = g.colors_precomp ? nullptr : g.shs;
     a.viewmatrix = cam.viewmatrix; a.projmatrix = cam.projmatrix; a.campos = cam.campos;
-    a.radii = radii; a.clamped = gv.clamped; a.point_offsets = gv.point_offsets; a.inv_perm = bv.inv_perm;
+    a.radii = radii; a.clamped = gv.clamped; a.g_off = gv.g_off; a.g_list = bv.g_list;
     a.inst_grads = inst_grads; a.g = grads;
     int grid = (g.P + 127) / 128;
     StageScope ts(ST_PRE_BWD, s);

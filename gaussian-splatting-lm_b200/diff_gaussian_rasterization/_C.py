@@ -42,7 +42,33 @@ class GslmGrads(C.Structure):
 class GslmBufferView(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("point_list", "keys_sorted", "ranges", "n_contrib", "final_T",
                                           "tiles_touched", "point_offsets", "depths", "means2D", "conic_opacity",
-                                          "rgb", "cov3D", "clamped", "tile_max_contrib")]
+                                          "rgb", "cov3D", "clamped", "n_contrib_c", "cstart", "records", "cid",
+                                          "g_off", "g_list")]
+
+
+class NumRendered(int):
+    """The reference's `num_rendered` (R = sum of tiles_touched) as a plain int for API compatibility, carrying
+    the size of the compact linearisation cache in `.cached` (Rc <= R) for the derivative entry points."""
+    cached = 0
+
+    def __new__(cls, rendered, cached):
+        o = super().__new__(cls, rendered)
+        o.cached = int(cached)
+        return o
+
+
+def _cached(R, imageBuffer=None, W=None, H=None):
+    """Rc of a forward call: from the NumRendered it returned, else (a caller that rebuilt a plain int) read
+    back from the image buffer (cstart[T]) -- one 4-byte device read."""
+    if isinstance(R, NumRendered):
+        return R.cached
+    if imageBuffer is None or imageBuffer.numel() == 0:
+        return 0
+    v = GslmBufferView()
+    _check(lib().gslm_buffer_view(0, int(W), int(H), 0, 0, None, None, imageBuffer.data_ptr(), None, C.addressof(v)))
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    off = v.cstart - imageBuffer.data_ptr() + 4 * T
+    return int(imageBuffer[off:off + 4].view(torch.int32).item())
 
 
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_int32, C.c_size_t)
@@ -74,12 +100,12 @@ def lib():
         L.gslm_jtjv_scratch_bytes.argtypes = [C.c_int32, C.c_int64]
         vp = C.c_void_p
         L.gslm_mark_visible.argtypes = [C.c_int32, vp, vp, vp, vp, vp]
-        L.gslm_forward.argtypes = [vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp]
-        L.gslm_forward_jvp.argtypes = [vp, vp, vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp, vp, vp]
+        L.gslm_forward.argtypes = [vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp, vp]
+        L.gslm_forward_jvp.argtypes = [vp, vp, vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         L.gslm_backward.argtypes = [vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
         L.gslm_jvp_cached.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp]
         L.gslm_jtjv.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
-        L.gslm_buffer_view.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, vp, vp, vp, vp, vp]
+        L.gslm_buffer_view.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int64, vp, vp, vp, vp, vp]
         L.gslm_timing_stage_name.restype = C.c_char_p
         L.gslm_timing_collect.argtypes = [vp, vp]
         _lib = L
@@ -204,13 +230,13 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     if P == 0:   # rasterize_points.cu:105
         out_color.zero_(); out_invdepth.zero_()
         e = torch.empty(0, dtype=torch.uint8, device=dev)
-        return 0, out_color, radii, e, e.clone(), e.clone(), out_invdepth
+        return NumRendered(0, 0), out_color, radii, e, e.clone(), e.clone(), out_invdepth
     al = _Alloc(dev)
-    n = C.c_int32(0)
+    n, nc = C.c_int32(0), C.c_int32(0)
     _check(L.gslm_forward(C.addressof(g), C.addressof(cam), al.cb, None, out_color.data_ptr(),
-                          out_invdepth.data_ptr(), radii.data_ptr(), C.addressof(n), _stream()))
+                          out_invdepth.data_ptr(), radii.data_ptr(), C.addressof(n), C.addressof(nc), _stream()))
     _after_forward(al)
-    return int(n.value), out_color, radii, al.get(0), al.get(1), al.get(2), out_invdepth
+    return NumRendered(n.value, nc.value), out_color, radii, al.get(0), al.get(1), al.get(2), out_invdepth
 
 
 def rasterize_gaussians_jvp(background, background_grad, means3D, means3D_grad, colors, colors_grad, opacity,
@@ -242,14 +268,15 @@ def rasterize_gaussians_jvp(background, background_grad, means3D, means3D_grad, 
         for t in (out_color, out_invdepth, out_color_t, out_invdepth_t):
             t.zero_()
         e = torch.empty(0, dtype=torch.uint8, device=dev)
-        return 0, out_color, radii, e, e.clone(), e.clone(), out_invdepth, out_color_t, out_invdepth_t
+        return NumRendered(0, 0), out_color, radii, e, e.clone(), e.clone(), out_invdepth, out_color_t, out_invdepth_t
     al = _Alloc(dev)
-    n = C.c_int32(0)
+    n, nc = C.c_int32(0), C.c_int32(0)
     _check(L.gslm_forward_jvp(C.addressof(g), C.addressof(gt), C.addressof(cam), C.addressof(ct), al.cb, None,
                               out_color.data_ptr(), out_invdepth.data_ptr(), radii.data_ptr(),
-                              out_color_t.data_ptr(), out_invdepth_t.data_ptr(), C.addressof(n), _stream()))
+                              out_color_t.data_ptr(), out_invdepth_t.data_ptr(), C.addressof(n), C.addressof(nc),
+                              _stream()))
     _after_forward(al)
-    return (int(n.value), out_color, radii, al.get(0), al.get(1), al.get(2), out_invdepth, out_color_t,
+    return (NumRendered(n.value, nc.value), out_color, radii, al.get(0), al.get(1), al.get(2), out_invdepth, out_color_t,
             out_invdepth_t)
 
 
@@ -280,9 +307,10 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, opacities, 
     (gr.dL_dmeans2D, gr.dL_dcolors, gr.dL_dopacity, gr.dL_dmeans3D, gr.dL_dcov3D, gr.dL_dsh, gr.dL_dscales,
      gr.dL_drotations) = [_ptr(o) for o in outs]
     gr.accumulate = 0 if accumulate_into is None else 1
-    scratch = torch.empty(L.gslm_backward_scratch_bytes(int(R)), dtype=torch.uint8, device=dev)
+    Rc = _cached(R, imageBuffer, W, H)
+    scratch = torch.empty(L.gslm_backward_scratch_bytes(Rc), dtype=torch.uint8, device=dev)
     _check(L.gslm_backward(C.addressof(g), C.addressof(cam), _ptr(radii), _ptr(geomBuffer), _ptr(binningBuffer),
-                           _ptr(imageBuffer), int(R), _ptr(dcol), _ptr(dinv), scratch.data_ptr(), C.addressof(gr),
+                           _ptr(imageBuffer), Rc, _ptr(dcol), _ptr(dinv), scratch.data_ptr(), C.addressof(gr),
                            _stream()))
     return outs
 
@@ -316,7 +344,8 @@ def jvp_cached(gauss_args, tangent_args, cam_args, radii, geomBuffer, R, binning
     out_d = torch.empty((1, H, W), dtype=torch.float32, device=dev) if want_invdepth else None
     scratch = torch.empty(L.gslm_jvp_scratch_bytes(g.P), dtype=torch.uint8, device=dev)
     _check(L.gslm_jvp_cached(C.addressof(g), C.addressof(gt), C.addressof(cam), _ptr(radii), _ptr(geomBuffer),
-                             _ptr(binningBuffer), _ptr(imageBuffer), int(R), scratch.data_ptr(), out_t.data_ptr(),
+                             _ptr(binningBuffer), _ptr(imageBuffer), _cached(R, imageBuffer, W, H), scratch.data_ptr(),
+                             out_t.data_ptr(),
                              _ptr(out_d), _stream()))
     return out_t, out_d
 
@@ -331,7 +360,8 @@ def jtjv(gauss_args, tangent_args, cam_args, radii, geomBuffer, R, binningBuffer
     cam, k2 = _camera(bg, vm, pm, tfx, tfy, H, W, campos, False, aa, dbg)
     dev = k1[0].device
     w = _f32(weight)
-    need = L.gslm_jtjv_scratch_bytes(g.P, int(R))
+    Rc = _cached(R, imageBuffer, W, H)
+    need = L.gslm_jtjv_scratch_bytes(g.P, Rc)
     if scratch is None or scratch.numel() < need:
         scratch = torch.empty(need, dtype=torch.uint8, device=dev)
     gr = GslmGrads()
@@ -339,16 +369,19 @@ def jtjv(gauss_args, tangent_args, cam_args, radii, geomBuffer, R, binningBuffer
      gr.dL_drotations) = [_ptr(o) for o in outs]
     gr.accumulate = 1
     _check(L.gslm_jtjv(C.addressof(g), C.addressof(gt), C.addressof(cam), _ptr(radii), _ptr(geomBuffer),
-                       _ptr(binningBuffer), _ptr(imageBuffer), int(R), _ptr(w), scratch.data_ptr(),
+                       _ptr(binningBuffer), _ptr(imageBuffer), Rc, _ptr(w), scratch.data_ptr(),
                        C.addressof(gr), _ptr(out_vJJv), _stream()))
     return scratch
 
 
 def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer, sortScratch=None):
-    """Test helper: torch views of the integer state inside the opaque buffers (bit-exactness checks).
-    sortScratch (the which = 3 allocation of the forward call, see KEEP_SORT_SCRATCH) adds `keys_sorted`."""
+    """Test helper: torch views of the state inside the opaque buffers (bit-exactness checks).
+    sortScratch (the which = 3 allocation of the forward call, see KEEP_SORT_SCRATCH) adds `keys_sorted` and the
+    full sorted `point_list`."""
+    Rc = _cached(R, imageBuffer, W, H)
+    R = int(R)
     v = GslmBufferView()
-    _check(lib().gslm_buffer_view(int(P), int(W), int(H), int(R), _ptr(geomBuffer), _ptr(binningBuffer),
+    _check(lib().gslm_buffer_view(int(P), int(W), int(H), R, Rc, _ptr(geomBuffer), _ptr(binningBuffer),
                                   _ptr(imageBuffer), _ptr(sortScratch), C.addressof(v)))
 
     def view(buf, ptr, nbytes, dtype, shape):
@@ -357,16 +390,20 @@ def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer, sortScratch=
 
     T = ((W + 15) // 16) * ((H + 15) // 16)
     N = W * H
-    out = {}
-    if binningBuffer is not None and binningBuffer.numel() and R > 0:
-        out["point_list"] = view(binningBuffer, v.point_list, 4 * R, torch.int32, (R,))
+    out = {"num_cached": Rc}
+    if binningBuffer is not None and binningBuffer.numel() and Rc > 0:
+        out["records"] = view(binningBuffer, v.records, 48 * Rc, torch.float32, (Rc, 12))
+        out["cid"] = view(binningBuffer, v.cid, 4 * Rc, torch.int32, (Rc,))
+        out["g_list"] = view(binningBuffer, v.g_list, 4 * Rc, torch.int32, (Rc,))
     if sortScratch is not None and sortScratch.numel() and R > 0:
         out["keys_sorted"] = view(sortScratch, v.keys_sorted, 8 * R, torch.int64, (R,))
+        out["point_list"] = view(sortScratch, v.point_list, 4 * R, torch.int32, (R,))
     if imageBuffer is not None and imageBuffer.numel():
         out["ranges"] = view(imageBuffer, v.ranges, 8 * T, torch.int32, (T, 2))
         out["n_contrib"] = view(imageBuffer, v.n_contrib, 4 * N, torch.int32, (H, W))
+        out["n_contrib_c"] = view(imageBuffer, v.n_contrib_c, 4 * N, torch.int32, (H, W))
         out["final_T"] = view(imageBuffer, v.final_T, 4 * N, torch.float32, (H, W))
-        out["tile_max_contrib"] = view(imageBuffer, v.tile_max_contrib, 4 * T, torch.int32, (T,))
+        out["cstart"] = view(imageBuffer, v.cstart, 4 * (T + 1), torch.int32, (T + 1,))
     if geomBuffer is not None and geomBuffer.numel():
         out["tiles_touched"] = view(geomBuffer, v.tiles_touched, 4 * P, torch.int32, (P,))
         out["point_offsets"] = view(geomBuffer, v.point_offsets, 4 * P, torch.int32, (P,))
@@ -376,6 +413,7 @@ def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer, sortScratch=
         out["rgb"] = view(geomBuffer, v.rgb, 12 * P, torch.float32, (P, 3))
         out["cov3D"] = view(geomBuffer, v.cov3D, 24 * P, torch.float32, (P, 6))
         out["clamped"] = view(geomBuffer, v.clamped, P, torch.uint8, (P,))
+        out["g_off"] = view(geomBuffer, v.g_off, 4 * (P + 1), torch.int32, (P + 1,))
     return out
 
 

@@ -9,10 +9,16 @@
  *
  * All functions return 0 on success, non-zero on failure; gslm_last_error() gives the
  * message (thread-local).  Kernels are launched on `stream` (a cudaStream_t passed as
- * void*); the only host synchronisation is the 4-byte read-back of num_rendered inside
- * gslm_forward / gslm_forward_jvp (the reference has the same one,
- * DGR/cuda_rasterizer/rasterizer_impl.cu:325) plus a full sync when camera.debug != 0
- * (DGR/cuda_rasterizer/auxiliary.h:262-269).
+ * void*); the only host synchronisations are two 4-byte read-backs inside gslm_forward /
+ * gslm_forward_jvp -- num_rendered R (the reference has the same one,
+ * DGR/cuda_rasterizer/rasterizer_impl.cu:325) and num_cached Rc, the number of instances the
+ * forward pass actually blended, which sizes the compact linearisation cache -- plus a full
+ * sync when camera.debug != 0 (DGR/cuda_rasterizer/auxiliary.h:262-269).  The derivative
+ * entry points (backward, jvp_cached, jtjv) never synchronise.
+ *
+ * Two instance counts cross the ABI: num_rendered = R = sum of tiles_touched, the reference's
+ * num_rendered (rasterize_points.cu:117); num_cached = Rc <= R, the instances kept for the
+ * derivative passes (all others have exactly zero tangent and gradient).
  * ========================================================================== */
 #ifndef GSLM_B200_H
 #define GSLM_B200_H
@@ -96,8 +102,8 @@ int32_t gslm_abi_version(void);
  * (DGR/cuda_rasterizer/rasterizer_impl.h:29-43). */
 size_t gslm_geom_bytes(int32_t P);
 size_t gslm_image_bytes(int32_t width, int32_t height);
-size_t gslm_binning_bytes(int64_t num_rendered);
-size_t gslm_binning_temp_bytes(int64_t num_rendered);
+size_t gslm_binning_bytes(int64_t num_cached);        /* persistent compact cache: 56 B / cached instance */
+size_t gslm_binning_temp_bytes(int64_t num_rendered); /* sort scratch: ~96 B / rendered instance, dead after forward */
 
 /* Replaces _C.mark_visible (DGR/rasterize_points.cu:401-420). present: uint8 [P]. */
 int32_t gslm_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
@@ -107,7 +113,8 @@ int32_t gslm_mark_visible(int32_t P, const float* means3D, const float* viewmatr
  * CudaRasterizer::Rasterizer::forward, DGR/cuda_rasterizer/rasterizer_impl.cu:239-391).
  * out_color [3,H,W], out_invdepth [1,H,W], radii int32 [P], *num_rendered host int. */
 int32_t gslm_forward(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn alloc, void* alloc_ctx,
-                     float* out_color, float* out_invdepth, int32_t* radii, int32_t* num_rendered, void* stream);
+                     float* out_color, float* out_invdepth, int32_t* radii, int32_t* num_rendered,
+                     int32_t* num_cached, void* stream);
 
 /* Replaces _C.rasterize_gaussians_jvp (DGR/rasterize_points.cu:143-298; forwardJvp,
  * DGR/cuda_rasterizer/rasterizer_jvp_impl.h:125-325).  `gt` holds the tangent pointers in
@@ -117,14 +124,14 @@ int32_t gslm_forward(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn 
 int32_t gslm_forward_jvp(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam,
                          const GslmCameraTangent* camt, GslmAllocFn alloc, void* alloc_ctx, float* out_color,
                          float* out_invdepth, int32_t* radii, float* out_color_tangent, float* out_invdepth_tangent,
-                         int32_t* num_rendered, void* stream);
+                         int32_t* num_rendered, int32_t* num_cached, void* stream);
 
 /* Replaces _C.rasterize_gaussians_backward (DGR/rasterize_points.cu:300-399;
  * Rasterizer::backward, DGR/cuda_rasterizer/rasterizer_impl.cu:395-500).
- * dL_dinvdepth may be NULL.  `scratch` = gslm_backward_scratch_bytes(num_rendered) bytes. */
-size_t gslm_backward_scratch_bytes(int64_t num_rendered);
+ * dL_dinvdepth may be NULL.  `scratch` = gslm_backward_scratch_bytes(num_cached) bytes. */
+size_t gslm_backward_scratch_bytes(int64_t num_cached);
 int32_t gslm_backward(const GslmGaussians* g, const GslmCamera* cam, const int32_t* radii, const void* geom_buffer,
-                      const void* binning_buffer, const void* image_buffer, int32_t num_rendered,
+                      const void* binning_buffer, const void* image_buffer, int32_t num_cached,
                       const float* dL_dcolor, const float* dL_dinvdepth, void* scratch, GslmGrads* grads,
                       void* stream);
 
@@ -139,7 +146,7 @@ int32_t gslm_backward(const GslmGaussians* g, const GslmCamera* cam, const int32
 size_t gslm_jvp_scratch_bytes(int32_t P);
 int32_t gslm_jvp_cached(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam, const int32_t* radii,
                         const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
-                        int32_t num_rendered, void* scratch, float* out_color_tangent, float* out_invdepth_tangent,
+                        int32_t num_cached, void* scratch, float* out_color_tangent, float* out_invdepth_tangent,
                         void* stream);
 
 /* Fused Gauss-Newton product for one linearised view, J never materialised:
@@ -148,11 +155,11 @@ int32_t gslm_jvp_cached(const GslmGaussians* g, const GslmGaussians* gt, const G
  * gaussian_renderer/batch_render.py:118), NULL => w = 1.
  * out_vJJv (device float[1], may be NULL) accumulates v^T J^T W J v = sum w * (Jv)^2, the
  * p^T A p that CG needs (solver/conjugate_gradient.py:28), for free.
- * scratch: gslm_jtjv_scratch_bytes(P, num_rendered). */
-size_t gslm_jtjv_scratch_bytes(int32_t P, int64_t num_rendered);
+ * scratch: gslm_jtjv_scratch_bytes(P, num_cached). */
+size_t gslm_jtjv_scratch_bytes(int32_t P, int64_t num_cached);
 int32_t gslm_jtjv(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam, const int32_t* radii,
                   const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
-                  int32_t num_rendered, const float* weight, void* scratch, GslmGrads* grads, float* out_vJJv,
+                  int32_t num_cached, const float* weight, void* scratch, GslmGrads* grads, float* out_vJJv,
                   void* stream);
 
 /* ---- optional per-stage device timing (no reference counterpart; bench.py's live roofline numbers) ----
@@ -166,10 +173,10 @@ int32_t gslm_timing_collect(float* ms, int32_t* counts);
 
 /* Introspection for tests (bit-exact binning checks): device pointers INTO the buffers. */
 typedef struct GslmBufferView {
-    const uint32_t* point_list;   /* [R] sorted Gaussian ids   (rasterizer.h BinningState::point_list) */
-    const uint64_t* keys_sorted;  /* [R] tile<<32 | depth bits (lives in the sort scratch; NULL without it) */
-    const uint32_t* ranges;       /* [T,2] per-tile [start,end) (ImageState::ranges)                    */
-    const uint32_t* n_contrib;    /* [H*W]                                                              */
+    const uint32_t* point_list;   /* [R] sorted Gaussian ids (BinningState::point_list; lives in the sort scratch) */
+    const uint64_t* keys_sorted;  /* [R] tile<<32 | depth bits (sort scratch)                           */
+    const uint32_t* ranges;       /* [T,2] per-tile [start,end) in the full list (ImageState::ranges)   */
+    const uint32_t* n_contrib;    /* [H*W] reference numbering                                          */
     const float* final_T;         /* [H*W]                                                              */
     const uint32_t* tiles_touched;/* [P]                                                                */
     const uint32_t* point_offsets;/* [P] inclusive scan                                                 */
@@ -179,11 +186,16 @@ typedef struct GslmBufferView {
     const float* rgb;             /* [P,3]                                                              */
     const float* cov3D;           /* [P,6]                                                              */
     const uint8_t* clamped;       /* [P] bit c set <=> channel c clamped                                */
-    const uint32_t* tile_max_contrib; /* [T] max n_contrib over the tile: instances the cached sweeps visit */
+    const uint32_t* n_contrib_c;  /* [H*W] last blended position in the compact tile list               */
+    const uint32_t* cstart;       /* [T+1] compact tile offsets, cstart[T] = Rc                         */
+    const float* records;         /* [Rc,12] compact instance records                                   */
+    const uint32_t* cid;          /* [Rc] Gaussian id per compact instance                              */
+    const uint32_t* g_off;        /* [P+1] CSR offsets into g_list                                      */
+    const uint32_t* g_list;       /* [Rc] compact positions grouped by Gaussian                         */
 } GslmBufferView;
-int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_rendered, const void* geom_buffer,
-                         const void* binning_buffer, const void* image_buffer, const void* binning_temp_buffer,
-                         GslmBufferView* out);
+int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_rendered, int64_t num_cached,
+                         const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
+                         const void* binning_temp_buffer, GslmBufferView* out);
 
 #ifdef __cplusplus
 }

@@ -36,8 +36,18 @@ def cam_tensors(cam, bg=(0.0, 0.0, 0.0), dev="cuda"):
                 H=cam.image_height, W=cam.image_width)
 
 
-def c_forward(_C, gd, ct, antialiasing=False, scale_modifier=1.0, debug=False):
+def c_forward(_C, gd, ct, antialiasing=False, scale_modifier=1.0, debug=False, keep_sort_scratch=False):
+    """keep_sort_scratch: keep the sort scratch of this call alive in _C.LAST_SORT_SCRATCH (sorted keys / full
+    point_list for the bit-exactness checks)."""
     e = torch.empty(0, device=gd["means3D"].device)
+    _C.KEEP_SORT_SCRATCH = bool(keep_sort_scratch)
+    try:
+        return _c_forward(_C, gd, ct, antialiasing, scale_modifier, debug, e)
+    finally:
+        _C.KEEP_SORT_SCRATCH = False
+
+
+def _c_forward(_C, gd, ct, antialiasing, scale_modifier, debug, e):
     return _C.rasterize_gaussians(ct["bg"], gd["means3D"], gd.get("colors_precomp", e), gd["opacities"],
                                   gd.get("scales", e), gd.get("rotations", e), scale_modifier,
                                   gd.get("cov3D_precomp", e), ct["viewmatrix"], ct["projmatrix"], ct["tan_fovx"],

@@ -47,9 +47,9 @@ def test_size_queries(lib):
     assert lib.gslm_abi_version() >= 1
     g0, g1 = lib.gslm_geom_bytes(ctypes.c_int32(0)), lib.gslm_geom_bytes(ctypes.c_int32(1000))
     assert g1 > g0 and g1 % 128 == 0
-    # per-pixel state: final_T + n_contrib = 8 B / pixel (+ per-tile ranges)
+    # per-pixel state: final_T + n_contrib + n_contrib_c = 12 B / pixel (+ per-tile ranges / compact offsets)
     i = lib.gslm_image_bytes(ctypes.c_int32(1920), ctypes.c_int32(1080))
-    assert 8 * 1920 * 1080 <= i <= 9 * 1920 * 1080
+    assert 12 * 1920 * 1080 <= i <= 13 * 1920 * 1080
     b0, b1 = lib.gslm_binning_bytes(ctypes.c_int64(0)), lib.gslm_binning_bytes(ctypes.c_int64(1 << 20))
     assert b1 > b0 and b1 >= (1 << 20) * (48 + 4 + 4)
     assert lib.gslm_backward_scratch_bytes(ctypes.c_int64(1000)) >= 1000 * 40

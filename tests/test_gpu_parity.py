@@ -47,9 +47,10 @@ def test_golden_fixture_binning_bit_exact(C, golden):
     ct = dict(bg=t("bg"), viewmatrix=t("viewmatrix"), projmatrix=t("projmatrix"),
               campos=torch.from_numpy(d["campos_raw"][:3].copy()).to(dev), tan_fovx=float(d["tan_fovx"]),
               tan_fovy=float(d["tan_fovy"]), H=H, W=W)
-    R, color, radii, geom, binning, img, invd = h.c_forward(C, gd, ct, scale_modifier=float(d["scale_modifier"]))
+    R, color, radii, geom, binning, img, invd = h.c_forward(C, gd, ct, scale_modifier=float(d["scale_modifier"]),
+                                                            keep_sort_scratch=True)
     assert R == 91378
-    v = C.buffer_view(gd["means3D"].shape[0], W, H, R, geom, binning, img)
+    v = C.buffer_view(gd["means3D"].shape[0], W, H, R, geom, binning, img, C.LAST_SORT_SCRATCH)
     assert np.array_equal(v["point_offsets"].cpu().numpy().astype(np.uint32), d["point_offsets"])
     assert np.array_equal(v["point_list"].cpu().numpy().astype(np.uint32), d["point_list"])
     assert np.array_equal(v["ranges"].cpu().numpy().astype(np.uint32), d["ranges"])
@@ -66,9 +67,7 @@ def test_golden_fixture_binning_bit_exact(C, golden):
 def test_forward_vs_oracle(C, name, deg, aa):
     g, cam, c = _scene(name, deg=deg, aa=aa)
     gd, ct = h.to_dev(g), h.cam_tensors(cam, bg=c["bg"])
-    C.KEEP_SORT_SCRATCH = True
-    R, color, radii, geom, binning, img, invd = h.c_forward(C, gd, ct, antialiasing=aa)
-    C.KEEP_SORT_SCRATCH = False
+    R, color, radii, geom, binning, img, invd = h.c_forward(C, gd, ct, antialiasing=aa, keep_sort_scratch=True)
     ref = o.render_forward(g, c)
     P, W, H = g["means3D"].shape[0], c["W"], c["H"]
     v = C.buffer_view(P, W, H, R, geom, binning, img, C.LAST_SORT_SCRATCH)
@@ -321,3 +320,44 @@ def test_autograd_surface(C):
         assert tan is not None
         assert h.rel_l2(tan.cpu().numpy(), ref["t_color"]) < DER_TOL
         assert h.rel_l2(fwAD.unpack_dual(outd).tangent.cpu().numpy(), ref["t_invdepth"]) < DER_TOL
+
+
+def test_compact_cache_structure(C):
+    """The compact linearisation cache: tile offsets are a scan, every compact record carries its id, the CSR
+    (g_off, g_list) is a permutation of the compact positions grouped by Gaussian and ascending inside a group,
+    n_contrib_c never exceeds the tile's compact count, and a pixel's compact count equals the number of
+    instances it blended or skipped before its last hit that SOME pixel of the tile blended."""
+    g, cam, c = _scene("A", deg=1)
+    gd, ct = h.to_dev(g), h.cam_tensors(cam, bg=c["bg"])
+    R, color, radii, geom, binning, img, invd = h.c_forward(C, gd, ct, keep_sort_scratch=True)
+    P, W, H = g["means3D"].shape[0], c["W"], c["H"]
+    v = C.buffer_view(P, W, H, R, geom, binning, img, C.LAST_SORT_SCRATCH)
+    Rc = v["num_cached"]
+    assert 0 < Rc <= int(R) and R.cached == Rc
+    cstart = v["cstart"].cpu().numpy().astype(np.int64)
+    assert cstart[0] == 0 and cstart[-1] == Rc and (np.diff(cstart) >= 0).all()
+    ranges = v["ranges"].cpu().numpy().astype(np.int64)
+    assert (np.diff(cstart) <= ranges[:, 1] - ranges[:, 0]).all()
+    rec = v["records"]
+    cid = v["cid"].cpu().numpy()
+    assert np.array_equal(rec[:, 10].contiguous().view(torch.int32).cpu().numpy(), cid)
+    # each tile's compact list is a subsequence of its full sorted list
+    pl = v["point_list"].cpu().numpy()
+    for t in (0, len(ranges) // 2, len(ranges) - 1):
+        full = pl[ranges[t, 0]:ranges[t, 1]].tolist()
+        it = iter(full)
+        assert all(any(x == y for y in it) for x in cid[cstart[t]:cstart[t + 1]].tolist())
+    g_off = v["g_off"].cpu().numpy().astype(np.int64)
+    g_list = v["g_list"].cpu().numpy().astype(np.int64)
+    assert g_off[0] == 0 and g_off[-1] == Rc
+    assert np.array_equal(np.sort(g_list), np.arange(Rc))
+    owner = np.repeat(np.arange(P), np.diff(g_off))
+    assert np.array_equal(cid[g_list], owner)
+    same = owner[1:] == owner[:-1]
+    assert (np.diff(g_list)[same] > 0).all()
+    # per pixel
+    ncc = v["n_contrib_c"].cpu().numpy().astype(np.int64)
+    gx = (W + 15) // 16
+    tile_of = (np.arange(H)[:, None] // 16) * gx + (np.arange(W)[None, :] // 16)
+    assert (ncc <= np.diff(cstart)[tile_of]).all()
+    assert ((ncc == 0) == (v["n_contrib"].cpu().numpy() == 0)).all()
