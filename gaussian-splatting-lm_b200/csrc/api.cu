@@ -239,6 +239,7 @@ int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_r
     if (binning_buffer) {
         BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_cached);
         out->records = reinterpret_cast<const float*>(bv.records); out->cid = bv.cid; out->g_list = bv.g_list;
+        out->masks = reinterpret_cast<const uint32_t*>(bv.masks);
     }
     if (binning_temp_buffer) {
         BinningTemp bt = carve_binning_temp(const_cast<void*>(binning_temp_buffer), num_rendered);

@@ -97,6 +97,7 @@ BinningView carve_binning(void* base, int64_t Rc) {
     char* p = reinterpret_cast<char*>(base);
     size_t n = (size_t)Rc;
     v.records = take<float4>(p, REC_F4 * n);
+    v.masks = take<uint4>(p, 2 * n);
     v.cid = take<uint32_t>(p, n);
     v.g_list = take<uint32_t>(p, n);
     v.total = (size_t)(p - reinterpret_cast<char*>(base));
@@ -111,6 +112,7 @@ BinningTemp carve_binning_temp(void* base, int64_t R) {
     v.vals_unsorted = take<uint32_t>(p, n);
     v.point_list = take<uint32_t>(p, n);
     v.records_tmp = take<float4>(p, REC_F4 * n);
+    v.masks_tmp = take<uint4>(p, 2 * n);
     v.sort_temp_bytes = sort_temp_bytes(R);
     v.sort_temp = take<char>(p, v.sort_temp_bytes);
     v.total = (size_t)(p - reinterpret_cast<char*>(base));
@@ -251,24 +253,35 @@ int run_tile_scan(const ImageView& iv, int W, int H, cudaStream_t s) {
     return 0;
 }
 
-// one CTA per tile: tile-local compact records -> dense positions; ids; per-Gaussian counts
+// one CTA per tile: tile-local compact records -> dense positions in derivative form (gslm_common.cuh); hit
+// masks; ids; per-Gaussian counts
 __global__ void __launch_bounds__(256)
 k_compact_copy(const uint2* __restrict__ ranges, const uint32_t* __restrict__ cstart,
-               const uint32_t* __restrict__ ccount, const float4* __restrict__ src, float4* __restrict__ dst,
-               uint32_t* __restrict__ cid, uint32_t* __restrict__ g_cnt) {
+               const uint32_t* __restrict__ ccount, const float4* __restrict__ src, const uint4* __restrict__ msrc,
+               float4* __restrict__ dst, uint4* __restrict__ mdst, uint32_t* __restrict__ cid,
+               uint32_t* __restrict__ g_cnt) {
     const int tile = blockIdx.x;
     const uint32_t n = ccount[tile];
     if (n == 0) return;
+    const float L = 1.4426950408889634f;
     const size_t s0 = (size_t)ranges[tile].x * REC_F4, d0 = (size_t)cstart[tile] * REC_F4;
     for (uint32_t i = threadIdx.x; i < n * REC_F4; i += blockDim.x) {
-        const float4 q = src[s0 + i];
-        dst[d0 + i] = q;
-        if (i % REC_F4 == 2) {
+        float4 q = src[s0 + i];
+        const uint32_t part = i % REC_F4;
+        if (part == 0) {
+            q.z *= -0.5f * L; q.w *= -L;
+        } else if (part == 1) {
+            q.x *= -0.5f * L; q.y = log2f(q.y);
+        } else {
             const uint32_t id = __float_as_uint(q.z);
+            q.w = src[s0 + i - 1].y;   // opacity
             cid[cstart[tile] + i / REC_F4] = id;
             atomicAdd(&g_cnt[id], 1u);
         }
+        dst[d0 + i] = q;
     }
+    const size_t ms0 = (size_t)ranges[tile].x * 2, md0 = (size_t)cstart[tile] * 2;
+    for (uint32_t i = threadIdx.x; i < n * 2; i += blockDim.x) mdst[md0 + i] = msrc[ms0 + i];
 }
 __global__ void __launch_bounds__(256)
 k_fill_glist(uint32_t Rc, const uint32_t* __restrict__ cid, uint32_t* __restrict__ g_cursor, uint32_t* __restrict__ g_list) {
@@ -298,7 +311,8 @@ int run_compaction(const GeomView& gv, const BinningView& bv, const BinningTemp&
     GSLM_CUDA_OK(cudaMemsetAsync(gv.g_cursor, 0, sizeof(uint32_t) * (size_t)P, s));
     GSLM_CUDA_OK(cudaMemsetAsync(gv.g_off, 0, sizeof(uint32_t), s));
     if (Rc > 0) {
-        k_compact_copy<<<T, 256, 0, s>>>(iv.ranges, iv.cstart, iv.ccount, bt.records_tmp, bv.records, bv.cid, gv.g_cursor);
+        k_compact_copy<<<T, 256, 0, s>>>(iv.ranges, iv.cstart, iv.ccount, bt.records_tmp, bt.masks_tmp, bv.records, bv.masks,
+                                         bv.cid, gv.g_cursor);
         GSLM_CUDA_OK(cudaGetLastError());
     }
     // g_off[1..P] = inclusive scan of the counts (the forward pass's scan scratch is free again)

@@ -1,20 +1,20 @@
 // =============================================================================
 // blend_common.cuh -- building blocks of the tile kernels (a9, a11, a13, fused J^T J v).
 //
-// One CTA = one 16x16 tile (as DGR/cuda_rasterizer/forward.cu:278-402); the primal kernel maps one thread to one
-// pixel, the derivative kernels one thread to a vertical pair of pixels (128 threads per tile).
+// One 16x16 tile per CTA in the primal kernel (one thread per pixel, as DGR/cuda_rasterizer/forward.cu:278-402);
+// one tile per WARP in the derivative kernels (one thread = 8 pixels of one image column, blend_sweeps.cuh).
 // What is different from the reference:
-//  * a tile's instances are contiguous 48-byte records (binning.cu), staged 256 at a time
-//    by ONE cp.async.bulk (TMA bulk copy, SASS UBLKCP) per batch into a 2-stage shared-memory
-//    ring guarded by mbarriers -- no per-thread gathers, colour / depth never fetched from
-//    global per hit (forward.cu:377,380);
-//  * alpha is evaluated by ONE rounding-exact instruction sequence (alpha_column / alpha_pixel)
-//    shared by the primal, tangent and adjoint sweeps, so all three agree on every hit / skip
-//    decision whatever the surrounding code's FMA contraction or pixel-to-thread mapping;
-//  * the adjoint sweep pre-reduces its ten partials with a 12-shuffle recursive-halving
-//    warp reduction, merges warps in shared memory and writes ONE record per
-//    (tile, Gaussian) instance -- no global atomics (the reference does ten atomicAdd per
-//    (pixel, Gaussian) hit, backward.cu:593-635).
+//  * a tile's compact instances are contiguous 48-byte records + 32-byte hit masks (binning.cu), staged 32 at a
+//    time by cp.async.bulk (TMA bulk copy, SASS UBLKCP) into a 2-stage shared-memory ring guarded by
+//    mbarriers -- no per-thread gathers, colour / depth never fetched from global per hit (forward.cu:377,380);
+//  * the primal kernel evaluates alpha with the reference's own rounding sequence (alpha_column / alpha_pixel:
+//    the image is a discontinuous function of alpha at the thresholds) and records, per compact instance, the
+//    256-bit mask of the pixels that blended it; the derivative sweeps take every hit / skip / termination
+//    decision from that mask, so they agree with the primal pass by construction and are free to evaluate
+//    alpha with contracted, packed (FFMA2) arithmetic;
+//  * the adjoint sweep pre-reduces its ten partials with a 12-shuffle recursive-halving warp reduction and
+//    writes ONE record per (tile, Gaussian) instance -- no atomics at all (the reference does ten atomicAdd
+//    per (pixel, Gaussian) hit, backward.cu:593-635).
 // =============================================================================
 #pragma once
 #include "gslm_common.cuh"
@@ -63,29 +63,43 @@ template <int N> __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-constexpr int DBATCH = 128;   // instances per staged batch in the derivative kernels (6 KB of records)
+constexpr int WBATCH = 32;    // compact instances per staged batch in the derivative kernels (one per lane)
+constexpr int MSK_U4 = 2;     // hit mask of one compact instance = 8 x u32 = 2 x uint4 (bit l of word k: see blend_sweeps.cuh)
 
-// Two-stage ring of record batches for one tile. All threads keep an identical copy of the
-// phase bits; thread 0 issues.
-struct RecordRing {
-    float4* buf;       // [2][DBATCH * REC_F4]
-    uint64_t* bar;     // [2]
-    const float4* src; // records of this tile (global)
-    int total;         // instances in the tile's range
-    uint32_t phase;    // bit s = parity of the next completion of stage s
+// Two-stage ring of (records, hit masks) batches for ONE WARP = one tile.  All lanes keep an identical copy
+// of the phase bits; lane 0 issues the two bulk copies of a batch on one mbarrier.
+struct WarpRing {
+    float4* rec;        // [2][WBATCH * REC_F4]
+    uint4* msk;         // [2][WBATCH * MSK_U4]
+    uint64_t* bar;      // [2]
+    const float4* src_rec;   // records of this tile (global)
+    const uint4* src_msk;    // masks of this tile (global)
+    int total;          // compact instances of the tile
+    uint32_t phase;     // bit s = parity of the next completion of stage s
 
-    __device__ __forceinline__ float4* stage(int s) const { return buf + s * (DBATCH * REC_F4); }
-    __device__ __forceinline__ int batch_size(int b) const { return min(DBATCH, total - b * DBATCH); }
-    __device__ __forceinline__ void issue(int b, int s) const {   // one thread
-        uint32_t bytes = (uint32_t)batch_size(b) * (REC_F4 * 16);
-        mbar_arrive_expect_tx(&bar[s], bytes);
-        bulk_g2s(stage(s), src + (size_t)b * DBATCH * REC_F4, bytes, &bar[s]);
+    __device__ __forceinline__ float4* rec_stage(int s) const { return rec + s * (WBATCH * REC_F4); }
+    __device__ __forceinline__ uint4* msk_stage(int s) const { return msk + s * (WBATCH * MSK_U4); }
+    __device__ __forceinline__ int batch_size(int b) const { return min(WBATCH, total - b * WBATCH); }
+    __device__ __forceinline__ void issue(int b, int s) const {   // one lane
+        const uint32_t n = (uint32_t)batch_size(b);
+        mbar_arrive_expect_tx(&bar[s], n * (REC_F4 * 16 + MSK_U4 * 16));
+        bulk_g2s(rec_stage(s), src_rec + (size_t)b * WBATCH * REC_F4, n * (REC_F4 * 16), &bar[s]);
+        bulk_g2s(msk_stage(s), src_msk + (size_t)b * WBATCH * MSK_U4, n * (MSK_U4 * 16), &bar[s]);
     }
     __device__ __forceinline__ void wait(int s) {
         mbar_wait(&bar[s], (phase >> s) & 1u);
         phase ^= (1u << s);
     }
 };
+
+// ---- packed fp32 pairs (sm_100a FFMA2 / FMUL2 / FADD2: one issue slot for two lanes' worth of FP32 work;
+//      measured on B200 with tools/ffma2_bench.cu: same FLOP peak as scalar FFMA, half the issue slots) ----
+typedef float2 f2;
+__device__ __forceinline__ f2 splat(float a) { return make_float2(a, a); }
+__device__ __forceinline__ f2 neg2(f2 a) { return make_float2(-a.x, -a.y); }
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ f2 add2(f2 a, f2 b) { return __fadd2_rn(a, b); }
 
 __device__ __forceinline__ float ex2_approx(float x) {
     float y;

@@ -11,9 +11,11 @@
 // loads of batch b+1 are in flight while batch b is blended.  The early exit means only
 // ~10 % of the sorted list is ever fetched, which is why the records are NOT pre-gathered.
 //
-// New: every instance that at least one pixel blended is flagged; per batch the flagged
-// records are written, densely and in order, to the tile's slice of a scratch array, and
-// every pixel's n_contrib is also kept in that compact numbering.  binning.cu turns the
+// New: for every instance the 256-bit mask of the pixels that blended it is collected (one
+// ballot per warp); per batch the records with a non-empty mask are written, densely and in
+// order, with their masks, to the tile's slice of a scratch array, and every pixel's
+// n_contrib is also kept in that compact numbering.  The masks carry every hit / skip /
+// termination decision of this pass to the derivative sweeps (blend_sweeps.cuh).  binning.cu turns the
 // slices into the dense compact cache that all derivative kernels run on.
 // Writes final_T, n_contrib (ImageState, rasterizer.h), n_contrib_c, ccount.
 // =============================================================================
@@ -35,13 +37,14 @@ struct FwdArgs {
     uint32_t* n_contrib_c;
     uint32_t* ccount;
     float4* records_tmp;
+    uint4* masks_tmp;
     float* out_color;
     float* out_invdepth;
 };
 
 __global__ void __launch_bounds__(TILE_PIX) k_blend_fwd(FwdArgs a) {
     __shared__ __align__(16) float4 s_rec[2][BATCH * REC_F4];
-    __shared__ uint32_t s_flag[BATCH];
+    __shared__ __align__(16) uint32_t s_mask[BATCH][8];   // word w of instance j = ballot of warp w: which of its 32 pixels blended j
     __shared__ uint32_t s_pref[BATCH];     // exclusive prefix of s_flag inside each warp's 32-instance group
     __shared__ uint32_t s_wsum[TILE_PIX / 32];
 
@@ -87,7 +90,8 @@ __global__ void __launch_bounds__(TILE_PIX) k_blend_fwd(FwdArgs a) {
             rec[REC_F4 * tid + 1] = r1;
             rec[REC_F4 * tid + 2] = r2;
         }
-        s_flag[tid] = 0;
+        *reinterpret_cast<uint4*>(&s_mask[tid][0]) = make_uint4(0u, 0u, 0u, 0u);
+        *reinterpret_cast<uint4*>(&s_mask[tid][4]) = make_uint4(0u, 0u, 0u, 0u);
         if (b + 1 < rounds) fetch(b + 1);   // in flight during the blend loop below
         __syncthreads();
         const int n = min(BATCH, total - b * BATCH);
@@ -117,11 +121,13 @@ __global__ void __launch_bounds__(TILE_PIX) k_blend_fwd(FwdArgs a) {
                     }
                 }
             }
-            if (__any_sync(0xffffffffu, blended) && lane == 0) s_flag[j] = 1;   // benign race: every writer stores 1
+            const uint32_t bal = __ballot_sync(0xffffffffu, blended);
+            if (bal != 0u && lane == 0) s_mask[j][warp] = bal;
         }
         __syncthreads();
         // block-wide exclusive prefix over the 256 flags
-        const uint32_t f = s_flag[tid];
+        const uint4 mk0 = *reinterpret_cast<const uint4*>(&s_mask[tid][0]), mk1 = *reinterpret_cast<const uint4*>(&s_mask[tid][4]);
+        const uint32_t f = mk0.x | mk0.y | mk0.z | mk0.w | mk1.x | mk1.y | mk1.z | mk1.w;
         const uint32_t bal = __ballot_sync(0xffffffffu, f != 0);
         s_pref[tid] = __popc(bal & ((1u << lane) - 1u));
         if (lane == 0) s_wsum[warp] = __popc(bal);
@@ -131,10 +137,13 @@ __global__ void __launch_bounds__(TILE_PIX) k_blend_fwd(FwdArgs a) {
 #pragma unroll
         for (int w = 0; w < TILE_PIX / 32; w++) woff[w + 1] = woff[w] + s_wsum[w];
         if (f) {
-            float4* dst = a.records_tmp + ((size_t)range.x + run + woff[warp] + s_pref[tid]) * REC_F4;
+            const size_t pos = (size_t)range.x + run + woff[warp] + s_pref[tid];
+            float4* dst = a.records_tmp + pos * REC_F4;
             dst[0] = rec[REC_F4 * tid];
             dst[1] = rec[REC_F4 * tid + 1];
             dst[2] = rec[REC_F4 * tid + 2];
+            a.masks_tmp[2 * pos] = mk0;
+            a.masks_tmp[2 * pos + 1] = mk1;
         }
         if (last_j >= 0) last_c = run + woff[last_j >> 5] + s_pref[last_j] + 1;   // the pixel's own last hit is flagged
         run += woff[TILE_PIX / 32];
@@ -160,7 +169,7 @@ int launch_blend_fwd(const GeomView& gv, const BinningTemp& bt, const ImageView&
     FwdArgs a;
     a.ranges = iv.ranges; a.point_list = bt.point_list; a.xy = gv.means2D; a.conic_opacity = gv.conic_opacity;
     a.features = features; a.depths = gv.depths; a.W = W; a.H = H; a.bg = bg; a.final_T = iv.final_T;
-    a.n_contrib = iv.n_contrib; a.n_contrib_c = iv.n_contrib_c; a.ccount = iv.ccount; a.records_tmp = bt.records_tmp;
+    a.n_contrib = iv.n_contrib; a.n_contrib_c = iv.n_contrib_c; a.ccount = iv.ccount; a.records_tmp = bt.records_tmp; a.masks_tmp = bt.masks_tmp;
     a.out_color = out_color; a.out_invdepth = out_invdepth;
     StageScope ts(ST_BLEND_FWD, s);
     k_blend_fwd<<<tiles, TILE_PIX, 0, s>>>(a);

@@ -4,200 +4,217 @@
 //   k_blend_bwd   J^T u   per-instance gradient partials from dL/dimage (a13)
 //   k_blend_jtjv  J^T W J v fused: tangent sweep, per-pixel weighting in registers, adjoint
 //                 sweep -- the image-space vector J v never reaches HBM   
-// The sweeps themselves live in blend_sweeps.cuh.  One CTA of 128 threads per 16x16 tile,
-// one thread per vertical pixel pair.
+// The sweeps themselves live in blend_sweeps.cuh.  One WARP per 16x16 tile, one thread per
+// eight pixels of a column; DWARPS independent warps (tiles) per CTA, each with its own slice
+// of shared memory -- warps never synchronise with each other.
 // =============================================================================
 #include "blend_sweeps.cuh"
 
 namespace gslm {
 
-constexpr int REC_STAGE_F4 = 2 * DBATCH * REC_F4;                 // float4 per record ring
-constexpr size_t SMEM_RING = REC_STAGE_F4 * sizeof(float4);       // 12 KB
-constexpr size_t SMEM_ACC = DBATCH * ACC_STRIDE * sizeof(float);  // 5.5 KB
+constexpr int DWARPS = 4;                               // tiles per CTA
+constexpr int DTHREADS = DWARPS * 32;
+constexpr int RING_F4 = 2 * WBATCH * REC_F4;            // float4 per warp: record ring (3 KB)
+constexpr int RING_U4 = 2 * WBATCH * MSK_U4;            // uint4 per warp: mask ring (2 KB)
 
-__device__ __forceinline__ TileCtx make_ctx(const uint32_t* __restrict__ cstart, int W, int H) {
-    TileCtx c;
-    c.tid = threadIdx.x; c.lane = c.tid & 31; c.warp = c.tid >> 5;
-    const int gx = (W + TILE_X - 1) / TILE_X;
-    const int tile = blockIdx.x;
-    c.px = (tile % gx) * TILE_X + (c.tid & (TILE_X - 1));
-    c.py0 = (tile / gx) * TILE_Y + 2 * (c.tid >> 4);
-    c.in0 = c.px < W && c.py0 < H;
-    c.in1 = c.px < W && c.py0 + 1 < H;
-    c.pxf = (float)c.px; c.pyf0 = (float)c.py0; c.pyf1 = (float)(c.py0 + 1);
-    c.range = make_uint2(cstart[tile], cstart[tile + 1]);
+struct TileArgs {          // one linearised view
+    const uint32_t* cstart;
+    const float4* records;
+    const uint4* masks;
+    const uint32_t* cid;
+    const float* final_T;
+    int W, H, tiles;
+    const float* bg;
+};
+
+__device__ __forceinline__ bool make_tile(const TileArgs& a, int warp, WTile& c) {
+    c.lane = threadIdx.x & 31;
+    c.lbit = 1u << c.lane;
+    const int tile = blockIdx.x * DWARPS + warp;
+    if (tile >= a.tiles) return false;
+    const int gx = (a.W + TILE_X - 1) / TILE_X;
+    c.W = a.W; c.H = a.H;
+    c.px = (tile % gx) * TILE_X + (c.lane & 15);
+    c.pyb = (tile / gx) * TILE_Y + (c.lane >> 4);
+    c.pxf = (float)c.px; c.pyf = (float)c.pyb;
+    c.range = make_uint2(a.cstart[tile], a.cstart[tile + 1]);
     c.total = (int)(c.range.y - c.range.x);
-    return c;
+    return true;
 }
 
-__device__ __forceinline__ void init_ring(RecordRing& ring, const TileCtx& c, float4* s_rec, uint64_t* s_bar,
-                                          const float4* __restrict__ records) {
-    ring.buf = s_rec; ring.bar = s_bar; ring.src = records + (size_t)c.range.x * REC_F4;
+__device__ __forceinline__ void init_ring(WarpRing& ring, const WTile& c, const TileArgs& a, float4* s_rec, uint4* s_msk,
+                                          uint64_t* s_bar) {
+    ring.rec = s_rec; ring.msk = s_msk; ring.bar = s_bar;
+    ring.src_rec = a.records + (size_t)c.range.x * REC_F4;
+    ring.src_msk = a.masks + (size_t)c.range.x * MSK_U4;
     ring.total = c.total; ring.phase = 0;
-    if (c.tid == 0) {
+    if (c.lane == 0) {
         mbar_init(&s_bar[0], 1);
         mbar_init(&s_bar[1], 1);
         mbar_fence_init();
     }
-    __syncthreads();
+    __syncwarp();
 }
 
 template <bool WITH_D>
-__global__ void __launch_bounds__(PAIR_THREADS)
-k_blend_jvp(const uint32_t* __restrict__ cstart, const float4* __restrict__ records, const uint32_t* __restrict__ cid,
-            const uint32_t* __restrict__ n_contrib_c, const float4* __restrict__ tgeom, int W, int H,
-            const float* __restrict__ bg, const float* __restrict__ bg_t, float* __restrict__ out_color_t,
-            float* __restrict__ out_invdepth_t) {
-    __shared__ __align__(128) float4 s_rec[REC_STAGE_F4];
-    __shared__ __align__(16) float4 s_tan[REC_STAGE_F4];
-    __shared__ __align__(8) uint64_t s_bar[2];
-    const TileCtx c = make_ctx(cstart, W, H);
-    RecordRing ring;
-    init_ring(ring, c, s_rec, s_bar, records);
-    const size_t pix0 = (size_t)c.py0 * W + c.px, pix1 = pix0 + W, HW = (size_t)H * W;
-    const uint32_t contrib0 = c.in0 ? n_contrib_c[pix0] : 0u, contrib1 = c.in1 ? n_contrib_c[pix1] : 0u;
-    PixTangent t0, t1;
-    tangent_sweep<WITH_D>(c, ring, s_tan, cid, tgeom, contrib0, contrib1, t0, t1);
+__global__ void __launch_bounds__(DTHREADS)
+k_blend_jvp(TileArgs a, const float4* __restrict__ tgeom, const float* __restrict__ bg_t,
+            float* __restrict__ out_color_t, float* __restrict__ out_invdepth_t) {
+    __shared__ __align__(128) float4 s_rec[DWARPS][RING_F4];
+    __shared__ __align__(128) uint4 s_msk[DWARPS][RING_U4];
+    __shared__ __align__(16) float4 s_tan[DWARPS][RING_F4];
+    __shared__ __align__(8) uint64_t s_bar[DWARPS][2];
+    const int warp = threadIdx.x >> 5;
+    WTile c;
+    if (!make_tile(a, warp, c)) return;
+    WarpRing ring;
+    init_ring(ring, c, a, s_rec[warp], s_msk[warp], s_bar[warp]);
+    PairT st[4];
+    tangent_sweep<WITH_D>(c, ring, s_tan[warp], a.cid, tgeom, st);
+    const size_t HW = (size_t)a.H * a.W;
+    const float b0 = a.bg[0], b1 = a.bg[1], b2 = a.bg[2];
+    const float bt0 = bg_t ? bg_t[0] : 0.f, bt1 = bg_t ? bg_t[1] : 0.f, bt2 = bg_t ? bg_t[2] : 0.f;
 #pragma unroll
-    for (int ch = 0; ch < 3; ch++) {   // forward_impl.h:531: C + T * bg on duals
-        const float b = bg[ch], bt = bg_t ? bg_t[ch] : 0.f;
-        if (c.in0) out_color_t[ch * HW + pix0] = t0.Ct[ch] + t0.Tt * b + t0.T * bt;
-        if (c.in1) out_color_t[ch * HW + pix1] = t1.Ct[ch] + t1.Tt * b + t1.T * bt;
-    }
-    if (WITH_D) {
-        if (c.in0) out_invdepth_t[pix0] = t0.Dt;
-        if (c.in1) out_invdepth_t[pix1] = t1.Dt;
+    for (int k = 0; k < 8; k++) {   // forward_impl.h:531: C + T * bg on duals
+        if (!c.inside(k)) continue;
+        const PairT& s = st[k >> 1];
+        const bool hi = k & 1;
+        const float T = hi ? s.T.y : s.T.x, Tt = hi ? s.Tt.y : s.Tt.x;
+        const size_t pix = c.pix(k);
+        out_color_t[pix] = (hi ? s.C0.y : s.C0.x) + Tt * b0 + T * bt0;
+        out_color_t[HW + pix] = (hi ? s.C1.y : s.C1.x) + Tt * b1 + T * bt1;
+        out_color_t[2 * HW + pix] = (hi ? s.C2.y : s.C2.x) + Tt * b2 + T * bt2;
+        if (WITH_D) out_invdepth_t[pix] = hi ? s.D.y : s.D.x;
     }
 }
 
-__device__ __forceinline__ void load_cotangent(PixAdjoint& p, bool inside, size_t pix, size_t HW,
-                                               const float* __restrict__ final_T, const float* __restrict__ dL_dcolor,
-                                               const float* __restrict__ dL_dinvdepth) {
-    p.T = inside ? final_T[pix] : 0.f;
-    p.S = 0.f;
-#pragma unroll
-    for (int ch = 0; ch < 3; ch++) p.g[ch] = inside ? dL_dcolor[ch * HW + pix] : 0.f;
-    p.gd = (inside && dL_dinvdepth) ? dL_dinvdepth[pix] : 0.f;
-}
+__device__ __forceinline__ void set_lane(f2& v, bool hi, float x) { if (hi) v.y = x; else v.x = x; }
 
 template <bool WITH_D>
-__global__ void __launch_bounds__(PAIR_THREADS)
-k_blend_bwd(const uint32_t* __restrict__ cstart, const float4* __restrict__ records,
-            const uint32_t* __restrict__ n_contrib_c, const float* __restrict__ final_T, int W, int H,
-            const float* __restrict__ bg, const float* __restrict__ dL_dcolor,
-            const float* __restrict__ dL_dinvdepth, float4* __restrict__ inst_grads) {
-    __shared__ __align__(128) float4 s_rec[REC_STAGE_F4];
-    __shared__ float s_acc[DBATCH * ACC_STRIDE];
-    __shared__ __align__(8) uint64_t s_bar[2];
-    const TileCtx c = make_ctx(cstart, W, H);
-    for (int i = c.tid; i < DBATCH * ACC_STRIDE; i += PAIR_THREADS) s_acc[i] = 0.f;
-    RecordRing ring;
-    init_ring(ring, c, s_rec, s_bar, records);
-    const size_t pix0 = (size_t)c.py0 * W + c.px, pix1 = pix0 + W, HW = (size_t)H * W;
-    const uint32_t contrib0 = c.in0 ? n_contrib_c[pix0] : 0u, contrib1 = c.in1 ? n_contrib_c[pix1] : 0u;
-    PixAdjoint p0, p1;
-    load_cotangent(p0, c.in0, pix0, HW, final_T, dL_dcolor, dL_dinvdepth);
-    load_cotangent(p1, c.in1, pix1, HW, final_T, dL_dcolor, dL_dinvdepth);
-    const float bgv[3] = {bg[0], bg[1], bg[2]};
-    adjoint_sweep<WITH_D>(c, ring, s_acc, W, H, bgv, p0, p1, contrib0, contrib1, inst_grads);
+__global__ void __launch_bounds__(DTHREADS)
+k_blend_bwd(TileArgs a, const float* __restrict__ dL_dcolor, const float* __restrict__ dL_dinvdepth,
+            float4* __restrict__ inst_grads) {
+    __shared__ __align__(128) float4 s_rec[DWARPS][RING_F4];
+    __shared__ __align__(128) uint4 s_msk[DWARPS][RING_U4];
+    __shared__ float s_acc[DWARPS][WBATCH * ACC_STRIDE];
+    __shared__ __align__(8) uint64_t s_bar[DWARPS][2];
+    const int warp = threadIdx.x >> 5;
+    WTile c;
+    if (!make_tile(a, warp, c)) return;
+    WarpRing ring;
+    init_ring(ring, c, a, s_rec[warp], s_msk[warp], s_bar[warp]);
+    const size_t HW = (size_t)a.H * a.W;
+    PairA sa[4];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        PairA& s = sa[k >> 1];
+        const bool hi = k & 1, in = c.inside(k);
+        const size_t pix = in ? c.pix(k) : 0;
+        set_lane(s.T, hi, in ? a.final_T[pix] : 0.f);
+        set_lane(s.g0, hi, in ? dL_dcolor[pix] : 0.f);
+        set_lane(s.g1, hi, in ? dL_dcolor[HW + pix] : 0.f);
+        set_lane(s.g2, hi, in ? dL_dcolor[2 * HW + pix] : 0.f);
+        set_lane(s.gd, hi, (in && WITH_D) ? dL_dinvdepth[pix] : 0.f);
+    }
+    const float bgv[3] = {a.bg[0], a.bg[1], a.bg[2]};
+    adjoint_sweep<WITH_D>(c, ring, s_acc[warp], bgv, sa, inst_grads);
 }
 
-__device__ __forceinline__ float weigh(PixAdjoint& p, const PixTangent& t, bool inside, size_t pix, size_t HW,
-                                       const float* __restrict__ final_T, const float* __restrict__ weight,
-                                       const float bg[3]) {
-    p.T = inside ? final_T[pix] : 0.f;
-    p.S = 0.f;
-    p.gd = 0.f;
+__global__ void __launch_bounds__(DTHREADS)
+k_blend_jtjv(TileArgs a, const float4* __restrict__ tgeom, const float* __restrict__ weight,
+             float4* __restrict__ inst_grads, float* __restrict__ out_vJJv) {
+    __shared__ __align__(128) float4 s_rec[DWARPS][RING_F4];
+    __shared__ __align__(128) uint4 s_msk[DWARPS][RING_U4];
+    __shared__ __align__(16) float4 s_tan[DWARPS][RING_F4];
+    __shared__ float s_acc[DWARPS][WBATCH * ACC_STRIDE];
+    __shared__ __align__(8) uint64_t s_bar[DWARPS][2];
+    const int warp = threadIdx.x >> 5;
+    WTile c;
+    if (!make_tile(a, warp, c)) return;
+    if (c.total == 0) return;   // nothing blended in this tile: J v = 0 there and no instance to write
+    WarpRing ring;
+    init_ring(ring, c, a, s_rec[warp], s_msk[warp], s_bar[warp]);
+    const size_t HW = (size_t)a.H * a.W;
+    const float bgv[3] = {a.bg[0], a.bg[1], a.bg[2]};
+
+    // pass 1: J v for the eight pixels, kept in registers
+    PairT st[4];
+    tangent_sweep<false>(c, ring, s_tan[warp], a.cid, tgeom, st);
+    // u = W J v (cotangent) and the quadratic form v^T J^T W J v
+    PairA sa[4];
     float quad = 0.f;
 #pragma unroll
-    for (int ch = 0; ch < 3; ch++) {
-        const float jv = t.Ct[ch] + t.Tt * bg[ch];
-        const float w = inside ? (weight ? weight[ch * HW + pix] : 1.f) : 0.f;
-        p.g[ch] = w * jv;          // cotangent u = W J v
-        quad += p.g[ch] * jv;      // v^T J^T W J v
+    for (int k = 0; k < 8; k++) {
+        const PairT& s = st[k >> 1];
+        PairA& d = sa[k >> 1];
+        const bool hi = k & 1, in = c.inside(k);
+        const size_t pix = in ? c.pix(k) : 0;
+        const float Tt = hi ? s.Tt.y : s.Tt.x;
+        const float jv0 = (hi ? s.C0.y : s.C0.x) + Tt * bgv[0];
+        const float jv1 = (hi ? s.C1.y : s.C1.x) + Tt * bgv[1];
+        const float jv2 = (hi ? s.C2.y : s.C2.x) + Tt * bgv[2];
+        const float w0 = in ? (weight ? weight[pix] : 1.f) : 0.f;
+        const float w1 = in ? (weight ? weight[HW + pix] : 1.f) : 0.f;
+        const float w2 = in ? (weight ? weight[2 * HW + pix] : 1.f) : 0.f;
+        const float g0 = w0 * jv0, g1 = w1 * jv1, g2 = w2 * jv2;
+        quad += g0 * jv0 + g1 * jv1 + g2 * jv2;
+        set_lane(d.T, hi, in ? a.final_T[pix] : 0.f);
+        set_lane(d.g0, hi, g0);
+        set_lane(d.g1, hi, g1);
+        set_lane(d.g2, hi, g2);
+        set_lane(d.gd, hi, 0.f);
     }
-    return quad;
-}
-
-__global__ void __launch_bounds__(PAIR_THREADS)
-k_blend_jtjv(const uint32_t* __restrict__ cstart, const float4* __restrict__ records, const uint32_t* __restrict__ cid,
-             const uint32_t* __restrict__ n_contrib_c, const float* __restrict__ final_T,
-             const float4* __restrict__ tgeom, int W, int H, const float* __restrict__ bg,
-             const float* __restrict__ weight, float4* __restrict__ inst_grads, float* __restrict__ out_vJJv) {
-    __shared__ __align__(128) float4 s_rec[REC_STAGE_F4];
-    __shared__ __align__(16) float4 s_tan[REC_STAGE_F4];
-    __shared__ float s_acc[DBATCH * ACC_STRIDE];
-    __shared__ __align__(8) uint64_t s_bar[2];
-    __shared__ float s_sum[PAIR_THREADS / 32];
-    const TileCtx c = make_ctx(cstart, W, H);
-    for (int i = c.tid; i < DBATCH * ACC_STRIDE; i += PAIR_THREADS) s_acc[i] = 0.f;
-    RecordRing ring;
-    init_ring(ring, c, s_rec, s_bar, records);
-    const size_t pix0 = (size_t)c.py0 * W + c.px, pix1 = pix0 + W, HW = (size_t)H * W;
-    const uint32_t contrib0 = c.in0 ? n_contrib_c[pix0] : 0u, contrib1 = c.in1 ? n_contrib_c[pix1] : 0u;
-    const float bgv[3] = {bg[0], bg[1], bg[2]};
-
-    // pass 1: J v for the two pixels, kept in registers
-    PixTangent t0, t1;
-    tangent_sweep<false>(c, ring, s_tan, cid, tgeom, contrib0, contrib1, t0, t1);
-    PixAdjoint p0, p1;
-    float quad = weigh(p0, t0, c.in0, pix0, HW, final_T, weight, bgv) + weigh(p1, t1, c.in1, pix1, HW, final_T, weight, bgv);
     // pass 2: J^T u
-    adjoint_sweep<false>(c, ring, s_acc, W, H, bgv, p0, p1, contrib0, contrib1, inst_grads);
+    adjoint_sweep<false>(c, ring, s_acc[warp], bgv, sa, inst_grads);
 
     if (out_vJJv) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) quad += __shfl_xor_sync(0xffffffffu, quad, o);
-        if (c.lane == 0) s_sum[c.warp] = quad;
-        __syncthreads();
-        if (c.tid == 0) {
-            float s = 0.f;
-#pragma unroll
-            for (int i = 0; i < PAIR_THREADS / 32; i++) s += s_sum[i];
-            atomicAdd(out_vJJv, s);
-        }
+        if (c.lane == 0) atomicAdd(out_vJJv, quad);
     }
 }
 
 static int tiles_of(int W, int H) { return ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y); }
+static TileArgs tile_args(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg) {
+    TileArgs a;
+    a.cstart = iv.cstart; a.records = bv.records; a.masks = bv.masks; a.cid = bv.cid; a.final_T = iv.final_T;
+    a.W = W; a.H = H; a.tiles = tiles_of(W, H); a.bg = bg;
+    return a;
+}
+static int grid_of(int tiles) { return (tiles + DWARPS - 1) / DWARPS; }
 
 int launch_blend_jvp(const BinningView& bv, const ImageView& iv, int W, int H, const float4* tgeom, const float* bg,
                      const float* bg_tangent, float* out_color_t, float* out_invdepth_t, cudaStream_t s) {
-    const int tiles = tiles_of(W, H);
-    if (tiles == 0) return 0;
+    const TileArgs a = tile_args(bv, iv, W, H, bg);
+    if (a.tiles == 0) return 0;
     StageScope ts(ST_BLEND_JVP, s);
     if (out_invdepth_t)
-        k_blend_jvp<true><<<tiles, PAIR_THREADS, 0, s>>>(iv.cstart, bv.records, bv.cid, iv.n_contrib_c, tgeom, W, H, bg,
-                                                        bg_tangent, out_color_t, out_invdepth_t);
+        k_blend_jvp<true><<<grid_of(a.tiles), DTHREADS, 0, s>>>(a, tgeom, bg_tangent, out_color_t, out_invdepth_t);
     else
-        k_blend_jvp<false><<<tiles, PAIR_THREADS, 0, s>>>(iv.cstart, bv.records, bv.cid, iv.n_contrib_c, tgeom, W, H, bg,
-                                                         bg_tangent, out_color_t, out_invdepth_t);
+        k_blend_jvp<false><<<grid_of(a.tiles), DTHREADS, 0, s>>>(a, tgeom, bg_tangent, out_color_t, out_invdepth_t);
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
 }
 
 int launch_blend_bwd(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg,
                      const float* dL_dcolor, const float* dL_dinvdepth, float4* inst_grads, cudaStream_t s) {
-    const int tiles = tiles_of(W, H);
-    if (tiles == 0) return 0;
+    const TileArgs a = tile_args(bv, iv, W, H, bg);
+    if (a.tiles == 0) return 0;
     StageScope ts(ST_BLEND_BWD, s);
     if (dL_dinvdepth)
-        k_blend_bwd<true><<<tiles, PAIR_THREADS, 0, s>>>(iv.cstart, bv.records, iv.n_contrib_c, iv.final_T, W, H, bg,
-                                                        dL_dcolor, dL_dinvdepth, inst_grads);
+        k_blend_bwd<true><<<grid_of(a.tiles), DTHREADS, 0, s>>>(a, dL_dcolor, dL_dinvdepth, inst_grads);
     else
-        k_blend_bwd<false><<<tiles, PAIR_THREADS, 0, s>>>(iv.cstart, bv.records, iv.n_contrib_c, iv.final_T, W, H, bg,
-                                                         dL_dcolor, dL_dinvdepth, inst_grads);
+        k_blend_bwd<false><<<grid_of(a.tiles), DTHREADS, 0, s>>>(a, dL_dcolor, dL_dinvdepth, inst_grads);
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
 }
 
 int launch_blend_jtjv(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg,
                       const float4* tgeom, const float* weight, float4* inst_grads, float* out_vJJv, cudaStream_t s) {
-    const int tiles = tiles_of(W, H);
-    if (tiles == 0) return 0;
+    const TileArgs a = tile_args(bv, iv, W, H, bg);
+    if (a.tiles == 0) return 0;
     StageScope ts(ST_BLEND_JTJV, s);
-    k_blend_jtjv<<<tiles, PAIR_THREADS, 0, s>>>(iv.cstart, bv.records, bv.cid, iv.n_contrib_c, iv.final_T, tgeom, W, H,
-                                               bg, weight, inst_grads, out_vJJv);
+    k_blend_jtjv<<<grid_of(a.tiles), DTHREADS, 0, s>>>(a, tgeom, weight, inst_grads, out_vJJv);
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
 }

@@ -7,18 +7,28 @@
 // alpha has zero tangent (helper_math.h:70-80).
 // Adjoint sweep: DGR/cuda_rasterizer/backward.cu:452-638 (bwd renderCUDA), including its
 // quirk that the 0.99 clamp is NOT masked in the gradient (backward.cu:569).
-// Both sweeps run on the COMPACT per-tile lists (only instances some pixel blended) and use the
-// cached n_contrib_c / final_T of the primal pass, so they never test for termination: a hit at
-// a compact position < n_contrib_c was blended by construction.
 //
-// Mapping: 128 threads per 16x16 tile, one thread = the vertical pixel pair (x, 2r), (x, 2r+1);
-// record loads, the column part of the alpha evaluation, loop control and -- in the adjoint --
-// the warp reduction are paid once per pair instead of once per pixel.
+// Both sweeps run on the COMPACT per-tile lists (only instances some pixel blended).  Every
+// per-(pixel, instance) decision of the primal pass -- power > 0, alpha < 1/255, "this pixel
+// has already terminated" -- is read from the instance's 256-bit hit mask written by
+// k_blend_fwd, so the sweeps contain no data-dependent branch and no threshold test.
+//
+// Mapping: ONE WARP per 16x16 tile.  Lane l owns image column (l & 15) and the eight rows
+// 2k + (l >> 4), k = 0..7, i.e. exactly the pixels whose hit bit is bit l of mask word k
+// (k_blend_fwd's warp k covers rows 2k, 2k+1 with lane = (row & 1) * 16 + column).  The eight
+// pixels are processed as four float2 pairs (rows 4p + h, 4p + 2 + h) with packed FFMA2 /
+// FMUL2 / FADD2, so one issue slot does the work of two pixels; record loads, the column part
+// of the exponent, loop control and -- in the adjoint -- the warp reduction are paid once per
+// (tile, instance) instead of once per (warp of 64 pixels, instance).  A warp never waits for
+// another warp: there is no __syncthreads and no shared-memory atomic in these kernels.
 //
 // Algebra (same mathematics as the reference, fewer operations per (pixel, Gaussian) pair):
-//  * tangent of the exponent as a polynomial in (dx, dy) with per-Gaussian coefficients
+//  * the compact record stores the exponent in log2 units with the opacity folded in:
+//      alpha_raw = o exp(power) = exp2(a dx^2 + b dx dy + c dy^2 + log2 o),
+//      (a, b, c) = -log2(e) (A/2, B, C/2);  alpha = min(0.99, alpha_raw) only when o > 0.99;
+//  * tangent: alpha_t = alpha_raw (power_t + o_t / o) with power_t a polynomial in (dx, dy),
 //      power_t = dx (a3 dx + a5 dy + a1) + dy (a4 dy + a2)           (coefficients: preprocess.cu)
-//  * adjoint: with q = G dL/dalpha the six geometric partials are moments of q,
+//  * adjoint: with q = alpha_raw dL/dalpha the six geometric partials are moments of q,
 //      sum q, q dx, q dy, q dx^2, q dx dy, q dy^2,
 //    turned into (dmean2D, dconic, dopacity) ONCE per instance after the reduction; and
 //      dL/dalpha_j = T_j (c_j . g) - (S_j + T_final bg . g) / (1 - alpha_j),  S_j = sum_{k>j} (c_k . g) alpha_k T_k
@@ -29,203 +39,236 @@
 
 namespace gslm {
 
-constexpr int PAIR_THREADS = TILE_PIX / 2;   // 128 threads per tile in the derivative kernels
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr float LN2 = 0.6931471805599453f;
 
-struct TileCtx {
-    int tid, lane, warp;
-    int px, py0;            // pixel column and the first of the two rows
-    bool in0, in1;
-    float pxf, pyf0, pyf1;
+struct WTile {
+    int lane;
+    uint32_t lbit;          // 1 << lane: this lane's bit in every mask word
+    int px, pyb;            // pixel column; row of pixel k is pyb + 2 k
+    float pxf, pyf;
     uint2 range;            // compact range of the tile
     int total;              // compact instances of the tile (every one was blended by some pixel)
+    int W, H;
+    __device__ __forceinline__ bool inside(int k) const { return px < W && pyb + 2 * k < H; }
+    __device__ __forceinline__ size_t pix(int k) const { return (size_t)(pyb + 2 * k) * W + px; }
 };
 
-// Per-thread gather of the tangent records of batch b into shared memory (cp.async, 3 x 16 B per record,
-// two records per thread).
-__device__ __forceinline__ void stage_tangents(const TileCtx& c, int b, const uint32_t* __restrict__ cid,
+// Per-lane gather of the tangent record of instance (b, lane) into shared memory (cp.async, 3 x 16 B).
+__device__ __forceinline__ void stage_tangents(const WTile& c, int b, const uint32_t* __restrict__ cid,
                                                const float4* __restrict__ tgeom, float4* dst) {
-#pragma unroll
-    for (int h = 0; h < DBATCH / PAIR_THREADS; h++) {
-        const int slot = c.tid + h * PAIR_THREADS;
-        const int k = b * DBATCH + slot;
-        if (k < c.total) {
-            const uint32_t id = __ldg(cid + c.range.x + k);
-            const float4* src = tgeom + (size_t)REC_F4 * id;
-            cp_async16(dst + REC_F4 * slot, src);
-            cp_async16(dst + REC_F4 * slot + 1, src + 1);
-            cp_async16(dst + REC_F4 * slot + 2, src + 2);
-        }
+    const int k = b * WBATCH + c.lane;
+    if (k < c.total) {
+        const uint32_t id = __ldg(cid + c.range.x + k);
+        const float4* src = tgeom + (size_t)REC_F4 * id;
+        cp_async16(dst + REC_F4 * c.lane, src);
+        cp_async16(dst + REC_F4 * c.lane + 1, src + 1);
+        cp_async16(dst + REC_F4 * c.lane + 2, src + 2);
     }
     cp_async_commit();
 }
 
-struct PixTangent {
-    float T, Tt;            // transmittance and its tangent at the end of the sweep
-    float Ct[3], Dt;        // tangents of colour (without background) and inverse depth
+// What one lane needs of one instance, shared by both sweeps.
+struct InstCol {
+    float dx, ex, fx, cc, dyb;
+    bool clampable;
 };
-__device__ __forceinline__ void pix_tangent_init(PixTangent& o) {
-    o.T = 1.f; o.Tt = 0.f; o.Ct[0] = o.Ct[1] = o.Ct[2] = 0.f; o.Dt = 0.f;
+__device__ __forceinline__ InstCol inst_column(const WTile& c, const float4& q0, const float4& q1, const float4& q2) {
+    InstCol i;
+    i.dx = q0.x - c.pxf;
+    i.ex = fmaf(q0.z * i.dx, i.dx, q1.y);   // a dx^2 + log2 o
+    i.fx = q0.w * i.dx;                     // b dx
+    i.cc = q1.x;
+    i.dyb = q0.y - c.pyf;
+    i.clampable = q2.w > 0.99f;             // alpha_raw <= o: the 0.99 clamp can only bind when o > 0.99
+    return i;
+}
+__device__ __forceinline__ uint32_t mask_word(const uint4& m0, const uint4& m1, int k) {
+    switch (k) {
+        case 0: return m0.x; case 1: return m0.y; case 2: return m0.z; case 3: return m0.w;
+        case 4: return m1.x; case 5: return m1.y; case 6: return m1.z; default: return m1.w;
+    }
+}
+// alpha_raw of pixel pair p (rows 4p + h, 4p + 2 + h) and its dy; 0 where the primal pass did not blend
+__device__ __forceinline__ f2 pair_alpha(const WTile& c, const InstCol& i, const uint4& m0, const uint4& m1, int p, f2& dy) {
+    dy = add2(splat(i.dyb), make_float2(-4.f * p, -4.f * p - 2.f));
+    const f2 pl = fma2(dy, fma2(splat(i.cc), dy, splat(i.fx)), splat(i.ex));
+    f2 a;
+    a.x = (mask_word(m0, m1, 2 * p) & c.lbit) ? ex2_approx(pl.x) : 0.f;
+    a.y = (mask_word(m0, m1, 2 * p + 1) & c.lbit) ? ex2_approx(pl.y) : 0.f;
+    return a;
 }
 
-template <bool WITH_D>
-__device__ __forceinline__ void tangent_update(PixTangent& o, float dx, float dy, float h, float G, float alpha,
-                                               const float4& q1, const float4& q2, const float4& t0,
-                                               const float4& t1, const float4& t2) {
-    // power_t = dx (a3 dx + a1 + a5 dy) + dy (a4 dy + a2);  h = a3 dx + a1 is shared by the pixel pair
-    const float pw_t = fmaf(dy, fmaf(t0.w, dy, t0.y), dx * fmaf(t1.x, dy, h));
-    // alpha = min(0.99, o G): the constant branch carries no tangent
-    const float alpha_t = alpha < 0.99f ? G * fmaf(q1.y, pw_t, t1.y) : 0.f;
-    const float aT = alpha * o.T;
-    const float aT_t = fmaf(alpha_t, o.T, alpha * o.Tt);
-    o.Ct[0] += fmaf(t1.z, aT, q1.z * aT_t);
-    o.Ct[1] += fmaf(t1.w, aT, q1.w * aT_t);
-    o.Ct[2] += fmaf(t2.x, aT, q2.x * aT_t);
-    if (WITH_D) o.Dt += fmaf(t2.y, aT, q2.y * aT_t);
-    const float om = 1.f - alpha;
-    o.Tt = fmaf(o.Tt, om, -o.T * alpha_t);
-    o.T *= om;
+// ---------------------------------------------------------------------------------------------
+// tangent sweep
+// ---------------------------------------------------------------------------------------------
+struct PairT {
+    f2 T, Tt;               // transmittance and its tangent
+    f2 C0, C1, C2, D;       // tangents of colour (without background) and inverse depth
+};
+__device__ __forceinline__ void pair_tangent_init(PairT& o) {
+    o.T = splat(1.f);
+    o.Tt = o.C0 = o.C1 = o.C2 = o.D = splat(0.f);
 }
 
-// Front-to-back tangent sweep over the tile's compact list. s_tan: [2][DBATCH*REC_F4] shared memory.
+// Front-to-back tangent sweep over the tile's compact list. s_tan: [2][WBATCH * REC_F4] shared memory.
 template <bool WITH_D>
-__device__ __forceinline__ void tangent_sweep(const TileCtx& c, RecordRing& ring, float4* s_tan,
+__device__ __forceinline__ void tangent_sweep(const WTile& c, WarpRing& ring, float4* s_tan,
                                               const uint32_t* __restrict__ cid, const float4* __restrict__ tgeom,
-                                              uint32_t contrib0, uint32_t contrib1, PixTangent& o0, PixTangent& o1) {
-    pix_tangent_init(o0);
-    pix_tangent_init(o1);
-    const int rounds = (c.total + DBATCH - 1) / DBATCH;
+                                              PairT (&st)[4]) {
+#pragma unroll
+    for (int p = 0; p < 4; p++) pair_tangent_init(st[p]);
+    const int rounds = (c.total + WBATCH - 1) / WBATCH;
     if (rounds == 0) return;
-    if (c.tid == 0) ring.issue(0, 0);
+    if (c.lane == 0) ring.issue(0, 0);
     stage_tangents(c, 0, cid, tgeom, s_tan);
-    const int cmax = (int)max(contrib0, contrib1);
     for (int b = 0; b < rounds; b++) {
-        __syncthreads();   // batch b-1 fully consumed: stage (b+1)&1 is free
+        __syncwarp();   // batch b-1 fully consumed: stage (b+1)&1 is free
         if (b + 1 < rounds) {
-            if (c.tid == 0) ring.issue(b + 1, (b + 1) & 1);
-            stage_tangents(c, b + 1, cid, tgeom, s_tan + ((b + 1) & 1) * (DBATCH * REC_F4));
+            if (c.lane == 0) ring.issue(b + 1, (b + 1) & 1);
+            stage_tangents(c, b + 1, cid, tgeom, s_tan + ((b + 1) & 1) * (WBATCH * REC_F4));
             cp_async_wait<1>();
         } else {
             cp_async_wait<0>();
         }
         ring.wait(b & 1);
-        __syncthreads();   // everybody's cp.async for batch b is visible
-        const float4* rec = ring.stage(b & 1);
-        const float4* tan = s_tan + (b & 1) * (DBATCH * REC_F4);
-        const int n = min(DBATCH, c.total - b * DBATCH);
-        const int mine = min(n, cmax - b * DBATCH);   // a pixel blends compact positions < its n_contrib_c only
-        for (int j = 0; j < mine; j++) {
-            const float4 q0 = rec[REC_F4 * j], q1 = rec[REC_F4 * j + 1];
-            float dx, e, f, dy0, dy1, G0, G1, al0, al1;
-            alpha_column(q0, c.pxf, dx, e, f);
-            const uint32_t pos = (uint32_t)(b * DBATCH + j);
-            const bool hit0 = pos < contrib0 && alpha_pixel(q0, q1, e, f, c.pyf0, dy0, G0, al0);
-            const bool hit1 = pos < contrib1 && alpha_pixel(q0, q1, e, f, c.pyf1, dy1, G1, al1);
-            if (!(hit0 || hit1)) continue;
-            const float4 q2 = rec[REC_F4 * j + 2];
+        __syncwarp();   // every lane's cp.async for batch b is visible
+        const float4* rec = ring.rec_stage(b & 1);
+        const uint4* msk = ring.msk_stage(b & 1);
+        const float4* tan = s_tan + (b & 1) * (WBATCH * REC_F4);
+        const int n = ring.batch_size(b);
+        for (int j = 0; j < n; j++) {
+            const float4 q0 = rec[REC_F4 * j], q1 = rec[REC_F4 * j + 1], q2 = rec[REC_F4 * j + 2];
+            const uint4 m0 = msk[MSK_U4 * j], m1 = msk[MSK_U4 * j + 1];
             const float4 t0 = tan[REC_F4 * j], t1 = tan[REC_F4 * j + 1], t2 = tan[REC_F4 * j + 2];
-            const float h = fmaf(t0.z, dx, t0.x);
-            if (hit0) tangent_update<WITH_D>(o0, dx, dy0, h, G0, al0, q1, q2, t0, t1, t2);
-            if (hit1) tangent_update<WITH_D>(o1, dx, dy1, h, G1, al1, q1, q2, t0, t1, t2);
+            const InstCol i = inst_column(c, q0, q1, q2);
+            // power_t + o_t / o = dy (a4 dy + kx) + hx
+            const float hx = fmaf(fmaf(t0.z, i.dx, t0.x), i.dx, t1.y);
+            const float kx = fmaf(t1.x, i.dx, t0.y);
+            f2 a[4], at[4];
+#pragma unroll
+            for (int p = 0; p < 4; p++) {
+                f2 dy;
+                a[p] = pair_alpha(c, i, m0, m1, p, dy);
+                const f2 pw = fma2(dy, fma2(splat(t0.w), dy, splat(kx)), splat(hx));
+                at[p] = mul2(a[p], pw);
+            }
+            if (i.clampable) {   // warp-uniform and rare: alpha = min(0.99, alpha_raw), the constant branch has no tangent
+#pragma unroll
+                for (int p = 0; p < 4; p++) {
+                    if (a[p].x >= 0.99f) { a[p].x = 0.99f; at[p].x = 0.f; }
+                    if (a[p].y >= 0.99f) { a[p].y = 0.99f; at[p].y = 0.f; }
+                }
+            }
+#pragma unroll
+            for (int p = 0; p < 4; p++) {
+                PairT& s = st[p];
+                const f2 aT = mul2(a[p], s.T);
+                const f2 aTt = fma2(at[p], s.T, mul2(a[p], s.Tt));
+                s.C0 = fma2(splat(t1.z), aT, fma2(splat(q1.z), aTt, s.C0));
+                s.C1 = fma2(splat(t1.w), aT, fma2(splat(q1.w), aTt, s.C1));
+                s.C2 = fma2(splat(t2.x), aT, fma2(splat(q2.x), aTt, s.C2));
+                if (WITH_D) s.D = fma2(splat(t2.y), aT, fma2(splat(q2.y), aTt, s.D));
+                const f2 om = add2(splat(1.f), neg2(a[p]));
+                s.Tt = fma2(s.Tt, om, neg2(mul2(s.T, at[p])));
+                s.T = mul2(s.T, om);
+            }
         }
     }
 }
 
-// Per-pixel state of the back-to-front adjoint sweep.
-struct PixAdjoint {
-    float T;          // transmittance BEHIND the current instance, starts at T_final
-    float S;          // sum over the instances behind of (c_k . g + invd_k gd) alpha_k T_k, plus T_final (bg . g)
-    float g[3], gd;   // the pixel's cotangent
+// ---------------------------------------------------------------------------------------------
+// adjoint sweep
+// ---------------------------------------------------------------------------------------------
+struct PairA {
+    f2 T;             // transmittance BEHIND the current instance, starts at T_final
+    f2 S;             // sum over the instances behind of (c_k . g + invd_k gd) alpha_k T_k, plus T_final (bg . g)
+    f2 g0, g1, g2, gd;   // the pixels' cotangent
 };
 
-template <bool WITH_D>
-__device__ __forceinline__ void adjoint_update(PixAdjoint& p, float dx, float dy, float G, float alpha,
-                                               const float4& q1, const float4& q2, float (&v)[10]) {
-    const float r = rcp_approx(1.f - alpha);
-    p.T *= r;                                            // T_j = T_{j+1} / (1 - alpha_j)   (backward.cu:573)
-    float cg = fmaf(q1.z, p.g[0], fmaf(q1.w, p.g[1], q2.x * p.g[2]));
-    if (WITH_D) cg = fmaf(q2.y, p.gd, cg);
-    const float dL_dalpha = fmaf(p.T, cg, -r * p.S);
-    const float w = alpha * p.T;
-    p.S = fmaf(w, cg, p.S);
-    const float q = G * dL_dalpha;
-    const float qx = q * dx, qy = q * dy;
-    v[0] += q;
-    v[1] += qx;
-    v[2] += qy;
-    v[3] = fmaf(qx, dx, v[3]);
-    v[4] = fmaf(qx, dy, v[4]);
-    v[5] = fmaf(qy, dy, v[5]);
-    v[6] = fmaf(w, p.g[0], v[6]);
-    v[7] = fmaf(w, p.g[1], v[7]);
-    v[8] = fmaf(w, p.g[2], v[8]);
-    if (WITH_D) v[9] = fmaf(w, p.gd, v[9]);
-}
-
-// Back-to-front adjoint sweep.  p0 / p1 arrive with T = T_final and the pixel's cotangent (g, gd).
+// Back-to-front adjoint sweep.  sa[p] arrive with T = T_final and the pixels' cotangent (g, gd).
 // Writes one 48-byte partial per compact instance of the tile:
 // (dmean2D.xy | dconic xx,xy,yy | dopacity | dcolour rgb | dinvdepth | 0 0).
-// s_acc: [DBATCH * ACC_STRIDE] floats, zero on entry and on exit.
+// s_acc: [WBATCH * ACC_STRIDE] floats of this warp.
 template <bool WITH_D>
-__device__ __forceinline__ void adjoint_sweep(const TileCtx& c, RecordRing& ring, float* s_acc, int W, int H,
-                                              const float bg[3], PixAdjoint& p0, PixAdjoint& p1, uint32_t contrib0,
-                                              uint32_t contrib1, float4* __restrict__ inst_grads) {
-    const int rounds = (c.total + DBATCH - 1) / DBATCH;
+__device__ __forceinline__ void adjoint_sweep(const WTile& c, WarpRing& ring, float* s_acc, const float bg[3],
+                                              PairA (&sa)[4], float4* __restrict__ inst_grads) {
+    const int rounds = (c.total + WBATCH - 1) / WBATCH;
     if (rounds == 0) return;
     float4* out = inst_grads + (size_t)c.range.x * REC_F4;
     const int my_slot = slot10(c.lane);
-    const float half_W = 0.5f * W, half_H = 0.5f * H;   // backward.cu:527-528
+    const float half_W = 0.5f * c.W, half_H = 0.5f * c.H;   // backward.cu:527-528
     // the background term of dL/dalpha, -T_final (bg . g) / (1 - alpha), rides in S
-    p0.S = p0.T * (bg[0] * p0.g[0] + bg[1] * p0.g[1] + bg[2] * p0.g[2]);
-    p1.S = p1.T * (bg[0] * p1.g[0] + bg[1] * p1.g[1] + bg[2] * p1.g[2]);
-    const uint32_t warp_contrib = __reduce_max_sync(0xffffffffu, max(contrib0, contrib1));
+#pragma unroll
+    for (int p = 0; p < 4; p++)
+        sa[p].S = mul2(sa[p].T, fma2(splat(bg[0]), sa[p].g0, fma2(splat(bg[1]), sa[p].g1, mul2(splat(bg[2]), sa[p].g2))));
 
-    __syncthreads();   // a preceding tangent sweep may still be reading the ring
-    if (c.tid == 0) ring.issue(rounds - 1, (rounds - 1) & 1);
+    __syncwarp();   // a preceding tangent sweep may still be reading the ring
+    if (c.lane == 0) ring.issue(rounds - 1, (rounds - 1) & 1);
     for (int b = rounds - 1; b >= 0; b--) {
-        __syncthreads();   // batch b+1 consumed and written out; s_acc is zero
-        if (c.tid == 0 && b > 0) ring.issue(b - 1, (b - 1) & 1);
+        __syncwarp();   // batch b+1 consumed and written out
+        if (c.lane == 0 && b > 0) ring.issue(b - 1, (b - 1) & 1);
         ring.wait(b & 1);
-        const float4* rec = ring.stage(b & 1);
-        const int n = min(DBATCH, c.total - b * DBATCH);
-        const int jtop = min(n, (int)warp_contrib - b * DBATCH);   // warp-uniform upper bound
-        for (int j = jtop - 1; j >= 0; j--) {
-            const float4 q0 = rec[REC_F4 * j], q1 = rec[REC_F4 * j + 1];
-            float dx, e, f, dy0, dy1, G0, G1, al0, al1;
-            alpha_column(q0, c.pxf, dx, e, f);
-            const uint32_t pos = (uint32_t)(b * DBATCH + j);
-            const bool hit0 = pos < contrib0 && alpha_pixel(q0, q1, e, f, c.pyf0, dy0, G0, al0);
-            const bool hit1 = pos < contrib1 && alpha_pixel(q0, q1, e, f, c.pyf1, dy1, G1, al1);
-            if (!__any_sync(0xffffffffu, hit0 || hit1)) continue;
+        const float4* rec = ring.rec_stage(b & 1);
+        const uint4* msk = ring.msk_stage(b & 1);
+        const int n = ring.batch_size(b);
+        for (int j = n - 1; j >= 0; j--) {
+            const float4 q0 = rec[REC_F4 * j], q1 = rec[REC_F4 * j + 1], q2 = rec[REC_F4 * j + 2];
+            const uint4 m0 = msk[MSK_U4 * j], m1 = msk[MSK_U4 * j + 1];
+            const InstCol i = inst_column(c, q0, q1, q2);
+            f2 V[10];
+#pragma unroll
+            for (int k = 0; k < 10; k++) V[k] = splat(0.f);
+            f2 araw[4], a[4], dy[4];
+#pragma unroll
+            for (int p = 0; p < 4; p++) a[p] = araw[p] = pair_alpha(c, i, m0, m1, p, dy[p]);
+            if (i.clampable) {   // backward.cu:569: T and the weights use the clamped alpha, dG does not
+#pragma unroll
+                for (int p = 0; p < 4; p++) { a[p].x = fminf(0.99f, a[p].x); a[p].y = fminf(0.99f, a[p].y); }
+            }
+#pragma unroll
+            for (int p = 0; p < 4; p++) {
+                PairA& s = sa[p];
+                const f2 om = add2(splat(1.f), neg2(a[p]));
+                const f2 r = make_float2(rcp_approx(om.x), rcp_approx(om.y));
+                s.T = mul2(s.T, r);                                  // T_j = T_{j+1} / (1 - alpha_j)   (backward.cu:573)
+                f2 cg = fma2(splat(q1.z), s.g0, fma2(splat(q1.w), s.g1, mul2(splat(q2.x), s.g2)));
+                if (WITH_D) cg = fma2(splat(q2.y), s.gd, cg);
+                const f2 dL_dalpha = fma2(s.T, cg, neg2(mul2(r, s.S)));
+                const f2 w = mul2(a[p], s.T);
+                s.S = fma2(w, cg, s.S);
+                const f2 q = mul2(araw[p], dL_dalpha);
+                const f2 qx = mul2(q, splat(i.dx)), qy = mul2(q, dy[p]);
+                V[0] = add2(V[0], q);
+                V[1] = add2(V[1], qx);
+                V[2] = add2(V[2], qy);
+                V[3] = fma2(qx, splat(i.dx), V[3]);
+                V[4] = fma2(qx, dy[p], V[4]);
+                V[5] = fma2(qy, dy[p], V[5]);
+                V[6] = fma2(w, s.g0, V[6]);
+                V[7] = fma2(w, s.g1, V[7]);
+                V[8] = fma2(w, s.g2, V[8]);
+                if (WITH_D) V[9] = fma2(w, s.gd, V[9]);
+            }
             float v[10];
 #pragma unroll
-            for (int i = 0; i < 10; i++) v[i] = 0.f;
-            if (hit0 || hit1) {
-                const float4 q2 = rec[REC_F4 * j + 2];
-                if (hit0) adjoint_update<WITH_D>(p0, dx, dy0, G0, al0, q1, q2, v);
-                if (hit1) adjoint_update<WITH_D>(p1, dx, dy1, G1, al1, q1, q2, v);
-            }
+            for (int k = 0; k < 10; k++) v[k] = V[k].x + V[k].y;
             const float tot = warp_reduce10(v, c.lane);
-            if (my_slot >= 0) atomicAdd(&s_acc[j * ACC_STRIDE + my_slot], tot);
+            if (my_slot >= 0) s_acc[j * ACC_STRIDE + my_slot] = tot;
         }
-        __syncthreads();   // all warps' partials of batch b are in s_acc
-        // moments -> gradient record, once per instance
-#pragma unroll
-        for (int hh = 0; hh < DBATCH / PAIR_THREADS; hh++) {
-            const int slot = c.tid + hh * PAIR_THREADS;
-            if (slot < n) {
-                float* a = s_acc + slot * ACC_STRIDE;
-                const float4 q0 = rec[REC_F4 * slot], q1 = rec[REC_F4 * slot + 1];
-                const float A = q0.z, B = q0.w, C = q1.x, o = q1.y;
-                const float m0 = a[0], mx = a[1], my = a[2], mxx = a[3], mxy = a[4], myy = a[5];
-                float4* dst = out + (size_t)REC_F4 * (b * DBATCH + slot);
-                // dL/dG = o dL/dalpha;  dG/ddelx = -G (A dx + B dy), ...   (backward.cu:606-635)
-                dst[0] = make_float4(-half_W * o * (A * mx + B * my), -half_H * o * (C * my + B * mx),
-                                     -0.5f * o * mxx, -0.5f * o * mxy);
-                dst[1] = make_float4(-0.5f * o * myy, m0, a[6], a[7]);
-                dst[2] = make_float4(a[8], a[9], 0.f, 0.f);
-#pragma unroll
-                for (int i = 0; i < 10; i++) a[i] = 0.f;
-            }
+        __syncwarp();   // the batch's moments are in s_acc
+        // moments -> gradient record, once per instance (lane = slot of the batch)
+        if (c.lane < n) {
+            const float* m = s_acc + c.lane * ACC_STRIDE;
+            const float4 q0 = rec[REC_F4 * c.lane], q1 = rec[REC_F4 * c.lane + 1], q2 = rec[REC_F4 * c.lane + 2];
+            // conic back from log2 units: A = -2 ln2 a, B = -ln2 b, C = -2 ln2 c
+            const float A = -2.f * LN2 * q0.z, B = -LN2 * q0.w, C = -2.f * LN2 * q1.x, o = q2.w;
+            const float m0 = m[0], mx = m[1], my = m[2], mxx = m[3], mxy = m[4], myy = m[5];
+            float4* dst = out + (size_t)REC_F4 * (b * WBATCH + c.lane);
+            // moments are of o G dL/dalpha:  dL/dG = o dL/dalpha;  dG/ddelx = -G (A dx + B dy), ...   (backward.cu:606-635)
+            dst[0] = make_float4(-half_W * (A * mx + B * my), -half_H * (C * my + B * mx), -0.5f * mxx, -0.5f * mxy);
+            dst[1] = make_float4(-0.5f * myy, o > 0.f ? m0 / o : 0.f, m[6], m[7]);
+            dst[2] = make_float4(m[8], WITH_D ? m[9] : 0.f, 0.f, 0.f);
         }
     }
 }

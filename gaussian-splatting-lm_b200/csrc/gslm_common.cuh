@@ -19,11 +19,15 @@ constexpr int BATCH = 256;                       // instances staged in shared m
 constexpr int REC_F4 = 3;                        // one instance record = 3 x float4 = 48 bytes
 
 // Instance record (one per (tile, Gaussian) pair, stored in tile|depth order so that a
-// tile's batch is ONE contiguous 12 KB block that a single cp.async.bulk can stage):
-//   q0 = (x, y, conic.x, conic.y)   q1 = (conic.z, opacity, r, g)   q2 = (b, 1/depth, id bits, 0).
+// tile's batch is ONE contiguous block that a single cp.async.bulk can stage):
+//   primal form (k_blend_fwd, records_tmp):
+//     q0 = (x, y, conic.x, conic.y)   q1 = (conic.z, opacity, r, g)   q2 = (b, 1/depth, id bits, 0)
+//   derivative form (compact cache, written by k_compact_copy): exponent in log2 units, opacity folded in
+//     q0 = (x, y, a, b)   q1 = (c, log2 o, r, g)   q2 = (b, 1/depth, id bits, o),   (a, b, c) = -log2(e) (A/2, B, C/2)
+//   so that alpha_raw = o exp(power) = exp2(a dx^2 + b dx dy + c dy^2 + log2 o).
 // The per-instance gradient record is (dmean2D.xy | dconic xx,xy,yy | dopacity | drgb |
 // dinvdepth); the per-Gaussian tangent record holds the coefficients of the power tangent as a polynomial in
-// (dx, dy): (a1, a2, a3, a4 | a5, opacity_t, r_t, g_t | b_t, invdepth_t, 0, 0), see preprocess.cu.
+// (dx, dy): (a1, a2, a3, a4 | a5, opacity_t / opacity, r_t, g_t | b_t, invdepth_t, 0, 0), see preprocess.cu.
 //
 // COMPACT CACHE.  Only instances that at least one pixel of their tile actually BLENDED survive
 // the forward pass (k_blend_fwd flags them): instances behind the point where every pixel of
@@ -59,18 +63,20 @@ struct ImageView {  // per-pixel / per-tile state
     uint32_t* cstart;         // [T+1] exclusive scan of ccount; cstart[T] = Rc
     size_t total;
 };
-struct BinningView {  // compact per-instance state that outlives the forward pass (56 B / compact instance)
-    float4* records;          // [3 Rc] compact records, tile|depth order
+struct BinningView {  // compact per-instance state that outlives the forward pass (88 B / compact instance)
+    float4* records;          // [3 Rc] compact records in derivative form (see below), tile|depth order
+    uint4* masks;             // [2 Rc] 256-bit hit mask: bit l of word k <=> pixel (row 2k + (l>>4), column l&15) of the tile blended it
     uint32_t* cid;            // [Rc] Gaussian id of each compact instance
     uint32_t* g_list;         // [Rc] CSR payload: compact positions grouped by Gaussian (ascending within a Gaussian)
     size_t total;
 };
-struct BinningTemp {  // per-instance state that is dead once the forward pass returns (84 B / instance)
+struct BinningTemp {  // per-instance state that is dead once the forward pass returns (116 B / instance + sort temporaries)
     uint64_t* keys_sorted;    // [R]
     uint64_t* keys_unsorted;  // [R]
     uint32_t* vals_unsorted;  // [R]
     uint32_t* point_list;     // [R] sorted Gaussian ids (BinningState::point_list)
     float4* records_tmp;      // [3R] compact records at tile-local positions (range.x + j), before the global scan
+    uint4* masks_tmp;         // [2R] their hit masks, same positions
     char* sort_temp;
     size_t sort_temp_bytes;
     size_t total;

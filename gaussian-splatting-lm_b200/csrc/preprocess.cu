@@ -206,7 +206,8 @@ k_preprocess_tangent(PreTanArgs a, const int32_t* __restrict__ radii, const uint
     const float a1 = -(o.conx.v * o.x.d + o.cony.v * o.y.d);
     const float a2 = -(o.conz.v * o.y.d + o.cony.v * o.x.d);
     out[0] = make_float4(a1, a2, -0.5f * o.conx.d, -0.5f * o.conz.d);
-    out[1] = make_float4(-o.cony.d, o.opac.d, cr_t, cg_t);
+    // the tile sweeps evaluate alpha_raw = exp2(... + log2 o): d alpha_raw = alpha_raw (power_t + o_t / o)
+    out[1] = make_float4(-o.cony.d, o.opac.v > 0.f ? o.opac.d / o.opac.v : 0.f, cr_t, cg_t);
     out[2] = make_float4(cb_t, invd.d, 0.f, 0.f);
 }
 

@@ -42,7 +42,7 @@ class GslmGrads(C.Structure):
 class GslmBufferView(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("point_list", "keys_sorted", "ranges", "n_contrib", "final_T",
                                           "tiles_touched", "point_offsets", "depths", "means2D", "conic_opacity",
-                                          "rgb", "cov3D", "clamped", "n_contrib_c", "cstart", "records", "cid",
+                                          "rgb", "cov3D", "clamped", "n_contrib_c", "cstart", "records", "masks", "cid",
                                           "g_off", "g_list")]
 
 
@@ -393,6 +393,7 @@ def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer, sortScratch=
     out = {"num_cached": Rc}
     if binningBuffer is not None and binningBuffer.numel() and Rc > 0:
         out["records"] = view(binningBuffer, v.records, 48 * Rc, torch.float32, (Rc, 12))
+        out["masks"] = view(binningBuffer, v.masks, 32 * Rc, torch.int32, (Rc, 8))
         out["cid"] = view(binningBuffer, v.cid, 4 * Rc, torch.int32, (Rc,))
         out["g_list"] = view(binningBuffer, v.g_list, 4 * Rc, torch.int32, (Rc,))
     if sortScratch is not None and sortScratch.numel() and R > 0:

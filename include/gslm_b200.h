@@ -89,7 +89,7 @@ typedef struct GslmGrads {
  * aligned, that stays valid until the caller frees it.  `which`: 0 geometry, 1 binning,
  * 2 image buffer -- the three opaque buffers of the reference
  * (geomBuffer / binningBuffer / imgBuffer, DGR/rasterize_points.cu:80-88) -- 3 = sort scratch
- * (keys + radix-sort temporaries, 32 B / instance) that may be freed or reused as soon as the
+ * (keys, radix-sort temporaries, uncompacted records and hit masks) that may be freed or reused as soon as the
  * call returns (the reference trims the same data off its binning buffer after the forward pass,
  * rasterizer_impl.cu:383-388), -1 = anonymous scratch for the duration of the call. */
 typedef void* (*GslmAllocFn)(void* ctx, int32_t which, size_t bytes);
@@ -102,8 +102,8 @@ int32_t gslm_abi_version(void);
  * (DGR/cuda_rasterizer/rasterizer_impl.h:29-43). */
 size_t gslm_geom_bytes(int32_t P);
 size_t gslm_image_bytes(int32_t width, int32_t height);
-size_t gslm_binning_bytes(int64_t num_cached);        /* persistent compact cache: 56 B / cached instance */
-size_t gslm_binning_temp_bytes(int64_t num_rendered); /* sort scratch: ~96 B / rendered instance, dead after forward */
+size_t gslm_binning_bytes(int64_t num_cached);        /* persistent compact cache: 88 B / cached instance */
+size_t gslm_binning_temp_bytes(int64_t num_rendered); /* sort scratch: ~128 B / rendered instance, dead after forward */
 
 /* Replaces _C.mark_visible (DGR/rasterize_points.cu:401-420). present: uint8 [P]. */
 int32_t gslm_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
@@ -188,7 +188,8 @@ typedef struct GslmBufferView {
     const uint8_t* clamped;       /* [P] bit c set <=> channel c clamped                                */
     const uint32_t* n_contrib_c;  /* [H*W] last blended position in the compact tile list               */
     const uint32_t* cstart;       /* [T+1] compact tile offsets, cstart[T] = Rc                         */
-    const float* records;         /* [Rc,12] compact instance records                                   */
+    const float* records;         /* [Rc,12] compact instance records (derivative form: log2-scaled conic, log2 o) */
+    const uint32_t* masks;        /* [Rc,8] hit masks: bit l of word k <=> pixel (row 2k + l/16, column l%16) blended it */
     const uint32_t* cid;          /* [Rc] Gaussian id per compact instance                              */
     const uint32_t* g_off;        /* [P+1] CSR offsets into g_list                                      */
     const uint32_t* g_list;       /* [Rc] compact positions grouped by Gaussian                         */

@@ -361,3 +361,21 @@ def test_compact_cache_structure(C):
     tile_of = (np.arange(H)[:, None] // 16) * gx + (np.arange(W)[None, :] // 16)
     assert (ncc <= np.diff(cstart)[tile_of]).all()
     assert ((ncc == 0) == (v["n_contrib"].cpu().numpy() == 0)).all()
+    # hit masks: bit l of word k of a compact instance <=> pixel (row 2k + l // 16, column l % 16) of its tile
+    # blended it.  No mask is empty, and a pixel's last set bit sits at its n_contrib_c - 1.
+    masks = v["masks"].cpu().numpy().view(np.uint32)
+    assert masks.shape == (Rc, 8) and (masks != 0).any(axis=1).all()
+    for t in (0, len(ranges) // 3, len(ranges) // 2, len(ranges) - 1):
+        m = masks[cstart[t]:cstart[t + 1]]
+        ty, tx = divmod(t, gx)
+        for k in range(8):
+            for l in range(32):
+                y, x = ty * 16 + 2 * k + l // 16, tx * 16 + l % 16
+                hit = np.nonzero((m[:, k] >> np.uint32(l)) & np.uint32(1))[0]
+                last = int(hit[-1]) + 1 if len(hit) else 0
+                if y < H and x < W:
+                    assert last == ncc[y, x], (t, k, l)
+                else:
+                    assert last == 0
+    # derivative-form records: q1.y = log2(opacity kept in q2.w)
+    assert torch.allclose(rec[:, 5], torch.log2(rec[:, 11]), atol=1e-5)
