@@ -12,8 +12,14 @@
 
 namespace gslm {
 
-constexpr int DWARPS = 4;                               // tiles per CTA
+#ifndef GSLM_DWARPS
+#define GSLM_DWARPS 4
+#endif
+constexpr int DWARPS = GSLM_DWARPS;                     // tiles (independent warps) per CTA
 constexpr int DTHREADS = DWARPS * 32;
+#ifndef GSLM_DMINB
+#define GSLM_DMINB 1
+#endif
 constexpr int RING_F4 = 2 * WBATCH * REC_F4;            // float4 per warp: record ring (3 KB)
 constexpr int RING_U4 = 2 * WBATCH * MSK_U4;            // uint4 per warp: mask ring (2 KB)
 
@@ -96,7 +102,7 @@ k_blend_bwd(TileArgs a, const float* __restrict__ dL_dcolor, const float* __rest
             float4* __restrict__ inst_grads) {
     __shared__ __align__(128) float4 s_rec[DWARPS][RING_F4];
     __shared__ __align__(128) uint4 s_msk[DWARPS][RING_U4];
-    __shared__ float s_acc[DWARPS][WBATCH * ACC_STRIDE];
+    __shared__ float s_acc[DWARPS][(WBATCH + 1) * ACC_STRIDE];
     __shared__ __align__(8) uint64_t s_bar[DWARPS][2];
     const int warp = threadIdx.x >> 5;
     WTile c;
@@ -120,13 +126,13 @@ k_blend_bwd(TileArgs a, const float* __restrict__ dL_dcolor, const float* __rest
     adjoint_sweep<WITH_D>(c, ring, s_acc[warp], bgv, sa, inst_grads);
 }
 
-__global__ void __launch_bounds__(DTHREADS)
+__global__ void __launch_bounds__(DTHREADS, GSLM_DMINB)
 k_blend_jtjv(TileArgs a, const float4* __restrict__ tgeom, const float* __restrict__ weight,
              float4* __restrict__ inst_grads, float* __restrict__ out_vJJv) {
     __shared__ __align__(128) float4 s_rec[DWARPS][RING_F4];
     __shared__ __align__(128) uint4 s_msk[DWARPS][RING_U4];
     __shared__ __align__(16) float4 s_tan[DWARPS][RING_F4];
-    __shared__ float s_acc[DWARPS][WBATCH * ACC_STRIDE];
+    __shared__ float s_acc[DWARPS][(WBATCH + 1) * ACC_STRIDE];
     __shared__ __align__(8) uint64_t s_bar[DWARPS][2];
     const int warp = threadIdx.x >> 5;
     WTile c;

@@ -39,6 +39,12 @@
 
 namespace gslm {
 
+#ifndef GSLM_CLAMP_BRANCH
+#define GSLM_CLAMP_BRANCH 1
+#endif
+#ifndef GSLM_DEFER_REDUCE
+#define GSLM_DEFER_REDUCE 0
+#endif
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 
@@ -71,7 +77,6 @@ __device__ __forceinline__ void stage_tangents(const WTile& c, int b, const uint
 // What one lane needs of one instance, shared by both sweeps.
 struct InstCol {
     float dx, ex, fx, cc, dyb;
-    bool clampable;
 };
 __device__ __forceinline__ InstCol inst_column(const WTile& c, const float4& q0, const float4& q1, const float4& q2) {
     InstCol i;
@@ -80,7 +85,6 @@ __device__ __forceinline__ InstCol inst_column(const WTile& c, const float4& q0,
     i.fx = q0.w * i.dx;                     // b dx
     i.cc = q1.x;
     i.dyb = q0.y - c.pyf;
-    i.clampable = q2.w > 0.99f;             // alpha_raw <= o: the 0.99 clamp can only bind when o > 0.99
     return i;
 }
 __device__ __forceinline__ uint32_t mask_word(const uint4& m0, const uint4& m1, int k) {
@@ -145,33 +149,38 @@ __device__ __forceinline__ void tangent_sweep(const WTile& c, WarpRing& ring, fl
             // power_t + o_t / o = dy (a4 dy + kx) + hx
             const float hx = fmaf(fmaf(t0.z, i.dx, t0.x), i.dx, t1.y);
             const float kx = fmaf(t1.x, i.dx, t0.y);
-            f2 a[4], at[4];
+            f2 a[4], pw[4];
 #pragma unroll
             for (int p = 0; p < 4; p++) {
                 f2 dy;
                 a[p] = pair_alpha(c, i, m0, m1, p, dy);
-                const f2 pw = fma2(dy, fma2(splat(t0.w), dy, splat(kx)), splat(hx));
-                at[p] = mul2(a[p], pw);
+                pw[p] = fma2(dy, fma2(splat(t0.w), dy, splat(kx)), splat(hx));
             }
-            if (i.clampable) {   // warp-uniform and rare: alpha = min(0.99, alpha_raw), the constant branch has no tangent
+            // alpha = min(0.99, alpha_raw); the constant branch has no tangent.  Branch-free on purpose (ALU-pipe work in
+            // the shadow of the FMA pipe, and the whole instance stays one basic block for the scheduler).
+#if GSLM_CLAMP_BRANCH
+            if (q2.w > 0.99f)   // warp-uniform: alpha_raw <= o, so the clamp can only bind when o > 0.99
+#endif
 #pragma unroll
-                for (int p = 0; p < 4; p++) {
-                    if (a[p].x >= 0.99f) { a[p].x = 0.99f; at[p].x = 0.f; }
-                    if (a[p].y >= 0.99f) { a[p].y = 0.99f; at[p].y = 0.f; }
-                }
+            for (int p = 0; p < 4; p++) {
+                pw[p].x = a[p].x < 0.99f ? pw[p].x : 0.f;
+                pw[p].y = a[p].y < 0.99f ? pw[p].y : 0.f;
+                a[p].x = fminf(0.99f, a[p].x);
+                a[p].y = fminf(0.99f, a[p].y);
             }
 #pragma unroll
             for (int p = 0; p < 4; p++) {
+                // with alpha_t = alpha pw:  (alpha T)_t = alpha (pw T + T_t) =: aTt,  T_t <- T_t (1 - alpha) - T alpha_t
+                // = T_t - aTt,  T <- T - alpha T
                 PairT& s = st[p];
                 const f2 aT = mul2(a[p], s.T);
-                const f2 aTt = fma2(at[p], s.T, mul2(a[p], s.Tt));
+                const f2 aTt = mul2(a[p], fma2(pw[p], s.T, s.Tt));
                 s.C0 = fma2(splat(t1.z), aT, fma2(splat(q1.z), aTt, s.C0));
                 s.C1 = fma2(splat(t1.w), aT, fma2(splat(q1.w), aTt, s.C1));
                 s.C2 = fma2(splat(t2.x), aT, fma2(splat(q2.x), aTt, s.C2));
                 if (WITH_D) s.D = fma2(splat(t2.y), aT, fma2(splat(q2.y), aTt, s.D));
-                const f2 om = add2(splat(1.f), neg2(a[p]));
-                s.Tt = fma2(s.Tt, om, neg2(mul2(s.T, at[p])));
-                s.T = mul2(s.T, om);
+                s.Tt = add2(s.Tt, neg2(aTt));
+                s.T = add2(s.T, neg2(aT));
             }
         }
     }
@@ -189,7 +198,7 @@ struct PairA {
 // Back-to-front adjoint sweep.  sa[p] arrive with T = T_final and the pixels' cotangent (g, gd).
 // Writes one 48-byte partial per compact instance of the tile:
 // (dmean2D.xy | dconic xx,xy,yy | dopacity | dcolour rgb | dinvdepth | 0 0).
-// s_acc: [WBATCH * ACC_STRIDE] floats of this warp.
+// s_acc: [(WBATCH + 1) * ACC_STRIDE] floats of this warp.
 template <bool WITH_D>
 __device__ __forceinline__ void adjoint_sweep(const WTile& c, WarpRing& ring, float* s_acc, const float bg[3],
                                               PairA (&sa)[4], float4* __restrict__ inst_grads) {
@@ -212,20 +221,28 @@ __device__ __forceinline__ void adjoint_sweep(const WTile& c, WarpRing& ring, fl
         const float4* rec = ring.rec_stage(b & 1);
         const uint4* msk = ring.msk_stage(b & 1);
         const int n = ring.batch_size(b);
+        // the warp reduction of instance j+1 is issued together with the arithmetic of instance j (software
+        // pipelining by hand: the five dependent shuffle stages hide behind independent FMA work); the first
+        // iteration reduces zeros into the spare row n
+        float vp[10];
+#pragma unroll
+        for (int k = 0; k < 10; k++) vp[k] = 0.f;
         for (int j = n - 1; j >= 0; j--) {
             const float4 q0 = rec[REC_F4 * j], q1 = rec[REC_F4 * j + 1], q2 = rec[REC_F4 * j + 2];
             const uint4 m0 = msk[MSK_U4 * j], m1 = msk[MSK_U4 * j + 1];
             const InstCol i = inst_column(c, q0, q1, q2);
-            f2 V[10];
-#pragma unroll
-            for (int k = 0; k < 10; k++) V[k] = splat(0.f);
+            // per-thread sums over its eight pixels; dx is common to them, so the moments with a dx factor
+            // follow from Q0 = sum q, Q1 = sum q dy, Q2 = sum q dy^2 after the loop
+            f2 Q0 = splat(0.f), Q1 = Q0, Q2 = Q0, G0 = Q0, G1 = Q0, G2 = Q0, GD = Q0;
             f2 araw[4], a[4], dy[4];
 #pragma unroll
             for (int p = 0; p < 4; p++) a[p] = araw[p] = pair_alpha(c, i, m0, m1, p, dy[p]);
-            if (i.clampable) {   // backward.cu:569: T and the weights use the clamped alpha, dG does not
+            // backward.cu:569: T and the weights use the clamped alpha, dG does not
+#if GSLM_CLAMP_BRANCH
+            if (q2.w > 0.99f)
+#endif
 #pragma unroll
-                for (int p = 0; p < 4; p++) { a[p].x = fminf(0.99f, a[p].x); a[p].y = fminf(0.99f, a[p].y); }
-            }
+            for (int p = 0; p < 4; p++) { a[p].x = fminf(0.99f, a[p].x); a[p].y = fminf(0.99f, a[p].y); }
 #pragma unroll
             for (int p = 0; p < 4; p++) {
                 PairA& s = sa[p];
@@ -238,24 +255,42 @@ __device__ __forceinline__ void adjoint_sweep(const WTile& c, WarpRing& ring, fl
                 const f2 w = mul2(a[p], s.T);
                 s.S = fma2(w, cg, s.S);
                 const f2 q = mul2(araw[p], dL_dalpha);
-                const f2 qx = mul2(q, splat(i.dx)), qy = mul2(q, dy[p]);
-                V[0] = add2(V[0], q);
-                V[1] = add2(V[1], qx);
-                V[2] = add2(V[2], qy);
-                V[3] = fma2(qx, splat(i.dx), V[3]);
-                V[4] = fma2(qx, dy[p], V[4]);
-                V[5] = fma2(qy, dy[p], V[5]);
-                V[6] = fma2(w, s.g0, V[6]);
-                V[7] = fma2(w, s.g1, V[7]);
-                V[8] = fma2(w, s.g2, V[8]);
-                if (WITH_D) V[9] = fma2(w, s.gd, V[9]);
+                const f2 qy = mul2(q, dy[p]);
+                Q0 = add2(Q0, q);
+                Q1 = add2(Q1, qy);
+                Q2 = fma2(qy, dy[p], Q2);
+                G0 = fma2(w, s.g0, G0);
+                G1 = fma2(w, s.g1, G1);
+                G2 = fma2(w, s.g2, G2);
+                if (WITH_D) GD = fma2(w, s.gd, GD);
             }
             float v[10];
+            v[0] = Q0.x + Q0.y;            // sum q
+            v[2] = Q1.x + Q1.y;            // sum q dy
+            v[5] = Q2.x + Q2.y;            // sum q dy^2
+            v[1] = v[0] * i.dx;            // sum q dx
+            v[3] = v[1] * i.dx;            // sum q dx^2
+            v[4] = v[2] * i.dx;            // sum q dx dy
+            v[6] = G0.x + G0.y;
+            v[7] = G1.x + G1.y;
+            v[8] = G2.x + G2.y;
+            v[9] = WITH_D ? GD.x + GD.y : 0.f;
+#if GSLM_DEFER_REDUCE
+            const float tot = warp_reduce10(vp, c.lane);
+            if (my_slot >= 0) s_acc[(j + 1) * ACC_STRIDE + my_slot] = tot;
 #pragma unroll
-            for (int k = 0; k < 10; k++) v[k] = V[k].x + V[k].y;
+            for (int k = 0; k < 10; k++) vp[k] = v[k];
+#else
             const float tot = warp_reduce10(v, c.lane);
             if (my_slot >= 0) s_acc[j * ACC_STRIDE + my_slot] = tot;
+#endif
         }
+#if GSLM_DEFER_REDUCE
+        {
+            const float tot = warp_reduce10(vp, c.lane);
+            if (my_slot >= 0) s_acc[my_slot] = tot;
+        }
+#endif
         __syncwarp();   // the batch's moments are in s_acc
         // moments -> gradient record, once per instance (lane = slot of the batch)
         if (c.lane < n) {
