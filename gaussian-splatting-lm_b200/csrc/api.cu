@@ -133,7 +133,7 @@ int32_t gslm_jvp_cached(const GslmGaussians* g, const GslmGaussians* gt, const G
     BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_cached);
     float4* tgeom = reinterpret_cast<float4*>(align_up((size_t)scratch));
     TangentPtrs t = make_tangents(gt, nullptr);
-    if (launch_preprocess_tangent(*g, t, *cam, radii, gv.g_off, tgeom, s)) return 1;
+    if (launch_preprocess_tangent(*g, t, *cam, gv, tgeom, s)) return 1;
     if (launch_blend_jvp(bv, iv, cam->width, cam->height, tgeom, cam->bg, nullptr, out_color_tangent,
                          out_invdepth_tangent, s)) return 1;
     return debug_sync(cam, s, "jvp_cached");
@@ -172,7 +172,7 @@ int32_t gslm_forward_jvp(const GslmGaussians* g, const GslmGaussians* gt, const 
         tgeom = reinterpret_cast<float4*>(align_up((size_t)extra));
     }
     TangentPtrs t = make_tangents(gt, camt);
-    if (launch_preprocess_tangent(*g, t, *cam, radii, gv.g_off, tgeom, s)) return 1;
+    if (launch_preprocess_tangent(*g, t, *cam, gv, tgeom, s)) return 1;
     if (launch_blend_jvp(bv, iv, W, H, tgeom, cam->bg, camt ? camt->bg : nullptr, out_color_tangent,
                          out_invdepth_tangent, s)) return 1;
     return debug_sync(cam, s, "forward_jvp");
@@ -217,11 +217,71 @@ int32_t gslm_jtjv(const GslmGaussians* g, const GslmGaussians* gt, const GslmCam
     float4* inst = reinterpret_cast<float4*>((char*)tgeom + gslm_jvp_scratch_bytes(P) - 128);
     inst = reinterpret_cast<float4*>(align_up((size_t)inst));
     TangentPtrs t = make_tangents(gt, nullptr);
-    if (launch_preprocess_tangent(*g, t, *cam, radii, gv.g_off, tgeom, s)) return 1;
+    if (launch_preprocess_tangent(*g, t, *cam, gv, tgeom, s)) return 1;
     if (num_cached > 0)
         if (launch_blend_jtjv(bv, iv, W, H, cam->bg, tgeom, weight, inst, out_vJJv, s)) return 1;
     if (launch_preprocess_bwd(*g, *cam, radii, gv, bv, inst, false, *grads, s)) return 1;
     return debug_sync(cam, s, "jtjv");
+}
+
+size_t gslm_jtjv_batch_scratch_bytes(int32_t P, int32_t n_views, const int32_t* num_cached) {
+    size_t worst = 0;
+    for (int v0 = 0; v0 < n_views; v0 += MAX_BATCH_VIEWS) {
+        size_t need = 0;
+        for (int v = v0; v < n_views && v < v0 + MAX_BATCH_VIEWS; v++)
+            need += gslm_jtjv_scratch_bytes(P, num_cached ? num_cached[v] : 0);
+        worst = need > worst ? need : worst;
+    }
+    return worst;
+}
+
+int32_t gslm_jtjv_batch(const GslmGaussians* g, const GslmGaussians* gt, int32_t n_views, const GslmCamera* cams,
+                        const int32_t* const* radii, const void* const* geom_buffers,
+                        const void* const* binning_buffers, const void* const* image_buffers,
+                        const int32_t* num_cached, const float* const* weights, void* scratch, size_t scratch_bytes,
+                        GslmGrads* grads, float* out_vJJv, void* stream) {
+    if (n_views < 0 || (n_views > 0 && (!cams || !radii || !geom_buffers || !binning_buffers || !image_buffers ||
+                                        !num_cached || !scratch)) || !grads || !g) {
+        set_error("null argument");
+        return 1;
+    }
+    if (scratch_bytes < gslm_jtjv_batch_scratch_bytes(g->P, n_views, num_cached)) {
+        set_error("scratch too small: need %zu bytes", gslm_jtjv_batch_scratch_bytes(g->P, n_views, num_cached));
+        return 1;
+    }
+    for (int v = 0; v < n_views; v++)
+        if (check_inputs(g, &cams[v])) return 1;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int P = g->P;
+    if (P == 0) return 0;
+    TangentPtrs t = make_tangents(gt, nullptr);
+    GslmGrads acc = *grads;
+    for (int v0 = 0; v0 < n_views; v0 += MAX_BATCH_VIEWS) {
+        const int n = (n_views - v0) < MAX_BATCH_VIEWS ? (n_views - v0) : MAX_BATCH_VIEWS;
+        GeomView gv[MAX_BATCH_VIEWS];
+        ImageView iv[MAX_BATCH_VIEWS];
+        BinningView bv[MAX_BATCH_VIEWS];
+        float4 *tgeom[MAX_BATCH_VIEWS], *inst[MAX_BATCH_VIEWS];
+        char* p = reinterpret_cast<char*>(align_up((size_t)scratch));
+        for (int i = 0; i < n; i++) {
+            const int v = v0 + i;
+            gv[i] = carve_geom(const_cast<void*>(geom_buffers[v]), P);
+            iv[i] = carve_image(const_cast<void*>(image_buffers[v]), cams[v].width, cams[v].height);
+            bv[i] = carve_binning(const_cast<void*>(binning_buffers[v]), num_cached[v]);
+            tgeom[i] = reinterpret_cast<float4*>(p);
+            p += align_up((size_t)P * REC_F4 * sizeof(float4));
+            inst[i] = reinterpret_cast<float4*>(p);
+            p += align_up((size_t)num_cached[v] * REC_F4 * sizeof(float4));
+        }
+        if (launch_preprocess_tangent_batch(*g, t, n, cams + v0, gv, tgeom, s)) return 1;
+        if (launch_blend_jtjv_batch(n, bv, iv, cams + v0, tgeom, weights ? weights + v0 : nullptr, inst, out_vJJv, s))
+            return 1;
+        for (int i = 0; i < n; i++) {   // per view, in order: the sum over views is deterministic
+            if (launch_preprocess_bwd(*g, cams[v0 + i], radii[v0 + i], gv[i], bv[i], inst[i], false, acc, s)) return 1;
+            acc.accumulate = 1;
+        }
+    }
+    return 0;
 }
 
 int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_rendered, int64_t num_cached,

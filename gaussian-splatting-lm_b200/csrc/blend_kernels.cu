@@ -9,6 +9,7 @@
 // of shared memory -- warps never synchronise with each other.
 // =============================================================================
 #include "blend_sweeps.cuh"
+#include <cstring>
 
 namespace gslm {
 
@@ -126,14 +127,26 @@ k_blend_bwd(TileArgs a, const float* __restrict__ dL_dcolor, const float* __rest
     adjoint_sweep<WITH_D>(c, ring, s_acc[warp], bgv, sa, inst_grads);
 }
 
+// Up to MAX_BATCH_VIEWS linearised views per launch (blockIdx.y): the tail of one view's tiles overlaps the next
+// view's, and a CG iteration needs n_views / MAX_BATCH_VIEWS launches of this kernel instead of n_views.
+struct JtjvBatch {
+    TileArgs t[MAX_BATCH_VIEWS];
+    const float4* tgeom[MAX_BATCH_VIEWS];
+    const float* weight[MAX_BATCH_VIEWS];
+    float4* inst_grads[MAX_BATCH_VIEWS];
+};
+
 __global__ void __launch_bounds__(DTHREADS, GSLM_DMINB)
-k_blend_jtjv(TileArgs a, const float4* __restrict__ tgeom, const float* __restrict__ weight,
-             float4* __restrict__ inst_grads, float* __restrict__ out_vJJv) {
+k_blend_jtjv(const __grid_constant__ JtjvBatch vb, float* __restrict__ out_vJJv) {
     __shared__ __align__(128) float4 s_rec[DWARPS][RING_F4];
     __shared__ __align__(128) uint4 s_msk[DWARPS][RING_U4];
     __shared__ __align__(16) float4 s_tan[DWARPS][RING_F4];
     __shared__ float s_acc[DWARPS][(WBATCH + 1) * ACC_STRIDE];
     __shared__ __align__(8) uint64_t s_bar[DWARPS][2];
+    const TileArgs& a = vb.t[blockIdx.y];
+    const float4* __restrict__ tgeom = vb.tgeom[blockIdx.y];
+    const float* __restrict__ weight = vb.weight[blockIdx.y];
+    float4* __restrict__ inst_grads = vb.inst_grads[blockIdx.y];
     const int warp = threadIdx.x >> 5;
     WTile c;
     if (!make_tile(a, warp, c)) return;
@@ -215,14 +228,33 @@ int launch_blend_bwd(const BinningView& bv, const ImageView& iv, int W, int H, c
     return 0;
 }
 
-int launch_blend_jtjv(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg,
-                      const float4* tgeom, const float* weight, float4* inst_grads, float* out_vJJv, cudaStream_t s) {
-    const TileArgs a = tile_args(bv, iv, W, H, bg);
-    if (a.tiles == 0) return 0;
+int launch_blend_jtjv_batch(int n_views, const BinningView* bvs, const ImageView* ivs, const GslmCamera* cams,
+                            const float4* const* tgeoms, const float* const* weights, float4* const* inst_grads,
+                            float* out_vJJv, cudaStream_t s) {
+    if (n_views > MAX_BATCH_VIEWS) { set_error("too many views in one batch"); return 1; }
+    JtjvBatch vb;
+    memset(&vb, 0, sizeof(vb));
+    int max_tiles = 0;
+    for (int i = 0; i < n_views; i++) {
+        vb.t[i] = tile_args(bvs[i], ivs[i], cams[i].width, cams[i].height, cams[i].bg);
+        vb.tgeom[i] = tgeoms[i];
+        vb.weight[i] = weights ? weights[i] : nullptr;
+        vb.inst_grads[i] = inst_grads[i];
+        max_tiles = max_tiles > vb.t[i].tiles ? max_tiles : vb.t[i].tiles;
+    }
+    if (max_tiles == 0 || n_views == 0) return 0;
     StageScope ts(ST_BLEND_JTJV, s);
-    k_blend_jtjv<<<grid_of(a.tiles), DTHREADS, 0, s>>>(a, tgeom, weight, inst_grads, out_vJJv);
+    k_blend_jtjv<<<dim3(grid_of(max_tiles), n_views), DTHREADS, 0, s>>>(vb, out_vJJv);
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
+}
+
+int launch_blend_jtjv(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg,
+                      const float4* tgeom, const float* weight, float4* inst_grads, float* out_vJJv, cudaStream_t s) {
+    GslmCamera cam;
+    memset(&cam, 0, sizeof(cam));
+    cam.width = W; cam.height = H; cam.bg = bg;
+    return launch_blend_jtjv_batch(1, &bv, &iv, &cam, &tgeom, weight ? &weight : nullptr, &inst_grads, out_vJJv, s);
 }
 
 }  // namespace gslm

@@ -16,6 +16,7 @@ namespace gslm {
 constexpr int TILE_X = 16, TILE_Y = 16;          // DGR/cuda_rasterizer/config.h:17-19
 constexpr int TILE_PIX = TILE_X * TILE_Y;        // 256 threads per tile CTA, one pixel each
 constexpr int BATCH = 256;                       // instances staged in shared memory per round
+constexpr int MAX_BATCH_VIEWS = 16;              // linearised views per batched launch (descriptors travel as kernel parameters)
 constexpr int REC_F4 = 3;                        // one instance record = 3 x float4 = 48 bytes
 
 // Instance record (one per (tile, Gaussian) pair, stored in tile|depth order so that a
@@ -50,6 +51,8 @@ struct GeomView {   // per-Gaussian state, SoA
     uint32_t* num_rendered;   // [1] device copy of R (tail of the scan)
     uint32_t* g_off;          // [P+1] CSR offsets: compact instances of Gaussian i are g_list[g_off[i] .. g_off[i+1])
     uint32_t* g_cursor;       // [P]   build-time counters / cursors of the CSR
+    uint32_t* active_ids;     // [n_active <= P] ascending ids of the Gaussians with >= 1 compact instance (aliases g_cursor)
+    uint32_t* n_active;       // [1]
     char* scan_temp;
     size_t scan_temp_bytes;
     size_t total;
@@ -122,9 +125,12 @@ struct TangentPtrs {   // tangent inputs of the forward-mode preprocess; any poi
 // preprocess.cu
 int launch_preprocess(const GslmGaussians& g, const GslmCamera& cam, const GeomView& gv, int32_t* radii,
                       cudaStream_t s);
-// writes the per-Gaussian tangent record tgeom[3P] for Gaussians with radii > 0 (zeros otherwise)
-int launch_preprocess_tangent(const GslmGaussians& g, const TangentPtrs& t, const GslmCamera& cam,
-                              const int32_t* radii, const uint32_t* g_off, float4* tgeom, cudaStream_t s);
+// writes the per-Gaussian tangent record tgeom[3 id] of every ACTIVE Gaussian (the others are never read)
+int launch_preprocess_tangent(const GslmGaussians& g, const TangentPtrs& t, const GslmCamera& cam, const GeomView& gv,
+                              float4* tgeom, cudaStream_t s);
+// the same for up to MAX_BATCH_VIEWS linearised views in ONE launch (gvs / tgeoms: host arrays of n_views entries)
+int launch_preprocess_tangent_batch(const GslmGaussians& g, const TangentPtrs& t, int n_views, const GslmCamera* cams,
+                                    const GeomView* gvs, float4* const* tgeoms, cudaStream_t s);
 int launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present, cudaStream_t s);
 int launch_preprocess_bwd(const GslmGaussians& g, const GslmCamera& cam, const int32_t* radii, const GeomView& gv,
                           const BinningView& bv, const float4* inst_grads, bool has_invdepth_grad,
@@ -147,5 +153,9 @@ int launch_blend_bwd(const BinningView& bv, const ImageView& iv, int W, int H, c
                      const float* dL_dcolor, const float* dL_dinvdepth, float4* inst_grads, cudaStream_t s);
 int launch_blend_jtjv(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg,
                       const float4* tgeom, const float* weight, float4* inst_grads, float* out_vJJv, cudaStream_t s);
+// up to MAX_BATCH_VIEWS views in one launch; weights may be null (all ones) or hold null entries
+int launch_blend_jtjv_batch(int n_views, const BinningView* bvs, const ImageView* ivs, const GslmCamera* cams,
+                            const float4* const* tgeoms, const float* const* weights, float4* const* inst_grads,
+                            float* out_vJJv, cudaStream_t s);
 
 }  // namespace gslm

@@ -10,6 +10,7 @@
 // =============================================================================
 #include "gslm_common.cuh"
 #include "gslm_math.cuh"
+#include <cstring>
 
 namespace gslm {
 
@@ -150,17 +151,32 @@ __device__ __forceinline__ dualf ldd(const float* p, const float* t, size_t i) {
     return dualf(__ldg(p + i), t ? __ldg(t + i) : 0.f);
 }
 
+// One launch covers up to MAX_BATCH_VIEWS linearised views (blockIdx.y) and, per view, only the Gaussians that own
+// compact instances there (active list built at compaction): dense warps instead of ~3 live lanes in 32.
+struct PreTanView {
+    const float *viewmatrix, *projmatrix, *campos;
+    const uint32_t* active_ids;
+    const uint32_t* n_active;
+    float4* tgeom;
+    float tan_fovx, tan_fovy, focal_x, focal_y, focal_x_t, focal_y_t;
+    int W, H;
+};
+struct PreTanBatch { PreTanView v[MAX_BATCH_VIEWS]; };
+
 template <bool CAMT>
 __global__ void __launch_bounds__(256)
-k_preprocess_tangent(PreTanArgs a, const int32_t* __restrict__ radii, const uint32_t* __restrict__ g_off,
-                     float4* __restrict__ tgeom) {
+k_preprocess_tangent(PreTanArgs a, const __grid_constant__ PreTanBatch vb) {
+    const PreTanView& vw = vb.v[blockIdx.y];
+    const uint32_t n_active = *vw.n_active;
+    if (blockIdx.x * blockDim.x >= n_active) return;
     __shared__ CamConst sc;
-    load_cam(&sc, a.p.viewmatrix, a.p.projmatrix, a.p.campos, a.t.viewmatrix, a.t.projmatrix, a.t.campos);
-    int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= a.p.P) return;
-    float4* out = tgeom + (size_t)REC_F4 * idx;
-    // only Gaussians with at least one compact instance are ever looked up by the tile sweeps
-    if (radii[idx] <= 0 || g_off[idx] == g_off[idx + 1]) return;
+    load_cam(&sc, vw.viewmatrix, vw.projmatrix, vw.campos, a.t.viewmatrix, a.t.projmatrix, a.t.campos);
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n_active) return;
+    const int idx = (int)__ldg(vw.active_ids + slot);
+    float4* out = vw.tgeom + (size_t)REC_F4 * idx;
+    a.p.W = vw.W; a.p.H = vw.H; a.p.focal_x = vw.focal_x; a.p.focal_y = vw.focal_y;
+    a.p.tan_fovx = vw.tan_fovx; a.p.tan_fovy = vw.tan_fovy; a.focal_x_t = vw.focal_x_t; a.focal_y_t = vw.focal_y_t;
     CamD<CAMT> cam{&sc, a.p.focal_x, a.p.focal_y, a.p.tan_fovx, a.p.tan_fovy,
                    a.focal_x_t, a.focal_y_t, a.t.tan_fovx, a.t.tan_fovy};
     v3<dualf> mean = {ldd(a.p.means3D, a.t.means3D, 3 * (size_t)idx), ldd(a.p.means3D, a.t.means3D, 3 * (size_t)idx + 1),
@@ -211,29 +227,45 @@ k_preprocess_tangent(PreTanArgs a, const int32_t* __restrict__ radii, const uint
     out[2] = make_float4(cb_t, invd.d, 0.f, 0.f);
 }
 
-int launch_preprocess_tangent(const GslmGaussians& g, const TangentPtrs& t, const GslmCamera& cam,
-                              const int32_t* radii, const uint32_t* g_off, float4* tgeom, cudaStream_t s) {
+int launch_preprocess_tangent_batch(const GslmGaussians& g, const TangentPtrs& t, int n_views, const GslmCamera* cams,
+                                    const GeomView* gvs, float4* const* tgeoms, cudaStream_t s) {
+    if (g.P == 0 || n_views == 0) return 0;
+    if (n_views > MAX_BATCH_VIEWS) { set_error("too many views in one batch"); return 1; }
     PreTanArgs a;
-    a.p.P = g.P; a.p.D = g.sh_degree; a.p.M = g.M; a.p.W = cam.width; a.p.H = cam.height;
-    a.p.scale_modifier = g.scale_modifier; a.p.tan_fovx = cam.tan_fovx; a.p.tan_fovy = cam.tan_fovy;
-    a.p.focal_y = cam.height / (2.0f * cam.tan_fovy);
-    a.p.focal_x = cam.width / (2.0f * cam.tan_fovx);
-    a.p.antialiasing = cam.antialiasing; a.p.prefiltered = cam.prefiltered;
+    memset(&a, 0, sizeof(a));
+    a.p.P = g.P; a.p.D = g.sh_degree; a.p.M = g.M; a.p.scale_modifier = g.scale_modifier;
+    a.p.antialiasing = cams[0].antialiasing; a.p.prefiltered = cams[0].prefiltered;
     a.p.means3D = g.means3D; a.p.opacities = g.opacities; a.p.scales = g.scales; a.p.rotations = g.rotations;
     a.p.cov3D_precomp = g.cov3D_precomp; a.p.shs = g.shs; a.p.colors_precomp = g.colors_precomp;
-    a.p.viewmatrix = cam.viewmatrix; a.p.projmatrix = cam.projmatrix; a.p.campos = cam.campos;
     a.t = t;
-    // focal = S / (2 tan)  =>  d focal = -focal / tan * d tan   (rasterizer_jvp_impl.h:182-183 on duals)
-    a.focal_x_t = -a.p.focal_x / cam.tan_fovx * t.tan_fovx;
-    a.focal_y_t = -a.p.focal_y / cam.tan_fovy * t.tan_fovy;
-    if (g.P == 0) return 0;
+    PreTanBatch vb;
+    memset(&vb, 0, sizeof(vb));
+    for (int i = 0; i < n_views; i++) {
+        const GslmCamera& cam = cams[i];
+        if (cam.antialiasing != cams[0].antialiasing) { set_error("views of one batch must agree on antialiasing"); return 1; }
+        PreTanView& v = vb.v[i];
+        v.viewmatrix = cam.viewmatrix; v.projmatrix = cam.projmatrix; v.campos = cam.campos;
+        v.active_ids = gvs[i].active_ids; v.n_active = gvs[i].n_active; v.tgeom = tgeoms[i];
+        v.tan_fovx = cam.tan_fovx; v.tan_fovy = cam.tan_fovy; v.W = cam.width; v.H = cam.height;
+        v.focal_y = cam.height / (2.0f * cam.tan_fovy);
+        v.focal_x = cam.width / (2.0f * cam.tan_fovx);
+        // focal = S / (2 tan)  =>  d focal = -focal / tan * d tan   (rasterizer_jvp_impl.h:182-183 on duals)
+        v.focal_x_t = -v.focal_x / cam.tan_fovx * t.tan_fovx;
+        v.focal_y_t = -v.focal_y / cam.tan_fovy * t.tan_fovy;
+    }
     StageScope ts(ST_PRE_TANGENT, s);
-    bool camt = t.viewmatrix || t.projmatrix || t.campos || t.tan_fovx != 0.f || t.tan_fovy != 0.f ||
-                t.scale_modifier != 0.f;
-    if (camt) k_preprocess_tangent<true><<<(g.P + 255) / 256, 256, 0, s>>>(a, radii, g_off, tgeom);
-    else k_preprocess_tangent<false><<<(g.P + 255) / 256, 256, 0, s>>>(a, radii, g_off, tgeom);
+    const bool camt = t.viewmatrix || t.projmatrix || t.campos || t.tan_fovx != 0.f || t.tan_fovy != 0.f ||
+                      t.scale_modifier != 0.f;
+    const dim3 grid((g.P + 255) / 256, n_views);
+    if (camt) k_preprocess_tangent<true><<<grid, 256, 0, s>>>(a, vb);
+    else k_preprocess_tangent<false><<<grid, 256, 0, s>>>(a, vb);
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
+}
+
+int launch_preprocess_tangent(const GslmGaussians& g, const TangentPtrs& t, const GslmCamera& cam, const GeomView& gv,
+                              float4* tgeom, cudaStream_t s) {
+    return launch_preprocess_tangent_batch(g, t, 1, &cam, &gv, &tgeom, s);
 }
 
 // rasterizer_impl.cu:54-66 + auxiliary.h:194-219 (prefiltered = false)

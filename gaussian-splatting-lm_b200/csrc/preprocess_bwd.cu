@@ -26,6 +26,8 @@ struct BwdArgs {
     const uint8_t* clamped;
     const uint32_t* g_off;
     const uint32_t* g_list;
+    const uint32_t* active_ids;   // accumulate mode: only the Gaussians with compact instances are visited
+    const uint32_t* n_active;
     const float4* inst_grads;
     GslmGrads g;
 };
@@ -38,12 +40,16 @@ template <bool ACC> __device__ __forceinline__ void put(float* p, size_t i, floa
 
 template <bool ACC>
 __global__ void __launch_bounds__(128) k_preprocess_bwd(BwdArgs a) {
+    if (ACC && blockIdx.x * blockDim.x >= *a.n_active) return;   // accumulate mode runs on the active list
     __shared__ float sV[16], sPV[16], sCam[3];
     if (threadIdx.x < 16) { sV[threadIdx.x] = a.viewmatrix[threadIdx.x]; sPV[threadIdx.x] = a.projmatrix[threadIdx.x]; }
     if (threadIdx.x < 3) sCam[threadIdx.x] = a.campos ? a.campos[threadIdx.x] : 0.f;
     __syncthreads();
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= a.P) return;
+    if (ACC) {
+        if ((uint32_t)idx >= *a.n_active) return;
+        idx = (int)__ldg(a.active_ids + idx);
+    } else if (idx >= a.P) return;
     const size_t i = idx;
     const int ncoef = a.shs ? a.M : 0;
     const uint32_t beg = a.g_off[idx], end = a.g_off[idx + 1];
@@ -305,6 +311,7 @@ int launch_preprocess_bwd(const GslmGaussians& g, const GslmCamera& cam, const i
     a.shs = g.colors_precomp ? nullptr : g.shs;
     a.viewmatrix = cam.viewmatrix; a.projmatrix = cam.projmatrix; a.campos = cam.campos;
     a.radii = radii; a.clamped = gv.clamped; a.g_off = gv.g_off; a.g_list = bv.g_list;
+    a.active_ids = gv.active_ids; a.n_active = gv.n_active;
     a.inst_grads = inst_grads; a.g = grads;
     int grid = (g.P + 127) / 128;
     StageScope ts(ST_PRE_BWD, s);

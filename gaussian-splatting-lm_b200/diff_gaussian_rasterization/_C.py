@@ -75,7 +75,8 @@ ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_int32, C.c_size_t)
 
 EXPORTS = ("gslm_last_error", "gslm_abi_version", "gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_binning_temp_bytes",
            "gslm_mark_visible", "gslm_forward", "gslm_forward_jvp", "gslm_backward_scratch_bytes", "gslm_backward",
-           "gslm_jvp_scratch_bytes", "gslm_jvp_cached", "gslm_jtjv_scratch_bytes", "gslm_jtjv", "gslm_buffer_view", "gslm_timing_num_stages",
+           "gslm_jvp_scratch_bytes", "gslm_jvp_cached", "gslm_jtjv_scratch_bytes", "gslm_jtjv",
+           "gslm_jtjv_batch_scratch_bytes", "gslm_jtjv_batch", "gslm_buffer_view", "gslm_timing_num_stages",
            "gslm_timing_stage_name", "gslm_timing_enable", "gslm_timing_collect")
 
 
@@ -89,7 +90,7 @@ def lib():
         L.gslm_last_error.restype = C.c_char_p
         for n in ("gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_binning_temp_bytes",
                   "gslm_backward_scratch_bytes",
-                  "gslm_jvp_scratch_bytes", "gslm_jtjv_scratch_bytes"):
+                  "gslm_jvp_scratch_bytes", "gslm_jtjv_scratch_bytes", "gslm_jtjv_batch_scratch_bytes"):
             getattr(L, n).restype = C.c_size_t
         L.gslm_geom_bytes.argtypes = [C.c_int32]
         L.gslm_image_bytes.argtypes = [C.c_int32, C.c_int32]
@@ -105,6 +106,8 @@ def lib():
         L.gslm_backward.argtypes = [vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
         L.gslm_jvp_cached.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp]
         L.gslm_jtjv.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
+        L.gslm_jtjv_batch_scratch_bytes.argtypes = [C.c_int32, C.c_int32, vp]
+        L.gslm_jtjv_batch.argtypes = [vp, vp, C.c_int32, vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, vp, vp, vp]
         L.gslm_buffer_view.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int64, vp, vp, vp, vp, vp]
         L.gslm_timing_stage_name.restype = C.c_char_p
         L.gslm_timing_collect.argtypes = [vp, vp]
@@ -372,6 +375,64 @@ def jtjv(gauss_args, tangent_args, cam_args, radii, geomBuffer, R, binningBuffer
                        _ptr(binningBuffer), _ptr(imageBuffer), Rc, _ptr(w), scratch.data_ptr(),
                        C.addressof(gr), _ptr(out_vJJv), _stream()))
     return scratch
+
+
+class JtjvBatchPlan:
+    """Host-side argument block of gslm_jtjv_batch for a fixed set of linearised views (built once per
+    linearisation, reused by every CG iteration): ctypes arrays of cameras, buffer pointers, compact counts and
+    weights, the scratch tensor, and references that keep every tensor alive."""
+
+    def __init__(self, views, device):
+        """views: list of (cam_args, radii, geomBuffer, R, binningBuffer, imageBuffer, weight-or-None)."""
+        L = lib()
+        n = len(views)
+        self.n = n
+        self.keep = []
+        self.cams = (GslmCamera * max(n, 1))()
+        VP = C.c_void_p * max(n, 1)
+        self.radii, self.geom, self.binning, self.image, self.weights = VP(), VP(), VP(), VP(), VP()
+        self.num_cached = (C.c_int32 * max(n, 1))()
+        any_weight = False
+        for i, (cam_args, radii, geomBuffer, R, binningBuffer, imageBuffer, weight) in enumerate(views):
+            bg, vm, pm, tfx, tfy, H, W, campos, aa, dbg = cam_args
+            cam, k = _camera(bg, vm, pm, tfx, tfy, H, W, campos, False, aa, dbg)
+            self.cams[i] = cam
+            w = _f32(weight)
+            self.keep.append((k, radii, geomBuffer, binningBuffer, imageBuffer, w))
+            self.radii[i], self.geom[i] = _ptr(radii), _ptr(geomBuffer)
+            self.binning[i], self.image[i] = _ptr(binningBuffer), _ptr(imageBuffer)
+            self.weights[i] = _ptr(w)
+            any_weight = any_weight or w is not None
+            self.num_cached[i] = _cached(R, imageBuffer, W, H)
+        self.any_weight = any_weight
+        self.device = device
+        self.scratch = None
+        self.P = None
+
+    def scratch_for(self, P):
+        if self.scratch is None or self.P != P:
+            need = lib().gslm_jtjv_batch_scratch_bytes(int(P), self.n, C.cast(self.num_cached, C.c_void_p))
+            self.scratch = torch.empty(max(int(need), 1), dtype=torch.uint8, device=self.device)
+            self.P = P
+        return self.scratch
+
+
+def jtjv_batch(gauss_args, tangent_args, plan, outs, out_vJJv=None, accumulate=True):
+    """outs (8-tuple like rasterize_gaussians_backward, entries may be None) (+)= sum over the plan's views of
+    J_v^T diag(weight_v) J_v v -- ONE call into the library per CG iteration."""
+    L = lib()
+    g, k1 = _gaussians(*gauss_args)
+    gt, k3 = _tangent_gaussians(*tangent_args)
+    scratch = plan.scratch_for(g.P)
+    gr = GslmGrads()
+    (gr.dL_dmeans2D, gr.dL_dcolors, gr.dL_dopacity, gr.dL_dmeans3D, gr.dL_dcov3D, gr.dL_dsh, gr.dL_dscales,
+     gr.dL_drotations) = [_ptr(o) for o in outs]
+    gr.accumulate = 1 if accumulate else 0
+    vp = lambda a: C.cast(a, C.c_void_p)
+    _check(L.gslm_jtjv_batch(C.addressof(g), C.addressof(gt), plan.n, vp(plan.cams), vp(plan.radii), vp(plan.geom),
+                             vp(plan.binning), vp(plan.image), vp(plan.num_cached),
+                             vp(plan.weights) if plan.any_weight else None, scratch.data_ptr(), scratch.numel(),
+                             C.addressof(gr), _ptr(out_vJJv), _stream()))
 
 
 def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer, sortScratch=None):

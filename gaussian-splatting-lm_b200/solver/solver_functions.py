@@ -70,6 +70,7 @@ class LinearSolverFunctions:
         self.cached = legal if cached is None else bool(cached)
         self._views = None
         self._scratch = None
+        self._plan = None
 
     # ------------------------------------------------------------------ reference API
     def get_initial_solution(self):
@@ -192,6 +193,7 @@ class LinearSolverFunctions:
         self._empty = torch.empty(0, device=dev)
         self._act = a = self._activated()
         self._views = []
+        self._plan = None
         losses = []
         for start, end in self._batches():
             cams = self.viewpoint_cams[start:end]
@@ -330,9 +332,10 @@ class LinearSolverFunctions:
         gargs = self._gauss_args()
         flat, views, sinks = self._act_accumulators()
         quad = torch.zeros(1, dtype=torch.float32, device=flat.device) if return_quad else None
-        for vc in self._views:
-            self._scratch = _C.jtjv(gargs, targs, vc.cam_args, vc.radii, vc.geom, vc.R, vc.binning, vc.img, vc.weight,
-                                    sinks, out_vJJv=quad, scratch=self._scratch)
+        if self._plan is None:
+            self._plan = _C.JtjvBatchPlan([(vc.cam_args, vc.radii, vc.geom, vc.R, vc.binning, vc.img, vc.weight)
+                                           for vc in self._views], flat.device)
+        _C.jtjv_batch(gargs, targs, self._plan, sinks, out_vJJv=quad)
         if self.dist:
             self.dist.all_reduce(flat)
             if quad is not None:

@@ -162,6 +162,21 @@ int32_t gslm_jtjv(const GslmGaussians* g, const GslmGaussians* gt, const GslmCam
                   int32_t num_cached, const float* weight, void* scratch, GslmGrads* grads, float* out_vJJv,
                   void* stream);
 
+/* The same product summed over n_views linearised views in one call:
+ *   grads (+)= sum_v J_v^T diag(w_v) J_v v,     out_vJJv += sum_v v^T J_v^T W_v J_v v.
+ * All array arguments are HOST arrays of n_views entries (device pointers inside).  Views are processed in chunks:
+ * ONE tangent-preprocess launch and ONE fused tile launch per chunk of up to 16 views, then the per-Gaussian adjoint
+ * view by view, in order (deterministic sum).  This is what solver.LinearSolverFunctions.normal_matvec calls once per
+ * CG iteration (solver/conjugate_gradient.py:28); it replaces n_views round trips through matvec / matvec_T
+ * (solver/solver_functions.py:74-123).  grads->accumulate == 0: the first view overwrites, the others add.
+ * scratch: gslm_jtjv_batch_scratch_bytes(P, n_views, num_cached) bytes. */
+size_t gslm_jtjv_batch_scratch_bytes(int32_t P, int32_t n_views, const int32_t* num_cached);
+int32_t gslm_jtjv_batch(const GslmGaussians* g, const GslmGaussians* gt, int32_t n_views, const GslmCamera* cams,
+                        const int32_t* const* radii, const void* const* geom_buffers,
+                        const void* const* binning_buffers, const void* const* image_buffers,
+                        const int32_t* num_cached, const float* const* weights, void* scratch, size_t scratch_bytes,
+                        GslmGrads* grads, float* out_vJJv, void* stream);
+
 /* ---- optional per-stage device timing (no reference counterpart; bench.py's live roofline numbers) ----
  * When enabled, each stage brackets its kernels with a cudaEvent pair on the launching stream.
  * gslm_timing_collect synchronises the device and returns, per stage, the summed elapsed milliseconds and the

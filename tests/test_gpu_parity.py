@@ -190,6 +190,44 @@ def test_fused_jtjv_equals_vjp_of_jvp(C, name, deg, weighted):
     assert h.rel_l2(outs[5].cpu().numpy(), 2 * two[5].cpu().numpy()) < DER_TOL
 
 
+def test_jtjv_batch_equals_sum_of_views(C):
+    """gslm_jtjv_batch over 19 views (two chunks of the 16-view launch limit, two image sizes, some weights None)
+    == the per-view fused calls accumulated in the same order: bit-identical (same kernels, same summation order),
+    in accumulate and in overwrite mode."""
+    g = ss.make_gaussians(3000, sh_degree=2, seed=21, scale_mult=0.8)
+    t = ss.random_tangent(g, seed=22)
+    gd, td = h.to_dev(g), h.to_dev(t)
+    cams = ss.hemisphere_rig(10, 112, 80) + ss.hemisphere_rig(9, 96, 64)
+    views, singles = [], []
+    gen = torch.Generator().manual_seed(5)
+    for i, cam in enumerate(cams):
+        ct = h.cam_tensors(cam, bg=(0.1, 0.0, 0.2))
+        R, color, radii, geom, binning, img, invd = h.c_forward(C, gd, ct)
+        w = None if i % 3 == 0 else (torch.rand(color.shape, generator=gen) > 0.3).float().cuda() * 2.0
+        views.append((h.cam_args(ct), radii, geom, R, binning, img, w))
+    P, M = g["means3D"].shape[0], g["shs"].shape[1]
+    zz = lambda *s: torch.zeros(s, device="cuda")
+    mk = lambda: (zz(P, 3), None, zz(P, 1), zz(P, 3), None, zz(P, M, 3), zz(P, 3), zz(P, 4))
+    ref, quad_ref = mk(), torch.zeros(1, device="cuda")
+    for v in views:
+        C.jtjv(h.gauss_args(gd), h.tangent_args(td), *v, ref, out_vJJv=quad_ref)
+    plan = C.JtjvBatchPlan(views, torch.device("cuda"))
+    out, quad = mk(), torch.zeros(1, device="cuda")
+    C.jtjv_batch(h.gauss_args(gd), h.tangent_args(td), plan, out, out_vJJv=quad)
+    for a, b in zip(out, ref):
+        if a is not None:
+            assert torch.equal(a, b)
+    assert abs(float(quad) - float(quad_ref)) <= 1e-5 * abs(float(quad_ref))
+    assert float(ref[5].abs().sum()) > 0
+    # overwrite mode: garbage in the sinks is replaced, not added to
+    out2 = tuple(None if o is None else torch.full_like(o, 7.0) for o in out)
+    C.jtjv_batch(h.gauss_args(gd), h.tangent_args(td), plan, out2, accumulate=False)
+    # (the overwrite and accumulate kernels contract their last multiply-add differently: last-bit differences)
+    for a, b in zip(out2, ref):
+        if a is not None:
+            assert h.relerr(a.cpu().numpy(), b.cpu().numpy()) < 1e-6
+
+
 def test_adjoint_identity_gpu(C):
     """<u, J v> == <J^T u, v>, rel 1e-4 (tests/test_matvec.py:81-83) on a scene away from the reference's
     non-adjoint quirks (see tests/test_oracle_golden.py::test_oracle_adjoint_identity)."""
