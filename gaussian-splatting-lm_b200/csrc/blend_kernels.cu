@@ -14,12 +14,12 @@
 namespace gslm {
 
 #ifndef GSLM_DWARPS
-#define GSLM_DWARPS 4
+#define GSLM_DWARPS 1
 #endif
 constexpr int DWARPS = GSLM_DWARPS;                     // tiles (independent warps) per CTA
 constexpr int DTHREADS = DWARPS * 32;
 #ifndef GSLM_DMINB
-#define GSLM_DMINB 1
+#define GSLM_DMINB 18
 #endif
 constexpr int RING_F4 = 2 * WBATCH * REC_F4;            // float4 per warp: record ring (3 KB)
 constexpr int RING_U4 = 2 * WBATCH * MSK_U4;            // uint4 per warp: mask ring (2 KB)
