@@ -102,6 +102,7 @@ BinningView carve_binning(void* base, int64_t Rc) {
     v.masks = take<uint4>(p, 2 * n);
     v.cid = take<uint32_t>(p, n);
     v.g_list = take<uint32_t>(p, n);
+    v.g_inv = take<uint32_t>(p, n);
     v.total = (size_t)(p - reinterpret_cast<char*>(base));
     return v;
 }
@@ -306,6 +307,12 @@ k_sort_glist(int P, const uint32_t* __restrict__ g_off, uint32_t* __restrict__ g
     }
 }
 
+__global__ void __launch_bounds__(256)
+k_invert_glist(uint32_t Rc, const uint32_t* __restrict__ g_list, uint32_t* __restrict__ g_inv) {
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < Rc) g_inv[g_list[s]] = s;
+}
+
 struct HasInstances {   // Gaussian i has at least one compact instance in this view
     const uint32_t* g_off;
     __device__ __forceinline__ bool operator()(uint32_t i) const { return g_off[i + 1] > g_off[i]; }
@@ -330,6 +337,8 @@ int run_compaction(const GeomView& gv, const BinningView& bv, const BinningTemp&
         k_fill_glist<<<(unsigned)((Rc + 255) / 256), 256, 0, s>>>((uint32_t)Rc, bv.cid, gv.g_cursor, bv.g_list);
         GSLM_CUDA_OK(cudaGetLastError());
         k_sort_glist<<<(P + 255) / 256, 256, 0, s>>>(P, gv.g_off, bv.g_list);
+        GSLM_CUDA_OK(cudaGetLastError());
+        k_invert_glist<<<(unsigned)((Rc + 255) / 256), 256, 0, s>>>((uint32_t)Rc, bv.g_list, bv.g_inv);
         GSLM_CUDA_OK(cudaGetLastError());
     }
     // ascending list of the Gaussians that own compact instances (the only ones the per-Gaussian derivative stages

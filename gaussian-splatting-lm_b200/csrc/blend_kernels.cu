@@ -29,6 +29,7 @@ struct TileArgs {          // one linearised view
     const float4* records;
     const uint4* masks;
     const uint32_t* cid;
+    const uint32_t* g_inv;
     const float* final_T;
     int W, H, tiles;
     const float* bg;
@@ -124,7 +125,7 @@ k_blend_bwd(TileArgs a, const float* __restrict__ dL_dcolor, const float* __rest
         set_lane(s.gd, hi, (in && WITH_D) ? dL_dinvdepth[pix] : 0.f);
     }
     const float bgv[3] = {a.bg[0], a.bg[1], a.bg[2]};
-    adjoint_sweep<WITH_D>(c, ring, s_acc[warp], bgv, sa, inst_grads);
+    adjoint_sweep<WITH_D>(c, ring, s_acc[warp], bgv, sa, a.g_inv, inst_grads);
 }
 
 // Up to MAX_BATCH_VIEWS linearised views per launch (blockIdx.y): the tail of one view's tiles overlaps the next
@@ -184,7 +185,7 @@ k_blend_jtjv(const __grid_constant__ JtjvBatch vb, float* __restrict__ out_vJJv)
         set_lane(d.gd, hi, 0.f);
     }
     // pass 2: J^T u
-    adjoint_sweep<false>(c, ring, s_acc[warp], bgv, sa, inst_grads);
+    adjoint_sweep<false>(c, ring, s_acc[warp], bgv, sa, a.g_inv, inst_grads);
 
     if (out_vJJv) {
 #pragma unroll
@@ -196,7 +197,7 @@ k_blend_jtjv(const __grid_constant__ JtjvBatch vb, float* __restrict__ out_vJJv)
 static int tiles_of(int W, int H) { return ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y); }
 static TileArgs tile_args(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg) {
     TileArgs a;
-    a.cstart = iv.cstart; a.records = bv.records; a.masks = bv.masks; a.cid = bv.cid; a.final_T = iv.final_T;
+    a.cstart = iv.cstart; a.records = bv.records; a.masks = bv.masks; a.cid = bv.cid; a.g_inv = bv.g_inv; a.final_T = iv.final_T;
     a.W = W; a.H = H; a.tiles = tiles_of(W, H); a.bg = bg;
     return a;
 }

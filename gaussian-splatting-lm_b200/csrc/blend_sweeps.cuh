@@ -226,15 +226,17 @@ struct PairA {
 };
 
 // Back-to-front adjoint sweep.  sa[p] arrive with T = T_final and the pixels' cotangent (g, gd).
-// Writes one 48-byte partial per compact instance of the tile:
+// Writes one 48-byte partial per compact instance of the tile, at the instance's slot in the per-Gaussian CSR
+// (g_inv), so that the per-Gaussian adjoint stage reads a Gaussian's partials as one contiguous run:
 // (dmean2D.xy | dconic xx,xy,yy | dopacity | dcolour rgb | dinvdepth | 0 0).
 // s_acc: [(WBATCH + 1) * ACC_STRIDE] floats of this warp.
 template <bool WITH_D>
 __device__ __forceinline__ void adjoint_sweep(const WTile& c, WarpRing& ring, float* s_acc, const float bg[3],
-                                              PairA (&sa)[4], float4* __restrict__ inst_grads) {
+                                              PairA (&sa)[4], const uint32_t* __restrict__ g_inv,
+                                              float4* __restrict__ inst_grads) {
     const int rounds = (c.total + WBATCH - 1) / WBATCH;
     if (rounds == 0) return;
-    float4* out = inst_grads + (size_t)c.range.x * REC_F4;
+    const uint32_t* inv = g_inv + c.range.x;   // gradient records go to Gaussian-major (CSR) slots
     const int my_slot = slot10(c.lane);
     const float half_W = 0.5f * c.W, half_H = 0.5f * c.H;   // backward.cu:527-528
     // the background term of dL/dalpha, -T_final (bg . g) / (1 - alpha), rides in S
@@ -358,7 +360,7 @@ __device__ __forceinline__ void adjoint_sweep(const WTile& c, WarpRing& ring, fl
             // conic back from log2 units: A = -2 ln2 a, B = -ln2 b, C = -2 ln2 c
             const float A = -2.f * LN2 * q0.z, B = -LN2 * q0.w, C = -2.f * LN2 * q1.x, o = q2.w;
             const float m0 = m[0], mx = m[1], my = m[2], mxx = m[3], mxy = m[4], myy = m[5];
-            float4* dst = out + (size_t)REC_F4 * (b * WBATCH + c.lane);
+            float4* dst = inst_grads + (size_t)REC_F4 * __ldg(inv + b * WBATCH + c.lane);
             // moments are of o G dL/dalpha:  dL/dG = o dL/dalpha;  dG/ddelx = -G (A dx + B dy), ...   (backward.cu:606-635)
             dst[0] = make_float4(-half_W * (A * mx + B * my), -half_H * (C * my + B * mx), -0.5f * mxx, -0.5f * mxy);
             dst[1] = make_float4(-0.5f * myy, o > 0.f ? m0 / o : 0.f, m[6], m[7]);

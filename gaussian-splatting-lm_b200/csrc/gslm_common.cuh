@@ -66,11 +66,12 @@ struct ImageView {  // per-pixel / per-tile state
     uint32_t* cstart;         // [T+1] exclusive scan of ccount; cstart[T] = Rc
     size_t total;
 };
-struct BinningView {  // compact per-instance state that outlives the forward pass (88 B / compact instance)
+struct BinningView {  // compact per-instance state that outlives the forward pass (92 B / compact instance)
     float4* records;          // [3 Rc] compact records in derivative form (see below), tile|depth order
     uint4* masks;             // [2 Rc] 256-bit hit mask: bit l of word k <=> pixel (row 2k + (l>>4), column l&15) of the tile blended it
     uint32_t* cid;            // [Rc] Gaussian id of each compact instance
     uint32_t* g_list;         // [Rc] CSR payload: compact positions grouped by Gaussian (ascending within a Gaussian)
+    uint32_t* g_inv;          // [Rc] inverse of g_list: compact position -> CSR slot (where the tile kernels put its gradient record)
     size_t total;
 };
 struct BinningTemp {  // per-instance state that is dead once the forward pass returns (116 B / instance + sort temporaries)

@@ -4,10 +4,9 @@
 // Replaces computeCov2DCUDA (backward.cu:147-326) + bwd preprocessCUDA (backward.cu:398-449)
 // + bwd computeColorFromSH (:23-142) + bwd computeCov3D (:330-393), and the ten float
 // atomicAdd per (pixel, Gaussian) hit of the reference's bwd renderCUDA (:593-635):
-// the tile kernels leave ONE 48-byte partial per (tile, Gaussian) instance in sorted
-// order (coalesced, no atomics); this kernel gathers a Gaussian's compact instances through
-// the CSR (g_off, g_list) built at linearisation time and sums them in a fixed order, so
-// the whole backward pass is deterministic.
+// the tile kernels leave ONE 48-byte partial per (tile, Gaussian) instance at the instance's
+// slot of the per-Gaussian CSR (no atomics); this kernel sums a Gaussian's compact instances -- one contiguous
+// run [g_off[i], g_off[i+1]) -- in a fixed order, so the whole backward pass is deterministic.
 // Quirks of the reference kept on purpose: 1/(det^2 + 1e-7) in the
 // conic adjoint, no quaternion-normalisation Jacobian, the alpha-clamp is not masked.
 // =============================================================================
@@ -65,13 +64,14 @@ __global__ void __launch_bounds__(128) k_preprocess_bwd(BwdArgs a) {
         }
         return;
     }
-    // ---- 1. deterministic gather-sum of this Gaussian's instance partials ----
+    // ---- 1. deterministic sum of this Gaussian's instance partials: the tile kernels wrote them at the CSR slots
+    //         [beg, end), i.e. one contiguous run in ascending tile order ----
     float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
     float2 s2 = make_float2(0.f, 0.f);
     {
-        for (uint32_t slot = beg; slot < end; slot++) {
-            const float4* r = a.inst_grads + (size_t)REC_F4 * __ldg(a.g_list + slot);
-            float4 q0 = __ldg(r), q1 = __ldg(r + 1), q2 = __ldg(r + 2);
+        const float4* r = a.inst_grads + (size_t)REC_F4 * beg;
+        for (uint32_t slot = beg; slot < end; slot++, r += REC_F4) {
+            const float4 q0 = __ldg(r), q1 = __ldg(r + 1), q2 = __ldg(r + 2);
             s0.x += q0.x; s0.y += q0.y; s0.z += q0.z; s0.w += q0.w;
             s1.x += q1.x; s1.y += q1.y; s1.z += q1.z; s1.w += q1.w;
             s2.x += q2.x; s2.y += q2.y;

@@ -102,7 +102,7 @@ int32_t gslm_abi_version(void);
  * (DGR/cuda_rasterizer/rasterizer_impl.h:29-43). */
 size_t gslm_geom_bytes(int32_t P);
 size_t gslm_image_bytes(int32_t width, int32_t height);
-size_t gslm_binning_bytes(int64_t num_cached);        /* persistent compact cache: 88 B / cached instance */
+size_t gslm_binning_bytes(int64_t num_cached);        /* persistent compact cache: 92 B / cached instance */
 size_t gslm_binning_temp_bytes(int64_t num_rendered); /* sort scratch: ~128 B / rendered instance, dead after forward */
 
 /* Replaces _C.mark_visible (DGR/rasterize_points.cu:401-420). present: uint8 [P]. */
