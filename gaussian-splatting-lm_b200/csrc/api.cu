@@ -256,12 +256,22 @@ int32_t gslm_jtjv_batch(const GslmGaussians* g, const GslmGaussians* gt, int32_t
     if (P == 0) return 0;
     TangentPtrs t = make_tangents(gt, nullptr);
     GslmGrads acc = *grads;
+    if (!acc.accumulate) {   // overwrite semantics = clear, then accumulate every view
+        const size_t n = (size_t)P;
+        struct { float* p; size_t count; } sinks[8] = {
+            {acc.dL_dmeans2D, 3 * n}, {acc.dL_dcolors, 3 * n}, {acc.dL_dopacity, n}, {acc.dL_dmeans3D, 3 * n},
+            {acc.dL_dcov3D, 6 * n}, {acc.dL_dsh, 3 * n * (size_t)g->M}, {acc.dL_dscales, 3 * n}, {acc.dL_drotations, 4 * n}};
+        for (auto& k : sinks)
+            if (k.p && k.count) GSLM_CUDA_OK(cudaMemsetAsync(k.p, 0, k.count * sizeof(float), s));
+        acc.accumulate = 1;
+    }
     for (int v0 = 0; v0 < n_views; v0 += MAX_BATCH_VIEWS) {
         const int n = (n_views - v0) < MAX_BATCH_VIEWS ? (n_views - v0) : MAX_BATCH_VIEWS;
         GeomView gv[MAX_BATCH_VIEWS];
         ImageView iv[MAX_BATCH_VIEWS];
         BinningView bv[MAX_BATCH_VIEWS];
-        float4 *tgeom[MAX_BATCH_VIEWS], *inst[MAX_BATCH_VIEWS];
+        float4* tgeom[MAX_BATCH_VIEWS];
+        float4* inst[MAX_BATCH_VIEWS];
         char* p = reinterpret_cast<char*>(align_up((size_t)scratch));
         for (int i = 0; i < n; i++) {
             const int v = v0 + i;
@@ -276,10 +286,7 @@ int32_t gslm_jtjv_batch(const GslmGaussians* g, const GslmGaussians* gt, int32_t
         if (launch_preprocess_tangent_batch(*g, t, n, cams + v0, gv, tgeom, s)) return 1;
         if (launch_blend_jtjv_batch(n, bv, iv, cams + v0, tgeom, weights ? weights + v0 : nullptr, inst, out_vJJv, s))
             return 1;
-        for (int i = 0; i < n; i++) {   // per view, in order: the sum over views is deterministic
-            if (launch_preprocess_bwd(*g, cams[v0 + i], radii[v0 + i], gv[i], bv[i], inst[i], false, acc, s)) return 1;
-            acc.accumulate = 1;
-        }
+        if (launch_preprocess_bwd_views(*g, n, cams + v0, radii + v0, gv, inst, acc, s)) return 1;
     }
     return 0;
 }

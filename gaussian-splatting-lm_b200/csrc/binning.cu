@@ -76,6 +76,7 @@ GeomView carve_geom(void* base, int P) {
     v.g_cursor = take<uint32_t>(p, n);
     v.active_ids = v.g_cursor;
     v.n_active = v.num_rendered + 1;
+    v.act_range = take<uint32_t>(p, n / ACT_RANGE + 2);
     v.scan_temp_bytes = scan_temp_bytes(P);
     v.scan_temp = take<char>(p, v.scan_temp_bytes);
     v.total = (size_t)(p - reinterpret_cast<char*>(base));
@@ -313,6 +314,22 @@ k_invert_glist(uint32_t Rc, const uint32_t* __restrict__ g_list, uint32_t* __res
     if (s < Rc) g_inv[g_list[s]] = s;
 }
 
+// act_range[r] = lower_bound(active_ids, ACT_RANGE * r): the slice of the active list a warp of the multi-view
+// adjoint stage visits in this view
+__global__ void __launch_bounds__(256)
+k_active_ranges(int nranges, const uint32_t* __restrict__ active_ids, const uint32_t* __restrict__ n_active,
+                uint32_t* __restrict__ act_range) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r > nranges) return;
+    const uint32_t n = *n_active, key = (uint32_t)r * ACT_RANGE;
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (active_ids[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    act_range[r] = lo;
+}
+
 struct HasInstances {   // Gaussian i has at least one compact instance in this view
     const uint32_t* g_off;
     __device__ __forceinline__ bool operator()(uint32_t i) const { return g_off[i + 1] > g_off[i]; }
@@ -355,6 +372,11 @@ int run_compaction(const GeomView& gv, const BinningView& bv, const BinningTemp&
         }
         size_t have2 = gv.scan_temp_bytes;
         GSLM_CUDA_OK(cub::DeviceSelect::If(gv.scan_temp, have2, ids, gv.active_ids, gv.n_active, P, pred, s));
+    }
+    {
+        const int nranges = (P + ACT_RANGE - 1) / ACT_RANGE;
+        k_active_ranges<<<(nranges + 1 + 255) / 256, 256, 0, s>>>(nranges, gv.active_ids, gv.n_active, gv.act_range);
+        GSLM_CUDA_OK(cudaGetLastError());
     }
     return 0;
 }

@@ -17,6 +17,7 @@ constexpr int TILE_X = 16, TILE_Y = 16;          // DGR/cuda_rasterizer/config.h
 constexpr int TILE_PIX = TILE_X * TILE_Y;        // 256 threads per tile CTA, one pixel each
 constexpr int BATCH = 256;                       // instances staged in shared memory per round
 constexpr int MAX_BATCH_VIEWS = 16;              // linearised views per batched launch (descriptors travel as kernel parameters)
+constexpr int ACT_RANGE = 256;                   // Gaussian ids per warp in the multi-view adjoint stage
 constexpr int REC_F4 = 3;                        // one instance record = 3 x float4 = 48 bytes
 
 // Instance record (one per (tile, Gaussian) pair, stored in tile|depth order so that a
@@ -53,6 +54,7 @@ struct GeomView {   // per-Gaussian state, SoA
     uint32_t* g_cursor;       // [P]   build-time counters / cursors of the CSR
     uint32_t* active_ids;     // [n_active <= P] ascending ids of the Gaussians with >= 1 compact instance (aliases g_cursor)
     uint32_t* n_active;       // [1]
+    uint32_t* act_range;      // [ceil(P / ACT_RANGE) + 1] act_range[r] = first slot of active_ids with id >= ACT_RANGE r
     char* scan_temp;
     size_t scan_temp_bytes;
     size_t total;
@@ -136,6 +138,10 @@ int launch_mark_visible(int P, const float* means3D, const float* viewmatrix, ui
 int launch_preprocess_bwd(const GslmGaussians& g, const GslmCamera& cam, const int32_t* radii, const GeomView& gv,
                           const BinningView& bv, const float4* inst_grads, bool has_invdepth_grad,
                           const GslmGrads& grads, cudaStream_t s);
+// accumulates the adjoints of up to MAX_BATCH_VIEWS views in ONE launch (deterministic, see preprocess_bwd.cu)
+int launch_preprocess_bwd_views(const GslmGaussians& g, int n_views, const GslmCamera* cams, const int32_t* const* radii,
+                                const GeomView* gvs, const float4* const* inst_grads, const GslmGrads& grads,
+                                cudaStream_t s);
 // binning.cu
 int run_scan(const GeomView& gv, int P, cudaStream_t s);
 int run_binning(const GeomView& gv, const int32_t* radii, const BinningTemp& bt, const ImageView& iv, int P, int W,

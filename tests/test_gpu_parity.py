@@ -192,8 +192,8 @@ def test_fused_jtjv_equals_vjp_of_jvp(C, name, deg, weighted):
 
 def test_jtjv_batch_equals_sum_of_views(C):
     """gslm_jtjv_batch over 19 views (two chunks of the 16-view launch limit, two image sizes, some weights None)
-    == the per-view fused calls accumulated in the same order: bit-identical (same kernels, same summation order),
-    in accumulate and in overwrite mode."""
+    == the per-view fused calls accumulated in the same order (to the last bits), in accumulate and in overwrite
+    mode, and bit-reproducible from run to run."""
     g = ss.make_gaussians(3000, sh_degree=2, seed=21, scale_mult=0.8)
     t = ss.random_tangent(g, seed=22)
     gd, td = h.to_dev(g), h.to_dev(t)
@@ -214,7 +214,15 @@ def test_jtjv_batch_equals_sum_of_views(C):
     plan = C.JtjvBatchPlan(views, torch.device("cuda"))
     out, quad = mk(), torch.zeros(1, device="cuda")
     C.jtjv_batch(h.gauss_args(gd), h.tangent_args(td), plan, out, out_vJJv=quad)
+    # same arithmetic and the same view order; the multi-view adjoint kernel is a different instantiation of the
+    # per-Gaussian adjoint, so multiply-adds may contract differently: last-bit differences only
     for a, b in zip(out, ref):
+        if a is not None:
+            assert h.relerr(a.cpu().numpy(), b.cpu().numpy()) < 1e-6
+    # run to run the batched path is bit-reproducible (no atomics anywhere on the gradient path)
+    again = mk()
+    C.jtjv_batch(h.gauss_args(gd), h.tangent_args(td), plan, again)
+    for a, b in zip(out, again):
         if a is not None:
             assert torch.equal(a, b)
     assert abs(float(quad) - float(quad_ref)) <= 1e-5 * abs(float(quad_ref))
