@@ -266,14 +266,32 @@ def main():
     if os.path.exists(pk):
         peaks = json.load(open(pk))
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    # algorithmic bytes of one k_blend_jtjv launch (DESIGN.md "kernels"): per CACHED instance 48 B primal record
-    # + 4 B id + 48 B gathered tangent record + 48 B gradient record out; per pixel n_contrib + final_T + 3 weights
+    # The dominant kernel is launched once per chunk of <= 16 views.  Algorithmic bytes of ONE launch (DESIGN.md
+    # "kernels"): per CACHED instance 48 B record + 32 B hit mask + 4 B id + 4 B gradient slot in, 48 B gathered
+    # tangent record in, 48 B gradient record out; per pixel final_T + 3 weights.
     n_local = max(len(F._views), 1)
-    alg_bytes = (R_cached * (48 + 4 + 48 + 48) + pix * (4 + 4 + 12)) / n_local
+    launches = max(jt_n // a.steps, 1)
+    alg_bytes = (R_cached * (48 + 32 + 4 + 4 + 48 + 48) + pix * (4 + 12)) / launches
     dur_s = (jt_ms / max(jt_n, 1)) * 1e-3
     achieved = alg_bytes / dur_s / 1e9 if dur_s > 0 else 0.0
     stage_share = {k: round(ms / a.steps, 4) for k, (ms, c) in stages.items() if c}
-
+    # what actually binds it: FP32 issue / FMA pipe.  Algorithmic flops: 24 per tested (pixel, instance)
+    # pair + 154 per hit, on the compact lists: tested = 256 per cached instance, hits = popcount of the hit masks.
+    hits = 0
+    for vc in F._views:
+        m = _C.buffer_view(P, vc.W, vc.H, vc.R, None, vc.binning, vc.img).get("masks")
+        if m is not None:
+            x = m.view(torch.uint8)
+            lut = torch.tensor([bin(i).count("1") for i in range(256)], dtype=torch.int64, device=dev)
+            hits += int(lut[x.long()].sum())
+    alg_flops = (24.0 * 256 * R_cached + 154.0 * hits) / launches
+    fp32_peak = 71.6   # TFLOP/s, scalar FFMA measured on this pool's B200 with tools/ffma2_bench.cu (profiles/r1_ffma2_bench.txt)
+    traffic = None
+    tj = os.path.join(ROOT, "profiles", "traffic.json")   # dram bytes of the same kernel from the ncu --set full capture
+    if os.path.exists(tj):
+        t = json.load(open(tj))
+        if t.get("kernel") == "k_blend_jtjv" and t.get("views_per_launch"):
+            traffic = t["dram_bytes_per_launch"] / t["views_per_launch"] * (n_local / launches)
     result = {
         "metric": METRIC, "value": 1e3 / ms_step, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
@@ -286,9 +304,13 @@ def main():
                 "d2h_bytes_per_step": 4 * n_flat},
         "gpu_launches": int(launches_per_step) * a.steps,
         "roofline": {"kernel": "k_blend_jtjv", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved / hbm_peak, "traffic": None,
+                     "frac": achieved / hbm_peak, "traffic": traffic,
                      "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s",
-                     "launch_ms": dur_s * 1e3, "alg_bytes_per_launch": alg_bytes},
+                     "launch_ms": dur_s * 1e3, "launches_per_step": launches, "alg_bytes_per_launch": alg_bytes,
+                     "binding_roof": {"bound": "fp32 (FMA pipe / issue slots; no tensor-core work on this path)",
+                                      "achieved": alg_flops / dur_s / 1e12 if dur_s > 0 else 0.0, "peak": fp32_peak,
+                                      "unit": "TFLOP/s", "frac": (alg_flops / dur_s / 1e12) / fp32_peak if dur_s > 0 else 0.0,
+                                      "alg_flops_per_launch": alg_flops, "pairs_hit_rank0": hits}},
         "stage_ms_per_step": stage_share,
     }
     if sampler:
