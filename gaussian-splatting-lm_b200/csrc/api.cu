@@ -58,7 +58,7 @@ int32_t gslm_abi_version(void) { return 1; }
 size_t gslm_geom_bytes(int32_t P) { return carve_geom(nullptr, P).total; }
 size_t gslm_image_bytes(int32_t width, int32_t height) { return carve_image(nullptr, width, height).total; }
 size_t gslm_binning_bytes(int64_t Rc) { return carve_binning(nullptr, Rc).total; }
-size_t gslm_binning_temp_bytes(int64_t R) { return carve_binning_temp(nullptr, R).total; }
+size_t gslm_binning_temp_bytes(int32_t P, int64_t R) { return carve_binning_temp(nullptr, R, P).total; }
 size_t gslm_backward_scratch_bytes(int64_t Rc) { return align_up((size_t)Rc * REC_F4 * sizeof(float4)) + 128; }
 size_t gslm_jvp_scratch_bytes(int32_t P) { return align_up((size_t)P * REC_F4 * sizeof(float4)) + 128; }
 size_t gslm_jtjv_scratch_bytes(int32_t P, int64_t Rc) {
@@ -98,9 +98,9 @@ int32_t gslm_forward(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn 
         GSLM_CUDA_OK(cudaStreamSynchronize(s));
     }
     *num_rendered = (int32_t)R;
-    void* tbuf = alloc(alloc_ctx, GSLM_BUF_BINNING_TEMP, gslm_binning_temp_bytes(R));
+    void* tbuf = alloc(alloc_ctx, GSLM_BUF_BINNING_TEMP, gslm_binning_temp_bytes(P, R));
     if (!tbuf) { set_error("allocator returned null"); return 1; }
-    BinningTemp bt = carve_binning_temp(tbuf, R);
+    BinningTemp bt = carve_binning_temp(tbuf, R, P);
     if (run_binning(gv, radii, bt, iv, P, W, H, R, s)) return 1;
     if (debug_sync(cam, s, "binning")) return 1;
     const float* features = g->colors_precomp ? g->colors_precomp : gv.rgb;
@@ -164,7 +164,7 @@ int32_t gslm_forward_jvp(const GslmGaussians* g, const GslmGaussians* gt, const 
     // forward pass has returned, when it fits; otherwise one more scratch allocation (which = -1)
     float4* tgeom = nullptr;
     const size_t need = gslm_jvp_scratch_bytes(P);
-    if (cap.p[GSLM_BUF_BINNING_TEMP] && gslm_binning_temp_bytes(*num_rendered) >= need)
+    if (cap.p[GSLM_BUF_BINNING_TEMP] && gslm_binning_temp_bytes(P, *num_rendered) >= need)
         tgeom = reinterpret_cast<float4*>(cap.p[GSLM_BUF_BINNING_TEMP]);
     else {
         void* extra = alloc(alloc_ctx, -1, need);
@@ -309,8 +309,8 @@ int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_r
         out->masks = reinterpret_cast<const uint32_t*>(bv.masks);
     }
     if (binning_temp_buffer) {
-        BinningTemp bt = carve_binning_temp(const_cast<void*>(binning_temp_buffer), num_rendered);
-        out->keys_sorted = bt.keys_sorted; out->point_list = bt.point_list;
+        BinningTemp bt = carve_binning_temp(const_cast<void*>(binning_temp_buffer), num_rendered, P);
+        out->tile_keys_sorted = bt.keys_sorted; out->point_list = bt.point_list;
     }
     if (image_buffer) {
         ImageView iv = carve_image(const_cast<void*>(image_buffer), width, height);

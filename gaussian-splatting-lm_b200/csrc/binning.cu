@@ -45,12 +45,11 @@ size_t scan_temp_bytes(int P) {
     // touching the device so that size queries work on a machine without a GPU.
     return align_up((size_t)(P / 128 + 1024) * 16 + 4096);
 }
-size_t sort_temp_bytes(int64_t R) {
-    // cub::DeviceRadixSort (non-DoubleBuffer overload) needs one alternate key and value buffer
-    // (12 B / item) plus the onesweep look-back table: 256 counters x 4 B per tile of >= 2048 items
-    // (<= 0.5 B / item; measured 0.18 B / item at R = 19.8 M) plus per-pass histograms.  The bound
-    // is checked against CUB's own answer at run time.
-    return align_up((size_t)R * (sizeof(uint64_t) + sizeof(uint32_t)) + (size_t)R / 2 + ((size_t)1 << 20));
+size_t sort_temp_bytes(int64_t n) {
+    // cub::DeviceRadixSort (non-DoubleBuffer overload) on (u32 key, u32 value) pairs needs one alternate key and
+    // value buffer (8 B / item) plus the onesweep look-back table: 256 counters x 4 B per tile of >= 2048 items
+    // (<= 0.5 B / item) plus per-pass histograms.  The bound is checked against CUB's own answer at run time.
+    return align_up((size_t)n * (2 * sizeof(uint32_t)) + (size_t)n / 2 + ((size_t)1 << 20));
 }
 
 template <class T> static T* take(char*& p, size_t n) {
@@ -74,6 +73,8 @@ GeomView carve_geom(void* base, int P) {
     v.num_rendered = take<uint32_t>(p, 32);
     v.g_off = take<uint32_t>(p, n + 1);
     v.g_cursor = take<uint32_t>(p, n);
+    v.depth_sorted = take<uint32_t>(p, n);
+    v.depth_perm = take<uint32_t>(p, n);
     v.active_ids = v.g_cursor;
     v.n_active = v.num_rendered + 1;
     v.act_range = take<uint32_t>(p, n / ACT_RANGE + 2);
@@ -107,17 +108,17 @@ BinningView carve_binning(void* base, int64_t Rc) {
     v.total = (size_t)(p - reinterpret_cast<char*>(base));
     return v;
 }
-BinningTemp carve_binning_temp(void* base, int64_t R) {
+BinningTemp carve_binning_temp(void* base, int64_t R, int P) {
     BinningTemp v;
     char* p = reinterpret_cast<char*>(base);
     size_t n = (size_t)R;
-    v.keys_sorted = take<uint64_t>(p, n);
-    v.keys_unsorted = take<uint64_t>(p, n);
+    v.keys_sorted = take<uint32_t>(p, n);
+    v.keys_unsorted = take<uint32_t>(p, n);
     v.vals_unsorted = take<uint32_t>(p, n);
     v.point_list = take<uint32_t>(p, n);
     v.records_tmp = take<float4>(p, REC_F4 * n);
     v.masks_tmp = take<uint4>(p, 2 * n);
-    v.sort_temp_bytes = sort_temp_bytes(R);
+    v.sort_temp_bytes = sort_temp_bytes(R > P ? R : (int64_t)P);   // the same scratch serves the depth sort over P items
     v.sort_temp = take<char>(p, v.sort_temp_bytes);
     v.total = (size_t)(p - reinterpret_cast<char*>(base));
     return v;
@@ -136,41 +137,63 @@ int run_scan(const GeomView& gv, int P, cudaStream_t s) {
     return 0;
 }
 
-// rasterizer_impl.cu:70-111. One thread per Gaussian; the rect is recomputed from the
-// stored pixel centre and radius exactly as the reference does (:91).
+// ---------------------------------------------------------------------------------------------
+// The reference sorts R (tile << 32 | depth bits) keys with a stable LSD radix sort over 32 + msb(T) bits (6 passes
+// of 12 B per instance at 1080p).  The same order comes out of a two-level sort that moves a third of the bytes:
+//   1. sort the P Gaussians by depth bits, stably from ascending id  (4 passes over P << R items);
+//   2. emit the instances in THAT order with the tile id alone as key;
+//   3. sort them stably by tile id                                  (2 passes of 8 B per instance).
+// Within a tile the instances then appear by (depth, id) -- exactly the reference's order: its ties in (tile, depth)
+// keep emission order, which is ascending Gaussian id (rasterizer_impl.cu:70-111, :346-354).  Bit-exact
+// point_list and ranges are asserted against the reference fixture and the reference's own kernels in tests/.
+// ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-k_duplicate_keys(int P, const float2* __restrict__ xy, const float* __restrict__ depths,
-                 const uint32_t* __restrict__ offsets, const int32_t* __restrict__ radii, int gx, int gy,
-                 uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+k_depth_keys(int P, const float* __restrict__ depths, const int32_t* __restrict__ radii, uint32_t* __restrict__ dkey,
+             uint32_t* __restrict__ iota) {
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P) return;
+    dkey[idx] = radii[idx] > 0 ? __float_as_uint(depths[idx]) : 0xffffffffu;   // depths > 0.2: bits are monotone
+    iota[idx] = (uint32_t)idx;
+}
+__global__ void __launch_bounds__(256)
+k_gather_tiles(int P, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ tiles_touched,
+               uint32_t* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < P) out[i] = tiles_touched[perm[i]];
+}
+
+// rasterizer_impl.cu:70-111, in depth order. One thread per Gaussian; the rect is recomputed from the stored pixel
+// centre and radius exactly as the reference does (:91).
+__global__ void __launch_bounds__(256)
+k_duplicate_keys(int P, const uint32_t* __restrict__ perm, const float2* __restrict__ xy,
+                 const uint32_t* __restrict__ offsets, const int32_t* __restrict__ radii, int gx, int gy,
+                 uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const uint32_t idx = perm[i];
     int rad = radii[idx];
     if (rad <= 0) return;
-    uint32_t off = idx == 0 ? 0u : offsets[idx - 1];
+    uint32_t off = offsets[i];
     float2 p = xy[idx];
     int x0, y0, x1, y1;
     tile_rect(p.x, p.y, rad, gx, gy, x0, y0, x1, y1);
-    const uint64_t dbits = (uint64_t)__float_as_uint(depths[idx]);
     for (int y = y0; y < y1; y++)
         for (int x = x0; x < x1; x++) {
-            uint64_t key = (uint64_t)(uint32_t)(y * gx + x);
-            key <<= 32;
-            key |= dbits;
-            keys[off] = key;
-            vals[off] = (uint32_t)idx;
+            keys[off] = (uint32_t)(y * gx + x);
+            vals[off] = idx;
             off++;
         }
 }
 
 // rasterizer_impl.cu:116-138; ranges are zero-filled first (:356)
 __global__ void __launch_bounds__(256)
-k_tile_ranges(uint32_t L, const uint64_t* __restrict__ keys, uint2* __restrict__ ranges) {
+k_tile_ranges(uint32_t L, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges) {
     uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= L) return;
-    uint32_t cur = (uint32_t)(keys[idx] >> 32);
+    uint32_t cur = keys[idx];
     if (idx == 0) ranges[cur].x = 0;
     else {
-        uint32_t prev = (uint32_t)(keys[idx - 1] >> 32);
+        uint32_t prev = keys[idx - 1];
         if (cur != prev) {
             ranges[prev].y = idx;
             ranges[cur].x = idx;
@@ -179,28 +202,48 @@ k_tile_ranges(uint32_t L, const uint64_t* __restrict__ keys, uint2* __restrict__
     if (idx == L - 1) ranges[cur].y = L;
 }
 
-int run_binning(const GeomView& gv, const int32_t* radii, const BinningTemp& bt, const ImageView& iv, int P, int W,
-                int H, int64_t R, cudaStream_t s) {
-    const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
-    GSLM_CUDA_OK(cudaMemsetAsync(iv.ranges, 0, sizeof(uint2) * (size_t)gx * gy, s));
-    if (R == 0 || P == 0) return 0;
-    stage_begin(ST_KEYS, s);
-    k_duplicate_keys<<<(P + 255) / 256, 256, 0, s>>>(P, gv.means2D, gv.depths, gv.point_offsets, radii, gx, gy,
-                                                     bt.keys_unsorted, bt.vals_unsorted);
-    stage_end(ST_KEYS, s);
-    GSLM_CUDA_OK(cudaGetLastError());
-    const int bit = (int)higher_msb((uint32_t)(gx * gy));
+static int sort_pairs_u32(const BinningTemp& bt, const uint32_t* kin, uint32_t* kout, const uint32_t* vin, uint32_t* vout,
+                          int64_t n, int end_bit, cudaStream_t s) {
     size_t need = 0;
-    GSLM_CUDA_OK(cub::DeviceRadixSort::SortPairs(nullptr, need, bt.keys_unsorted, bt.keys_sorted, bt.vals_unsorted,
-                                                 bt.point_list, (int)R, 0, 32 + bit, s));
+    GSLM_CUDA_OK(cub::DeviceRadixSort::SortPairs(nullptr, need, kin, kout, vin, vout, (int)n, 0, end_bit, s));
     if (need > bt.sort_temp_bytes) {
         set_error("sort temp storage too small: need %zu have %zu", need, bt.sort_temp_bytes);
         return 1;
     }
     size_t have = bt.sort_temp_bytes;
+    GSLM_CUDA_OK(cub::DeviceRadixSort::SortPairs(bt.sort_temp, have, kin, kout, vin, vout, (int)n, 0, end_bit, s));
+    return 0;
+}
+
+int run_binning(const GeomView& gv, const int32_t* radii, const BinningTemp& bt, const ImageView& iv, int P, int W,
+                int H, int64_t R, cudaStream_t s) {
+    const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    GSLM_CUDA_OK(cudaMemsetAsync(iv.ranges, 0, sizeof(uint2) * (size_t)gx * gy, s));
+    if (R == 0 || P == 0) return 0;
+    // g_off / g_cursor are free until compaction: depth keys and the identity permutation live there
+    uint32_t* dkey = gv.g_off;
+    uint32_t* iota = gv.g_cursor;
+    stage_begin(ST_KEYS, s);
+    k_depth_keys<<<(P + 255) / 256, 256, 0, s>>>(P, gv.depths, radii, dkey, iota);
+    GSLM_CUDA_OK(cudaGetLastError());
+    stage_end(ST_KEYS, s);
     stage_begin(ST_SORT, s);
-    GSLM_CUDA_OK(cub::DeviceRadixSort::SortPairs(bt.sort_temp, have, bt.keys_unsorted, bt.keys_sorted,
-                                                 bt.vals_unsorted, bt.point_list, (int)R, 0, 32 + bit, s));
+    if (sort_pairs_u32(bt, dkey, gv.depth_sorted, iota, gv.depth_perm, P, 32, s)) return 1;
+    stage_end(ST_SORT, s);
+    stage_begin(ST_KEYS, s);
+    uint32_t* tt_sorted = dkey;      // tiles_touched in depth order, then its exclusive scan = emission offsets
+    uint32_t* toff = iota;
+    k_gather_tiles<<<(P + 255) / 256, 256, 0, s>>>(P, gv.depth_perm, gv.tiles_touched, tt_sorted);
+    GSLM_CUDA_OK(cudaGetLastError());
+    size_t have = gv.scan_temp_bytes;
+    GSLM_CUDA_OK(cub::DeviceScan::ExclusiveSum(gv.scan_temp, have, tt_sorted, toff, P, s));
+    k_duplicate_keys<<<(P + 255) / 256, 256, 0, s>>>(P, gv.depth_perm, gv.means2D, toff, radii, gx, gy,
+                                                     bt.keys_unsorted, bt.vals_unsorted);
+    stage_end(ST_KEYS, s);
+    GSLM_CUDA_OK(cudaGetLastError());
+    const int bit = (int)higher_msb((uint32_t)(gx * gy));
+    stage_begin(ST_SORT, s);
+    if (sort_pairs_u32(bt, bt.keys_unsorted, bt.keys_sorted, bt.vals_unsorted, bt.point_list, R, bit, s)) return 1;
     stage_end(ST_SORT, s);
     const uint32_t L = (uint32_t)R;
     StageScope ts(ST_RANGES, s);
@@ -263,7 +306,7 @@ __global__ void __launch_bounds__(256)
 k_compact_copy(const uint2* __restrict__ ranges, const uint32_t* __restrict__ cstart,
                const uint32_t* __restrict__ ccount, const float4* __restrict__ src, const uint4* __restrict__ msrc,
                float4* __restrict__ dst, uint4* __restrict__ mdst, uint32_t* __restrict__ cid,
-               uint32_t* __restrict__ g_cnt) {
+               uint32_t* __restrict__ cpos, uint32_t* __restrict__ g_cnt) {
     const int tile = blockIdx.x;
     const uint32_t n = ccount[tile];
     if (n == 0) return;
@@ -279,7 +322,9 @@ k_compact_copy(const uint2* __restrict__ ranges, const uint32_t* __restrict__ cs
         } else {
             const uint32_t id = __float_as_uint(q.z);
             q.w = src[s0 + i - 1].y;   // opacity
-            cid[cstart[tile] + i / REC_F4] = id;
+            const uint32_t c = cstart[tile] + i / REC_F4;
+            cid[c] = id;
+            cpos[c] = c;
             atomicAdd(&g_cnt[id], 1u);
         }
         dst[d0 + i] = q;
@@ -287,27 +332,6 @@ k_compact_copy(const uint2* __restrict__ ranges, const uint32_t* __restrict__ cs
     const size_t ms0 = (size_t)ranges[tile].x * 2, md0 = (size_t)cstart[tile] * 2;
     for (uint32_t i = threadIdx.x; i < n * 2; i += blockDim.x) mdst[md0 + i] = msrc[ms0 + i];
 }
-__global__ void __launch_bounds__(256)
-k_fill_glist(uint32_t Rc, const uint32_t* __restrict__ cid, uint32_t* __restrict__ g_cursor, uint32_t* __restrict__ g_list) {
-    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= Rc) return;
-    g_list[atomicAdd(&g_cursor[cid[c]], 1u)] = c;
-}
-// atomics hand out slots in arbitrary order: sort every Gaussian's (short) list so that the
-// gradient gather always sums in the same order => deterministic gradients
-__global__ void __launch_bounds__(256)
-k_sort_glist(int P, const uint32_t* __restrict__ g_off, uint32_t* __restrict__ g_list) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= P) return;
-    const uint32_t b = g_off[i], e = g_off[i + 1];
-    for (uint32_t k = b + 1; k < e; k++) {
-        const uint32_t x = g_list[k];
-        uint32_t j = k;
-        while (j > b && g_list[j - 1] > x) { g_list[j] = g_list[j - 1]; j--; }
-        g_list[j] = x;
-    }
-}
-
 __global__ void __launch_bounds__(256)
 k_invert_glist(uint32_t Rc, const uint32_t* __restrict__ g_list, uint32_t* __restrict__ g_inv) {
     const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
@@ -343,18 +367,18 @@ int run_compaction(const GeomView& gv, const BinningView& bv, const BinningTemp&
     GSLM_CUDA_OK(cudaMemsetAsync(gv.g_off, 0, sizeof(uint32_t), s));
     if (Rc > 0) {
         k_compact_copy<<<T, 256, 0, s>>>(iv.ranges, iv.cstart, iv.ccount, bt.records_tmp, bt.masks_tmp, bv.records, bv.masks,
-                                         bv.cid, gv.g_cursor);
+                                         bv.cid, bt.vals_unsorted, gv.g_cursor);
         GSLM_CUDA_OK(cudaGetLastError());
     }
     // g_off[1..P] = inclusive scan of the counts (the forward pass's scan scratch is free again)
     size_t have = gv.scan_temp_bytes;
     GSLM_CUDA_OK(cub::DeviceScan::InclusiveSum(gv.scan_temp, have, gv.g_cursor, gv.g_off + 1, P, s));
     if (Rc > 0) {
-        GSLM_CUDA_OK(cudaMemcpyAsync(gv.g_cursor, gv.g_off, sizeof(uint32_t) * (size_t)P, cudaMemcpyDeviceToDevice, s));
-        k_fill_glist<<<(unsigned)((Rc + 255) / 256), 256, 0, s>>>((uint32_t)Rc, bv.cid, gv.g_cursor, bv.g_list);
-        GSLM_CUDA_OK(cudaGetLastError());
-        k_sort_glist<<<(P + 255) / 256, 256, 0, s>>>(P, gv.g_off, bv.g_list);
-        GSLM_CUDA_OK(cudaGetLastError());
+        // CSR payload: compact positions grouped by Gaussian, ascending inside a group = a STABLE sort of the positions
+        // by Gaussian id (deterministic; the sort scratch of the forward pass is free again)
+        int bits = 1;
+        while (bits < 32 && (1u << bits) < (uint32_t)P) bits++;
+        if (sort_pairs_u32(bt, bv.cid, bt.keys_unsorted, bt.vals_unsorted, bv.g_list, Rc, bits, s)) return 1;
         k_invert_glist<<<(unsigned)((Rc + 255) / 256), 256, 0, s>>>((uint32_t)Rc, bv.g_list, bv.g_inv);
         GSLM_CUDA_OK(cudaGetLastError());
     }

@@ -54,6 +54,8 @@ struct GeomView {   // per-Gaussian state, SoA
     uint32_t* g_cursor;       // [P]   build-time counters / cursors of the CSR
     uint32_t* active_ids;     // [n_active <= P] ascending ids of the Gaussians with >= 1 compact instance (aliases g_cursor)
     uint32_t* n_active;       // [1]
+    uint32_t* depth_sorted;   // [P] binning scratch: depth keys in ascending order
+    uint32_t* depth_perm;     // [P] binning scratch: Gaussian ids in (depth, id) order (invisible ones last)
     uint32_t* act_range;      // [ceil(P / ACT_RANGE) + 1] act_range[r] = first slot of active_ids with id >= ACT_RANGE r
     char* scan_temp;
     size_t scan_temp_bytes;
@@ -76,10 +78,10 @@ struct BinningView {  // compact per-instance state that outlives the forward pa
     uint32_t* g_inv;          // [Rc] inverse of g_list: compact position -> CSR slot (where the tile kernels put its gradient record)
     size_t total;
 };
-struct BinningTemp {  // per-instance state that is dead once the forward pass returns (116 B / instance + sort temporaries)
-    uint64_t* keys_sorted;    // [R]
-    uint64_t* keys_unsorted;  // [R]
-    uint32_t* vals_unsorted;  // [R]
+struct BinningTemp {  // per-instance state that is dead once the forward pass returns (96 B / instance + sort temporaries)
+    uint32_t* keys_sorted;    // [R] tile ids in sorted order
+    uint32_t* keys_unsorted;  // [R] tile ids in emission order
+    uint32_t* vals_unsorted;  // [R] Gaussian ids in emission order
     uint32_t* point_list;     // [R] sorted Gaussian ids (BinningState::point_list)
     float4* records_tmp;      // [3R] compact records at tile-local positions (range.x + j), before the global scan
     uint4* masks_tmp;         // [2R] their hit masks, same positions
@@ -89,11 +91,11 @@ struct BinningTemp {  // per-instance state that is dead once the forward pass r
 };
 
 size_t scan_temp_bytes(int P);
-size_t sort_temp_bytes(int64_t R);
+size_t sort_temp_bytes(int64_t n);
 GeomView carve_geom(void* base, int P);
 ImageView carve_image(void* base, int W, int H);
 BinningView carve_binning(void* base, int64_t Rc);
-BinningTemp carve_binning_temp(void* base, int64_t R);
+BinningTemp carve_binning_temp(void* base, int64_t R, int P);
 
 void set_error(const char* fmt, ...);
 const char* last_error();

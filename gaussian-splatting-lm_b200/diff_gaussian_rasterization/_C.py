@@ -40,7 +40,7 @@ class GslmGrads(C.Structure):
 
 
 class GslmBufferView(C.Structure):
-    _fields_ = [(n, C.c_void_p) for n in ("point_list", "keys_sorted", "ranges", "n_contrib", "final_T",
+    _fields_ = [(n, C.c_void_p) for n in ("point_list", "tile_keys_sorted", "ranges", "n_contrib", "final_T",
                                           "tiles_touched", "point_offsets", "depths", "means2D", "conic_opacity",
                                           "rgb", "cov3D", "clamped", "n_contrib_c", "cstart", "records", "masks", "cid",
                                           "g_off", "g_list")]
@@ -95,7 +95,7 @@ def lib():
         L.gslm_geom_bytes.argtypes = [C.c_int32]
         L.gslm_image_bytes.argtypes = [C.c_int32, C.c_int32]
         L.gslm_binning_bytes.argtypes = [C.c_int64]
-        L.gslm_binning_temp_bytes.argtypes = [C.c_int64]
+        L.gslm_binning_temp_bytes.argtypes = [C.c_int32, C.c_int64]
         L.gslm_backward_scratch_bytes.argtypes = [C.c_int64]
         L.gslm_jvp_scratch_bytes.argtypes = [C.c_int32]
         L.gslm_jtjv_scratch_bytes.argtypes = [C.c_int32, C.c_int64]
@@ -155,13 +155,34 @@ class _Alloc:
         self.cb = ALLOC_FN(self._alloc)
 
     def _alloc(self, _ctx, which, nbytes):
-        t = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=self.device)
-        self.bufs[int(which)] = t
+        which, nbytes = int(which), max(int(nbytes), 1)
+        if which == 3:
+            # sort scratch: dead when the call returns, so ONE grow-only buffer per (device, stream) serves every
+            # forward call (stream order makes the reuse safe); a fresh multi-GB torch.empty per view costs
+            # milliseconds of allocator work and fragments the cache
+            key = (self.device, _stream())
+            t = _SORT_SCRATCH.get(key)
+            if t is None or t.numel() < nbytes:
+                _SORT_SCRATCH.pop(key, None)
+                t = None
+                t = torch.empty(nbytes + nbytes // 4, dtype=torch.uint8, device=self.device)
+                _SORT_SCRATCH[key] = t
+        else:
+            t = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        self.bufs[which] = t
         return t.data_ptr()
 
     def get(self, which):
         t = self.bufs.get(which)
         return t if t is not None else torch.empty(0, dtype=torch.uint8, device=self.device)
+
+
+_SORT_SCRATCH = {}            # (device, stream) -> grow-only uint8 tensor
+
+
+def release_scratch():
+    """Drop the cached sort scratch (e.g. before handing the memory to another phase)."""
+    _SORT_SCRATCH.clear()
 
 
 KEEP_SORT_SCRATCH = False     # tests: keep the sort scratch (sorted keys) of the last forward call alive
@@ -458,7 +479,7 @@ def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer, sortScratch=
         out["cid"] = view(binningBuffer, v.cid, 4 * Rc, torch.int32, (Rc,))
         out["g_list"] = view(binningBuffer, v.g_list, 4 * Rc, torch.int32, (Rc,))
     if sortScratch is not None and sortScratch.numel() and R > 0:
-        out["keys_sorted"] = view(sortScratch, v.keys_sorted, 8 * R, torch.int64, (R,))
+        out["tile_keys_sorted"] = view(sortScratch, v.tile_keys_sorted, 4 * R, torch.int32, (R,))
         out["point_list"] = view(sortScratch, v.point_list, 4 * R, torch.int32, (R,))
     if imageBuffer is not None and imageBuffer.numel():
         out["ranges"] = view(imageBuffer, v.ranges, 8 * T, torch.int32, (T, 2))
@@ -472,6 +493,10 @@ def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer, sortScratch=
         out["depths"] = view(geomBuffer, v.depths, 4 * P, torch.float32, (P,))
         out["means2D"] = view(geomBuffer, v.means2D, 8 * P, torch.float32, (P, 2))
         out["conic_opacity"] = view(geomBuffer, v.conic_opacity, 16 * P, torch.float32, (P, 4))
+        if "tile_keys_sorted" in out:
+            # the reference's 64-bit sort key (rasterizer_impl.cu:97-103): tile << 32 | depth bits of the instance
+            dbits = out["depths"].view(torch.int32)[out["point_list"].long()].long() & 0xffffffff
+            out["keys_sorted"] = (out["tile_keys_sorted"].long() << 32) | dbits
         out["rgb"] = view(geomBuffer, v.rgb, 12 * P, torch.float32, (P, 3))
         out["cov3D"] = view(geomBuffer, v.cov3D, 24 * P, torch.float32, (P, 6))
         out["clamped"] = view(geomBuffer, v.clamped, P, torch.uint8, (P,))

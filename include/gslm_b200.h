@@ -103,7 +103,7 @@ int32_t gslm_abi_version(void);
 size_t gslm_geom_bytes(int32_t P);
 size_t gslm_image_bytes(int32_t width, int32_t height);
 size_t gslm_binning_bytes(int64_t num_cached);        /* persistent compact cache: 92 B / cached instance */
-size_t gslm_binning_temp_bytes(int64_t num_rendered); /* sort scratch: ~128 B / rendered instance, dead after forward */
+size_t gslm_binning_temp_bytes(int32_t P, int64_t num_rendered); /* sort scratch: ~105 B / rendered instance, dead after forward */
 
 /* Replaces _C.mark_visible (DGR/rasterize_points.cu:401-420). present: uint8 [P]. */
 int32_t gslm_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
@@ -189,7 +189,8 @@ int32_t gslm_timing_collect(float* ms, int32_t* counts);
 /* Introspection for tests (bit-exact binning checks): device pointers INTO the buffers. */
 typedef struct GslmBufferView {
     const uint32_t* point_list;   /* [R] sorted Gaussian ids (BinningState::point_list; lives in the sort scratch) */
-    const uint64_t* keys_sorted;  /* [R] tile<<32 | depth bits (sort scratch)                           */
+    const uint32_t* tile_keys_sorted; /* [R] tile id of every sorted instance (sort scratch); the reference's 64-bit key is
+                                       * tile << 32 | depth bits of point_list[i]                        */
     const uint32_t* ranges;       /* [T,2] per-tile [start,end) in the full list (ImageState::ranges)   */
     const uint32_t* n_contrib;    /* [H*W] reference numbering                                          */
     const float* final_T;         /* [H*W]                                                              */
