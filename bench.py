@@ -241,10 +241,14 @@ def main():
     v_host.copy_(v.packed().cpu())
     out_host = torch.empty(n_flat, dtype=torch.float32).pin_memory()
 
+    moved = [0, 0]
+
     def e2e_step():
-        v.packed().copy_(v_host, non_blocking=True)
+        # parameter-space vectors are replicated over ranks: every rank moves 1/N of v over its own PCIe link and
+        # one all_gather over NVLink completes it; the result goes back the same way (each rank its slice)
+        moved[0] = F.state_from_host(v_host, v)
         out = F.normal_matvec(v)
-        out_host.copy_(out.packed(), non_blocking=True)
+        moved[1] = F.state_to_host(out, out_host)
 
     for _ in range(max(1, a.warmup // 2)):
         e2e_step()
@@ -301,7 +305,8 @@ def main():
                    "l2_policy": "inputs larger than L2 (per-view records + gradients >> 126 MB)",
                    "linearize_ms": round(linearize_ms, 2), "mask_xyz": bool(a.mask_xyz)},
         "e2e": {"value": 1e3 / ms_e2e, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": 4 * n_flat,
-                "d2h_bytes_per_step": 4 * n_flat},
+                "d2h_bytes_per_step": 4 * n_flat, "per_rank_bytes": moved,
+                "staging": "each rank copies 1/N of the replicated vector from pinned host memory + all_gather; result slices back"},
         "gpu_launches": int(launches_per_step) * a.steps,
         "roofline": {"kernel": "k_blend_jtjv", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": traffic,

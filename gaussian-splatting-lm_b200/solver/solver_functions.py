@@ -165,6 +165,44 @@ class LinearSolverFunctions:
     def saxpy(self, a, x, y):
         return a * x + y
 
+    # ------------------------------------------------------------------ host staging of parameter-space vectors
+    # (additive; bench.py's end-to-end leg).  Parameter-space vectors are replicated over ranks, so with N ranks each
+    # rank moves only 1/N of the bytes over its own PCIe link and NVLink does the rest.
+    def _shard(self, n):
+        d = self.dist
+        world, rank = (d.get_world_size(), d.get_rank()) if d else (1, 0)
+        per = (n + world - 1) // world
+        return world, rank, per
+
+    def state_from_host(self, host_flat, state):
+        """state.packed() <- host_flat (pinned float32 [n], the same on every rank): each rank copies its 1/N
+        slice host->device, then ONE all_gather over NVLink.  Returns the bytes this rank copied."""
+        flat = state.packed()
+        n = flat.numel()
+        world, rank, per = self._shard(n)
+        if world == 1:
+            flat.copy_(host_flat, non_blocking=True)
+            return 4 * n
+        if getattr(self, "_stage", None) is None or self._stage.numel() != per * world:
+            self._stage = torch.empty(per * world, dtype=torch.float32, device=flat.device)
+        lo, hi = rank * per, min((rank + 1) * per, n)
+        mine = self._stage[rank * per:(rank + 1) * per]
+        if hi > lo:
+            mine[:hi - lo].copy_(host_flat[lo:hi], non_blocking=True)
+        self.dist.all_gather_into_tensor(self._stage, mine)
+        flat.copy_(self._stage[:n])
+        return 4 * max(hi - lo, 0)
+
+    def state_to_host(self, state, host_flat):
+        """host_flat[lo:hi] <- this rank's 1/N slice of the (replicated) state; returns the bytes copied."""
+        flat = state.packed()
+        n = flat.numel()
+        world, rank, per = self._shard(n)
+        lo, hi = rank * per, min((rank + 1) * per, n)
+        if hi > lo:
+            host_flat[lo:hi].copy_(flat[lo:hi], non_blocking=True)
+        return 4 * max(hi - lo, 0)
+
     # ------------------------------------------------------------------ cached mode
     def _kw(self, name, default=None):
         return self.loss_func.keywords.get(name, default)

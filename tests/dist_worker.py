@@ -35,6 +35,16 @@ def main():
     chk = a.packed().clone()
     dist.broadcast(chk, 0)
     assert torch.equal(chk, a.packed())
+    # host staging helpers: 1/N slices + all_gather reproduce the vector; slices of the result tile the host copy
+    host = torch.arange(v.length, dtype=torch.float32) * 0.5
+    w = GaussianModelState.from_gaussians(m)
+    moved = sharded.state_from_host(host, w)
+    assert torch.equal(w.packed(), host) and moved <= 4 * ((v.length + world - 1) // world)
+    back = torch.full((v.length,), -1.0)
+    sharded.state_to_host(w, back)
+    per = (v.length + world - 1) // world
+    lo, hi = rank * per, min((rank + 1) * per, v.length)
+    assert torch.equal(back[lo:hi], host[lo:hi]) and (back[:lo] == -1).all() and (back[hi:] == -1).all()
     dist.barrier()
     if rank == 0:
         print("DIST_OK")
