@@ -193,6 +193,9 @@ def _after_forward(al):
     global LAST_SORT_SCRATCH
     if KEEP_SORT_SCRATCH:
         LAST_SORT_SCRATCH = al.bufs.get(3)
+    # al -> cb -> bound method -> al is a reference cycle: without this the three buffers of every call would stay
+    # alive until the cycle collector runs, and every forward would cudaMalloc fresh blocks (measured: 6 ms per call)
+    al.cb = None
 
 
 def _gaussians(means3D, colors_precomp, opacities, scales, rotations, scale_modifier, cov3D_precomp, sh, degree):
