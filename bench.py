@@ -52,13 +52,17 @@ def parse():
     ap.add_argument("--points", type=int, default=0, help="override the number of Gaussians")
     ap.add_argument("--sh-degree", type=int, default=3)
     ap.add_argument("--mask-xyz", action="store_true", help="zero the xyz tangent like train_jvp.py:221-227")
+    ap.add_argument("--ssim", action="store_true",
+                    help="secondary workload: the full L1 + SSIM residual (disable_ssim=False): J^T J v runs as tangent "
+                         "tile kernel -> loss-block JVP / VJP kernels -> adjoint tile kernel (no CPU leg)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample-views", type=int, default=0, help="views in the CPU sample (0 = auto)")
     return ap.parse_args()
 
 
 def workload_name(a, P, V, W, H):
-    return f"config {a.config}: {P} Gaussians x {V} views at {W}x{H}, SH degree {a.sh_degree}, J^T J v (disable_ssim residual)"
+    resid = "L1 + SSIM residual, lambda_dssim 0.2" if a.ssim else "disable_ssim residual"
+    return f"config {a.config}: {P} Gaussians x {V} views at {W}x{H}, SH degree {a.sh_degree}, J^T J v ({resid})"
 
 
 # --------------------------------------------------------------------------------------- CPU arm
@@ -182,8 +186,9 @@ def main():
     pipe = SimpleNamespace(debug=False, antialiasing=False, compute_cov3D_python=False, convert_SHs_python=False)
     loss_func = functools.partial(batch_training_loss, iteration=1, opt=SimpleNamespace(lambda_dssim=0.2), pipe=pipe,
                                   bg=torch.zeros(3, device=dev), train_test_exp=False,
-                                  depth_l1_weight=lambda it: 0.0, disable_ssim=True)
-    F = LinearSolverFunctions(loss_func, model, cams, batch_size=1)
+                                  depth_l1_weight=lambda it: 0.0, disable_ssim=not a.ssim)
+    # ssim mode: 16 views per loss-kernel launch (the image-space tensors of a batch are [16,3,H,W])
+    F = LinearSolverFunctions(loss_func, model, cams, batch_size=16 if a.ssim else 1)
 
     def sync_all():
         torch.cuda.synchronize()
@@ -264,7 +269,7 @@ def main():
     stages = _C.timing_collect()
     _C.timing_enable(False)
     launches_per_step = sum(c for _, c in stages.values()) // a.steps
-    jt_ms, jt_n = stages["blend_jtjv"]
+    jt_ms, jt_n = stages["loss_blocks" if a.ssim else "blend_jtjv"]
     peaks = {}
     pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(pk):
@@ -276,6 +281,10 @@ def main():
     n_local = max(len(F._views), 1)
     launches = max(jt_n // a.steps, 1)
     alg_bytes = (R_cached * (48 + 32 + 4 + 4 + 48 + 48) + pix * (4 + 12)) / launches
+    if a.ssim:
+        # loss-block JVP and VJP kernels (csrc/loss_blocks.cu): 36 B per pixel and channel each (28 in + 8 out,
+        # 32 in + 4 out), one launch of each per batch of <= 16 views
+        alg_bytes = pix * 3 * 36.0 * 2 / launches
     dur_s = (jt_ms / max(jt_n, 1)) * 1e-3
     achieved = alg_bytes / dur_s / 1e9 if dur_s > 0 else 0.0
     stage_share = {k: round(ms / a.steps, 4) for k, (ms, c) in stages.items() if c}
@@ -289,12 +298,14 @@ def main():
             lut = torch.tensor([bin(i).count("1") for i in range(256)], dtype=torch.int64, device=dev)
             hits += int(lut[x.long()].sum())
     alg_flops = (24.0 * 256 * R_cached + 154.0 * hits) / launches
+    if a.ssim:
+        alg_flops = pix * 3 * (3 * 44.0 + 8) * 2 / launches       # 3 separable 11-tap blurs (22 FMA) + epilogue
     fp32_peak = 71.6   # TFLOP/s, scalar FFMA measured on this pool's B200 with tools/ffma2_bench.cu (profiles/r1_ffma2_bench.txt)
     traffic = None
     tj = os.path.join(ROOT, "profiles", "traffic.json")   # dram bytes of the same kernel from the ncu --set full capture
     if os.path.exists(tj):
         t = json.load(open(tj))
-        if t.get("kernel") == "k_blend_jtjv" and t.get("views_per_launch"):
+        if t.get("kernel") == "k_blend_jtjv" and t.get("views_per_launch") and not a.ssim:
             traffic = t["dram_bytes_per_launch"] / t["views_per_launch"] * (n_local / launches)
     result = {
         "metric": METRIC, "value": 1e3 / ms_step, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
@@ -308,7 +319,7 @@ def main():
                 "d2h_bytes_per_step": 4 * n_flat, "per_rank_bytes": moved,
                 "staging": "each rank copies 1/N of the replicated vector from pinned host memory + all_gather; result slices back"},
         "gpu_launches": int(launches_per_step) * a.steps,
-        "roofline": {"kernel": "k_blend_jtjv", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+        "roofline": {"kernel": "k_loss_stream<3> (loss-block JVP, VJP)" if a.ssim else "k_blend_jtjv", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": traffic,
                      "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s",
                      "launch_ms": dur_s * 1e3, "launches_per_step": launches, "alg_bytes_per_launch": alg_bytes,
@@ -321,7 +332,7 @@ def main():
     if sampler:
         sampler.join(timeout=2)
         result["clocks"] = sampler.summary()
-    if rank == 0 and not a.no_cpu_baseline and world == 1:
+    if rank == 0 and not a.no_cpu_baseline and world == 1 and not a.ssim:
         n = cpu_sample_size(a, P, V)
         dt, cores = cpu_jtjv_views(g, cams_np, tan, list(range(n)))
         result["cpu_baseline"] = {"value": 1.0 / (dt / n * V), "unit": UNIT, "cores": cores, "kind": "port",

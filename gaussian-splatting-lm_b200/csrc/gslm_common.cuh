@@ -111,7 +111,7 @@ const char* last_error();
 
 // ---- optional per-stage device timing (gslm_timing_*; used by bench.py for the live roofline numbers) ----
 enum Stage { ST_PREPROCESS = 0, ST_SCAN, ST_KEYS, ST_SORT, ST_RANGES, ST_GATHER, ST_BLEND_FWD, ST_PRE_TANGENT,
-             ST_BLEND_JVP, ST_BLEND_BWD, ST_BLEND_JTJV, ST_PRE_BWD, ST_COUNT };
+             ST_BLEND_JVP, ST_BLEND_BWD, ST_BLEND_JTJV, ST_PRE_BWD, ST_LOSS, ST_ACTIVATION, ST_COUNT };
 void stage_begin(int stage, cudaStream_t s);   // no-ops unless timing is enabled
 void stage_end(int stage, cudaStream_t s);
 struct StageScope {

@@ -50,7 +50,7 @@ extern "C" {
 
 static const char* kStageNames[ST_COUNT] = {"preprocess", "scan", "duplicate_keys", "radix_sort", "tile_ranges",
                                             "gather_records", "blend_fwd", "preprocess_tangent", "blend_jvp",
-                                            "blend_bwd", "blend_jtjv", "preprocess_bwd"};
+                                            "blend_bwd", "blend_jtjv", "preprocess_bwd", "loss_blocks", "activation_layer"};
 
 int32_t gslm_timing_num_stages(void) { return ST_COUNT; }
 const char* gslm_timing_stage_name(int32_t stage) { return (stage >= 0 && stage < ST_COUNT) ? kStageNames[stage] : ""; }

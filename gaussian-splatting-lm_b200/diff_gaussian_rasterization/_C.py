@@ -39,6 +39,24 @@ class GslmGrads(C.Structure):
                 ("dL_dscales", C.c_void_p), ("dL_drotations", C.c_void_p), ("accumulate", C.c_int32)]
 
 
+class GslmLossBatch(C.Structure):
+    _fields_ = [("B", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("images", C.c_void_p),
+                ("alpha_masks", C.c_void_p), ("gt", C.c_void_p), ("alphas", C.c_void_p), ("betas", C.c_void_p)]
+
+
+class GslmActivations(C.Structure):
+    _fields_ = [("P", C.c_int32), ("M", C.c_int32), ("scales", C.c_void_p), ("rotations", C.c_void_p),
+                ("rot_norm", C.c_void_p), ("opacities", C.c_void_p)]
+
+
+class GslmRawVector(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("xyz", "features_dc", "features_rest", "scaling", "rotation", "opacity")]
+
+
+class GslmActVector(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("means3D", "shs", "scales", "rotations", "opacities")]
+
+
 class GslmBufferView(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("point_list", "tile_keys_sorted", "ranges", "n_contrib", "final_T",
                                           "tiles_touched", "point_offsets", "depths", "means2D", "conic_opacity",
@@ -76,7 +94,9 @@ ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_int32, C.c_size_t)
 EXPORTS = ("gslm_last_error", "gslm_abi_version", "gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_binning_temp_bytes",
            "gslm_mark_visible", "gslm_forward", "gslm_forward_jvp", "gslm_backward_scratch_bytes", "gslm_backward",
            "gslm_jvp_scratch_bytes", "gslm_jvp_cached", "gslm_jtjv_scratch_bytes", "gslm_jtjv",
-           "gslm_jtjv_batch_scratch_bytes", "gslm_jtjv_batch", "gslm_buffer_view", "gslm_timing_num_stages",
+           "gslm_jtjv_batch_scratch_bytes", "gslm_jtjv_batch", "gslm_loss_lin_bytes", "gslm_loss_blocks",
+           "gslm_loss_blocks_jvp", "gslm_loss_blocks_vjp", "gslm_activation_jvp", "gslm_activation_vjp",
+           "gslm_buffer_view", "gslm_timing_num_stages",
            "gslm_timing_stage_name", "gslm_timing_enable", "gslm_timing_collect")
 
 
@@ -108,6 +128,13 @@ def lib():
         L.gslm_jtjv.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
         L.gslm_jtjv_batch_scratch_bytes.argtypes = [C.c_int32, C.c_int32, vp]
         L.gslm_jtjv_batch.argtypes = [vp, vp, C.c_int32, vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, vp, vp, vp]
+        L.gslm_loss_lin_bytes.restype = C.c_size_t
+        L.gslm_loss_lin_bytes.argtypes = [C.c_int32, C.c_int32, C.c_int32]
+        L.gslm_loss_blocks.argtypes = [vp, vp, vp, vp, vp]
+        L.gslm_loss_blocks_jvp.argtypes = [vp, vp, vp, vp, vp, vp]
+        L.gslm_loss_blocks_vjp.argtypes = [vp, vp, vp, vp, vp, C.c_int32, vp]
+        L.gslm_activation_jvp.argtypes = [vp, vp, vp, vp]
+        L.gslm_activation_vjp.argtypes = [vp, vp, vp, vp, vp, vp]
         L.gslm_buffer_view.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int64, vp, vp, vp, vp, vp]
         L.gslm_timing_stage_name.restype = C.c_char_p
         L.gslm_timing_collect.argtypes = [vp, vp]
@@ -505,6 +532,96 @@ def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer, sortScratch=
         out["clamped"] = view(geomBuffer, v.clamped, P, torch.uint8, (P,))
         out["g_off"] = view(geomBuffer, v.g_off, 4 * (P + 1), torch.int32, (P + 1,))
     return out
+
+
+# ---------------------------------------------------------------------- residual side (csrc/loss_blocks.cu)
+class LossBatch:
+    """One batch of image planes [B,3,H,W] at a fixed linearisation point: holds the contiguous fp32 tensors the
+    three loss-block calls share (images, alpha masks [B,1,H,W] or None, targets, per-image alphas / betas [B])."""
+
+    def __init__(self, images, alpha_masks, gt_images, per_image_alphas, per_image_betas):
+        if images.dim() != 4 or images.shape[1] != 3:
+            raise ValueError("images must be [B,3,H,W]")
+        if not images.is_cuda:
+            raise RuntimeError("gslm_b200: tensors must live on a CUDA device (no CPU path)")
+        self.images = _f32(images.detach())
+        self.B, _, self.H, self.W = self.images.shape
+        self.gt = _f32(gt_images.detach().expand_as(self.images))
+        self.masks = None
+        if alpha_masks is not None:
+            self.masks = _f32(alpha_masks.detach().expand(self.B, 1, self.H, self.W))
+        dev = self.images.device
+        self.alphas = _f32(torch.as_tensor(per_image_alphas, device=dev).detach().reshape(-1).expand(self.B))
+        self.betas = _f32(torch.as_tensor(per_image_betas, device=dev).detach().reshape(-1).expand(self.B))
+        self.lin = None
+        self.c = GslmLossBatch(self.B, self.H, self.W, _ptr(self.images), _ptr(self.masks), _ptr(self.gt),
+                               _ptr(self.alphas), _ptr(self.betas))
+
+    def blocks(self, want_lin=True):
+        """(Ll1_per_pixel, ssim_loss_per_pixel) of compute_batch_loss_block (disable_ssim=False); keeps the
+        linearisation record for jvp / vjp."""
+        r1, r2 = torch.empty_like(self.images), torch.empty_like(self.images)
+        if want_lin:
+            n = lib().gslm_loss_lin_bytes(self.B, self.H, self.W)
+            self.lin = torch.empty(max(n, 1), dtype=torch.uint8, device=self.images.device)
+        _check(lib().gslm_loss_blocks(C.addressof(self.c), _ptr(r1), _ptr(r2), _ptr(self.lin) if want_lin else None,
+                                      _stream()))
+        return r1, r2
+
+    def jvp(self, t_images):
+        """Tangents of the two blocks for an image tangent [B,3,H,W]."""
+        t = _f32(t_images)
+        t1, t2 = torch.empty_like(self.images), torch.empty_like(self.images)
+        _check(lib().gslm_loss_blocks_jvp(C.addressof(self.c), _ptr(self.lin), _ptr(t), _ptr(t1), _ptr(t2), _stream()))
+        return t1, t2
+
+    def vjp(self, u1, u2, out=None):
+        """Pull-back of the block cotangents to the images; out: accumulate into this [B,3,H,W] tensor."""
+        u1, u2 = _f32(u1), _f32(u2)
+        g = torch.empty_like(self.images) if out is None else out
+        _check(lib().gslm_loss_blocks_vjp(C.addressof(self.c), _ptr(self.lin), _ptr(u1), _ptr(u2), _ptr(g),
+                                          0 if out is None else 1, _stream()))
+        return g
+
+
+# ---------------------------------------------------------------------- parameter side (csrc/param_space.cu)
+def _raw_vector(state):
+    """GslmRawVector over the views of a packed GaussianModelState (solver/gaussian_model_state.py)."""
+    ts = (state.xyz_grad, state.features_dc_grad, state.features_rest_grad, state.scaling_grad, state.rotation_grad,
+          state.opacity_grad)
+    for t in ts:
+        if t.numel() and (not t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous()):
+            raise RuntimeError("gslm_b200: parameter-space vectors must be contiguous fp32 CUDA tensors")
+    return GslmRawVector(*[_ptr(t) for t in ts])
+
+
+class Activations:
+    """Activated parameters at the linearisation point + the two linear maps between raw and activated space."""
+
+    def __init__(self, scales, rotations, rot_norm, opacities, M):
+        self.keep = tuple(_f32(t) for t in (scales, rotations, rot_norm, opacities))
+        self.P, self.M = int(scales.shape[0]), int(M)
+        self.c = GslmActivations(self.P, self.M, *[_ptr(t) for t in self.keep])
+
+    def jvp(self, v_state, shs_t, scales_t, rotations_t, opacities_t):
+        """Tangents of (shs, scales, rotations, opacities) for the raw tangent `v_state`, written into the given
+        tensors (the tangent of means3D is v_state.xyz_grad itself)."""
+        rv = _raw_vector(v_state)
+        av = GslmActVector(None, _ptr(shs_t), _ptr(scales_t), _ptr(rotations_t), _ptr(opacities_t))
+        _check(lib().gslm_activation_jvp(C.addressof(self.c), C.addressof(rv), C.addressof(av), _stream()))
+
+    def vjp(self, means3D_g, shs_g, scales_g, rotations_g, opacities_g, out_state, v_state=None, damp6=None):
+        """out_state <- activation VJP of the activated-space gradient (+ damp6[k] * v_state per group)."""
+        av = GslmActVector(*[_ptr(t) for t in (means3D_g, shs_g, scales_g, rotations_g, opacities_g)])
+        ov = _raw_vector(out_state)
+        if v_state is None:
+            _check(lib().gslm_activation_vjp(C.addressof(self.c), C.addressof(av), None, None, C.addressof(ov),
+                                             _stream()))
+        else:
+            vv = _raw_vector(v_state)
+            d = (C.c_float * 6)(*[float(x) for x in damp6])
+            _check(lib().gslm_activation_vjp(C.addressof(self.c), C.addressof(av), C.addressof(vv), d,
+                                             C.addressof(ov), _stream()))
 
 
 def timing_enable(on=True):

@@ -6,13 +6,16 @@ Two execution modes with identical results:
 
 generic  (any loss_func): exactly the reference's composition -- forward-mode AD through loss_func for J v,
          loss.backward for J^T u; the rasterizer kernels run underneath via autograd.Function.{jvp,backward}.
-cached   (loss_func is a functools.partial of solver.batch_training_loss.batch_training_loss with
-         disable_ssim=True, the configuration the LM driver uses, train_jvp.py:212): the linearisation point is
+cached   (loss_func is a functools.partial of solver.batch_training_loss.batch_training_loss; disable_ssim=True is
+         the configuration the LM driver uses, train_jvp.py:212): the linearisation point is
          fixed for the whole CG solve, so evaluate_loss() keeps, per view, the sorted instance records, tile
          ranges, final_T / n_contrib and the pixel weights; every later matvec / matvec_T / normal_matvec then
          costs only the tangent-preprocess, one tile kernel and the per-Gaussian adjoint kernel per view: no
          preprocess, no scan / sort, no host synchronisation.
          normal_matvec uses the fused tangent->adjoint tile kernel, so J v is never written to HBM.
+         With disable_ssim=False (L1 + SSIM blocks) the residual Jacobian is no longer diagonal in image space
+         (11x11 windows), so J^T J v = J_r^T (L^T L) J_r v runs as tangent tile kernel -> loss-block JVP -> loss-block
+         VJP (csrc/loss_blocks.cu, one kernel each) -> adjoint tile kernel, still on the cached linearisation.
 
 Multi-GPU (torch.distributed initialised, one process per GPU): views are sharded over ranks, parameters and
 parameter-space vectors are replicated, and each normal_matvec / matvec_T ends with ONE allreduce(sum) of the
@@ -61,13 +64,14 @@ class LinearSolverFunctions:
         self.param_mask = param_mask
         self.splat_mask = splat_mask
         legal = (isinstance(loss_func, functools.partial) and loss_func.func is batch_training_loss
-                 and bool(loss_func.keywords.get("disable_ssim", False))
                  and not loss_func.keywords.get("train_test_exp", False)
                  and not getattr(loss_func.keywords.get("pipe"), "compute_cov3D_python", False)
                  and not getattr(loss_func.keywords.get("pipe"), "convert_SHs_python", False))
         if cached and not legal:
-            raise ValueError("cached=True needs loss_func = partial(batch_training_loss, ..., disable_ssim=True)")
+            raise ValueError("cached=True needs loss_func = partial(batch_training_loss, ...) without exposure "
+                             "training and without the Python SH / covariance paths")
         self.cached = legal if cached is None else bool(cached)
+        self.ssim = legal and not bool(loss_func.keywords.get("disable_ssim", False))
         self._views = None
         self._scratch = None
         self._plan = None
@@ -217,6 +221,10 @@ class LinearSolverFunctions:
                    "scales": torch.exp(g._scaling.detach()), "rotations": raw_rot / norm, "rot_norm": norm,
                    "shs": torch.cat((g._features_dc.detach(), g._features_rest.detach()), dim=1).contiguous(),
                    "sh_degree": int(g.active_sh_degree)}
+            # the differentiated activation layer (csrc/param_space.cu) + its persistent tangent buffers
+            act["layer"] = _C.Activations(act["scales"], act["rotations"], act["rot_norm"], act["opacities"],
+                                          act["shs"].shape[1])
+            act["tangent"] = tuple(torch.empty_like(act[k]) for k in ("shs", "scales", "rotations", "opacities"))
         return act
 
     def _gauss_args(self):
@@ -232,12 +240,14 @@ class LinearSolverFunctions:
         self._act = a = self._activated()
         self._views = []
         self._plan = None
+        self._loss_batches = []
         losses = []
         for start, end in self._batches():
             cams = self.viewpoint_cams[start:end]
             Hm, Wm = max(c.image_height for c in cams), max(c.image_width for c in cams)
             resid = torch.zeros((len(cams), 3, Hm, Wm), dtype=torch.float32, device=dev)
             gt, masks = gather_targets(cams, resid)
+            images = resid if self.ssim else None      # ssim mode: `resid` first collects the clamped renders
             for i, cam in enumerate(cams):
                 H, W = int(cam.image_height), int(cam.image_width)
                 vc = _ViewCache()
@@ -251,7 +261,9 @@ class LinearSolverFunctions:
                                cam.camera_center, pipe.antialiasing, pipe.debug)
                 # d clamp(x,0,1)/dx as torch defines it (inclusive bounds) times the alpha mask
                 m = ((color >= 0) & (color <= 1)).to(torch.float32)
-                if masks is not None:
+                if self.ssim:
+                    images[i, :, :H, :W] = color.clamp(0, 1)     # the alpha mask is applied inside the loss kernels
+                elif masks is not None:
                     m = m * masks[i, :, :H, :W]
                     resid[i, :, :H, :W] = color.clamp(0, 1) * masks[i, :, :H, :W] - gt[i, :, :H, :W]
                 else:
@@ -261,19 +273,26 @@ class LinearSolverFunctions:
                 self._views.append(vc)
             depth_block = torch.zeros((0,), dtype=torch.float32, device=dev)
             sizes = [(c.image_height, c.image_width) for c in cams]
-            losses.append(BatchLossImageState(resid, resid, depth_block, sizes, False))
+            if self.ssim:
+                lam = self._kw("opt").lambda_dssim
+                al = torch.tensor([math.sqrt((1.0 - lam) / (3 * h * w)) for h, w in sizes], device=dev)
+                be = torch.tensor([math.sqrt(lam / (3 * h * w)) for h, w in sizes], device=dev)
+                lb = _C.LossBatch(images, masks, gt, al, be)
+                r1, r2 = lb.blocks(want_lin=True)
+                self._loss_batches.append(lb)
+                losses.append(BatchLossImageState(r1, r2, depth_block, sizes, False))
+            else:
+                losses.append(BatchLossImageState(resid, resid, depth_block, sizes, False))
         self.loss = MultiBatchLossImageState(losses)
         return self.loss
 
     def _tangent_inputs(self, v):
-        """Activation JVP: raw-parameter tangent -> tangents of the kernel inputs (scene/gaussian_model.py:192-220)."""
+        """Activation JVP: raw-parameter tangent -> tangents of the kernel inputs (scene/gaussian_model.py:192-220),
+        one kernel into buffers that live as long as the linearisation."""
         a = self._act
-        q = a["rotations"]
-        vr = v.rotation_grad
-        t_rot = (vr - q * (q * vr).sum(dim=1, keepdim=True)) / a["rot_norm"]
-        o = a["opacities"]
-        return (v.xyz_grad.contiguous(), None, o * (1.0 - o) * v.opacity_grad, a["scales"] * v.scaling_grad, t_rot,
-                None, torch.cat((v.features_dc_grad, v.features_rest_grad), dim=1))
+        t_shs, t_scales, t_rot, t_op = a["tangent"]
+        a["layer"].jvp(v, t_shs, t_scales, t_rot, t_op)
+        return (v.xyz_grad.contiguous(), None, t_op, t_scales, t_rot, None, t_shs)
 
     def _act_accumulators(self):
         """Packed activated-space gradient buffer [means3D | shs | scales | rotations | opacity] (59 P floats:
@@ -294,21 +313,19 @@ class LinearSolverFunctions:
                  views["rotations"])
         return flat, views, sinks
 
-    def _to_state(self, views, extra=None):
-        """Activation VJP: activated-space gradients -> raw-parameter GaussianModelState (masked)."""
+    def _to_state(self, views, v=None, damp=None):
+        """Activation VJP: activated-space gradients -> raw-parameter GaussianModelState (masked), with the damping
+        term `+ damp * v` (float lambda or GaussianModelDampMatrix) fused into the same pass."""
         a = self._act
-        g = self.gaussians
-        out = GaussianModelState.from_gaussians(g)
-        out.xyz_grad.copy_(views["means3D"])
-        out.features_dc_grad.copy_(views["shs"][:, :1])
-        out.features_rest_grad.copy_(views["shs"][:, 1:])
-        torch.mul(a["scales"], views["scales"], out=out.scaling_grad)
-        q, gr = a["rotations"], views["rotations"]
-        out.rotation_grad.copy_((gr - q * (q * gr).sum(dim=1, keepdim=True)) / a["rot_norm"])
-        o = a["opacities"]
-        torch.mul(o * (1.0 - o), views["opacities"], out=out.opacity_grad)
-        if extra is not None:
-            out.packed().add_(extra)
+        out = GaussianModelState.from_gaussians(self.gaussians)
+        grads = (views["means3D"], views["shs"], views["scales"], views["rotations"], views["opacities"])
+        if damp is None:
+            a["layer"].vjp(*grads, out)
+        else:
+            d7 = damp.values() if isinstance(damp, GaussianModelDampMatrix) else (float(damp),) * 7
+            a["layer"].vjp(*grads, out, v, d7[:6])
+            if out.exposure_grad.numel():
+                out.exposure_grad.add_(v.exposure_grad, alpha=float(d7[6]))
         return GaussianModelState(*out.tensors(), param_mask=self.param_mask, splat_mask=self.splat_mask,
                                   _flat=out.flat)
 
@@ -331,8 +348,17 @@ class LinearSolverFunctions:
                 jv, _ = _C.jvp_cached(gargs, targs, vc.cam_args, vc.radii, vc.geom, vc.R, vc.binning, vc.img)
                 t[i, :, :vc.H, :vc.W] = jv * vc.mask
             depth_block = torch.zeros((0,), dtype=torch.float32, device=t.device)
-            out.append(BatchLossImageState(t, t, depth_block, [(c.image_height, c.image_width) for c in cams], False))
+            t1, t2 = self._loss_batches[len(out)].jvp(t) if self.ssim else (t, t)
+            out.append(BatchLossImageState(t1, t2, depth_block, [(c.image_height, c.image_width) for c in cams], False))
         return MultiBatchLossImageState(out)
+
+    def _backward_view(self, vc, g, sinks):
+        a = self._act
+        bg, vm, pm, tfx, tfy, H, W, campos, aa, dbg = vc.cam_args
+        _C.rasterize_gaussians_backward(bg, a["means3D"], vc.radii, self._empty, a["opacities"], a["scales"],
+                                        a["rotations"], 1.0, self._empty, vm, pm, tfx, tfy, g, None, a["shs"],
+                                        a["sh_degree"], campos, vc.geom, vc.R, vc.binning, vc.img, aa, dbg,
+                                        accumulate_into=sinks)
 
     def _matvec_T_cached(self, vs):
         self._require_linearized()
@@ -341,19 +367,37 @@ class LinearSolverFunctions:
         k = 0
         for idx, (start, end) in enumerate(self._batches()):
             u = vs.batch_losses[idx]
-            cot = u.Ll1_per_pixel + u.ssim_loss_per_pixel     # J^T of the two aliased blocks
+            if self.ssim:
+                cot = self._loss_batches[idx].vjp(u.Ll1_per_pixel, u.ssim_loss_per_pixel)
+            else:
+                cot = u.Ll1_per_pixel + u.ssim_loss_per_pixel     # J^T of the two aliased blocks
             for i in range(end - start):
                 vc = self._views[k]
                 k += 1
-                g = cot[i, :, :vc.H, :vc.W] * vc.mask
-                bg, vm, pm, tfx, tfy, H, W, campos, aa, dbg = vc.cam_args
-                _C.rasterize_gaussians_backward(bg, a["means3D"], vc.radii, self._empty, a["opacities"], a["scales"],
-                                                a["rotations"], 1.0, self._empty, vm, pm, tfx, tfy, g, None, a["shs"],
-                                                a["sh_degree"], campos, vc.geom, vc.R, vc.binning, vc.img, aa, dbg,
-                                                accumulate_into=sinks)
+                self._backward_view(vc, cot[i, :, :vc.H, :vc.W] * vc.mask, sinks)
         if self.dist:
             self.dist.all_reduce(flat)
         return self._to_state(views)
+
+    def _normal_matvec_ssim(self, gargs, targs, sinks, quad):
+        """J_r^T (L^T L) J_r v per batch of views: image tangents from the tangent tile kernel, the loss-block JVP and
+        VJP kernels in image space, then the adjoint tile kernel."""
+        k = 0
+        for idx, (start, end) in enumerate(self._batches()):
+            lb = self._loss_batches[idx]
+            t = torch.zeros((lb.B, 3, lb.H, lb.W), dtype=torch.float32, device=lb.images.device)
+            for i in range(end - start):
+                vc = self._views[k + i]
+                jv, _ = _C.jvp_cached(gargs, targs, vc.cam_args, vc.radii, vc.geom, vc.R, vc.binning, vc.img)
+                t[i, :, :vc.H, :vc.W] = jv * vc.mask
+            t1, t2 = lb.jvp(t)
+            if quad is not None:
+                quad += (t1 * t1).sum() + (t2 * t2).sum()
+            cot = lb.vjp(t1, t2)
+            for i in range(end - start):
+                vc = self._views[k + i]
+                self._backward_view(vc, cot[i, :, :vc.H, :vc.W] * vc.mask, sinks)
+            k += end - start
 
     def normal_matvec(self, v, damp=None, return_quad=False):
         """J^T J v (+ damp * v): the Gauss-Newton product CG needs, one fused tile kernel per view.
@@ -370,16 +414,16 @@ class LinearSolverFunctions:
         gargs = self._gauss_args()
         flat, views, sinks = self._act_accumulators()
         quad = torch.zeros(1, dtype=torch.float32, device=flat.device) if return_quad else None
-        if self._plan is None:
-            self._plan = _C.JtjvBatchPlan([(vc.cam_args, vc.radii, vc.geom, vc.R, vc.binning, vc.img, vc.weight)
-                                           for vc in self._views], flat.device)
-        _C.jtjv_batch(gargs, targs, self._plan, sinks, out_vJJv=quad)
+        if self.ssim:
+            self._normal_matvec_ssim(gargs, targs, sinks, quad)
+        else:
+            if self._plan is None:
+                self._plan = _C.JtjvBatchPlan([(vc.cam_args, vc.radii, vc.geom, vc.R, vc.binning, vc.img, vc.weight)
+                                               for vc in self._views], flat.device)
+            _C.jtjv_batch(gargs, targs, self._plan, sinks, out_vJJv=quad)
         if self.dist:
             self.dist.all_reduce(flat)
             if quad is not None:
                 self.dist.all_reduce(quad)
-        extra = None
-        if damp is not None:
-            extra = (v * damp).packed()
-        out = self._to_state(views, extra)
+        out = self._to_state(views, v, damp)
         return (out, quad) if return_quad else out

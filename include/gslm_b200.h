@@ -177,6 +177,73 @@ int32_t gslm_jtjv_batch(const GslmGaussians* g, const GslmGaussians* gt, int32_t
                         const int32_t* num_cached, const float* const* weights, void* scratch, size_t scratch_bytes,
                         GslmGrads* grads, float* out_vJJv, void* stream);
 
+/* ---- residual side: the two per-pixel loss blocks and their derivatives --------------------------------------
+ * Replaces compute_batch_loss_block (solver/batch_training_loss.py:10-31) with the SSIM map of ssim_per_pixel /
+ * _ssim_per_pixel (utils/loss_utils.py:91-117; 11x11 Gaussian window, sigma 1.5, zero padding, C1 = 0.01^2,
+ * C2 = 0.03^2) for disable_ssim=False:
+ *     r1 = alphas[i] sqrt(|x - gt| + 1e-6),   r2 = betas[i] sqrt(|1 - SSIM(x, gt)| + 1e-6),   x = images * alpha_masks
+ * and what PyTorch derives from it in the reference: the forward-AD tangent used by LinearSolverFunctions.matvec
+ * (solver/solver_functions.py:75-90) and the autograd pull-back used by matvec_T (:92-113).  It also stands in for
+ * the reference's fused-ssim extension pair fusedssim / fusedssim_backward (utils/loss_utils.py:24-38), which has
+ * no forward-mode rule.  All arrays are [B,3,H,W] fp32 device tensors (zero padded to the batch's Hmax x Wmax as
+ * batch_training_loss.py:54-66 lays them out); alpha_masks is [B,1,H,W] or NULL; alphas / betas are DEVICE arrays
+ * of B per-image factors (sqrt((1-lambda)/n_i), sqrt(lambda/n_i), batch_training_loss.py:68-77).
+ * `lin` is an opaque per-pixel linearisation record (gslm_loss_lin_bytes) written by gslm_loss_blocks (NULL: not
+ * wanted) and read by the two derivative calls, which are linear maps at that linearisation point. */
+typedef struct GslmLossBatch {
+    int32_t B, H, W;
+    const float* images;       /* [B,3,H,W] rendered images (already clamped by the renderer glue)   */
+    const float* alpha_masks;  /* [B,1,H,W] or NULL                                                  */
+    const float* gt;           /* [B,3,H,W]                                                          */
+    const float* alphas;       /* [B] device                                                         */
+    const float* betas;        /* [B] device                                                         */
+} GslmLossBatch;
+size_t gslm_loss_lin_bytes(int32_t B, int32_t H, int32_t W);       /* 16 B per pixel and channel */
+int32_t gslm_loss_blocks(const GslmLossBatch* batch, float* r1, float* r2, void* lin, void* stream);
+/* (t1, t2) = d(r1, r2)/d images . t_images */
+int32_t gslm_loss_blocks_jvp(const GslmLossBatch* batch, const void* lin, const float* t_images, float* t1, float* t2,
+                             void* stream);
+/* g_images (+)= (d(r1, r2)/d images)^T (u1, u2); accumulate != 0 adds into g_images */
+int32_t gslm_loss_blocks_vjp(const GslmLossBatch* batch, const void* lin, const float* u1, const float* u2,
+                             float* g_images, int32_t accumulate, void* stream);
+
+/* ---- parameter side: the activation layer, differentiated ---------------------------------------------------
+ * The solver's vectors live in RAW parameter space (GaussianModelState: xyz, features_dc, features_rest, scaling,
+ * rotation, opacity; solver/gaussian_model_state.py:4-60) while the rasterizer consumes ACTIVATED inputs
+ * (get_scaling = exp, get_rotation = normalize, get_opacity = sigmoid, get_features = cat(dc, rest);
+ * scene/gaussian_model.py:192-220).  The reference lets PyTorch differentiate those activations (forward AD inside
+ * make_dual, autograd in loss.backward: solver/solver_functions.py:75-113); here each direction is one pass over the
+ * 59 P floats.  `GslmActivations` holds the activated values at the linearisation point. */
+typedef struct GslmActivations {
+    int32_t P, M;             /* Gaussians; SH coefficients per channel (features_dc + features_rest rows)  */
+    const float* scales;      /* [P,3] exp(raw scaling)                                                      */
+    const float* rotations;   /* [P,4] raw quaternion / its norm                                             */
+    const float* rot_norm;    /* [P]   norm of the raw quaternion                                            */
+    const float* opacities;   /* [P]   sigmoid(raw opacity)                                                  */
+} GslmActivations;
+typedef struct GslmRawVector {   /* a GaussianModelState without the exposure block */
+    float* xyz;            /* [P,3]     */
+    float* features_dc;    /* [P,1,3]   */
+    float* features_rest;  /* [P,M-1,3] (may be NULL when M == 1) */
+    float* scaling;        /* [P,3]     */
+    float* rotation;       /* [P,4]     */
+    float* opacity;        /* [P,1]     */
+} GslmRawVector;
+typedef struct GslmActVector {   /* tangents or gradients of the rasterizer inputs */
+    float* means3D;        /* [P,3]   (JVP output: may be NULL, the tangent of means3D IS v.xyz) */
+    float* shs;            /* [P,M,3] */
+    float* scales;         /* [P,3]   */
+    float* rotations;      /* [P,4]   */
+    float* opacities;      /* [P]     */
+} GslmActVector;
+/* t = d(activated inputs)/d(raw parameters) . v */
+int32_t gslm_activation_jvp(const GslmActivations* act, const GslmRawVector* v, const GslmActVector* t, void* stream);
+/* out = (d(activated)/d(raw))^T g  [+ damp6[k] * v per parameter group k = xyz, dc, rest, scaling, rotation, opacity
+ * when v != NULL; damp6 is a HOST array]: the tail of J^T J v + D v (solver/conjugate_gradient.py:3-49 with the
+ * damping of train_jvp.py:237-260) */
+int32_t gslm_activation_vjp(const GslmActivations* act, const GslmActVector* g, const GslmRawVector* v,
+                            const float* damp6, const GslmRawVector* out, void* stream);
+
 /* ---- optional per-stage device timing (no reference counterpart; bench.py's live roofline numbers) ----
  * When enabled, each stage brackets its kernels with a cudaEvent pair on the launching stream.
  * gslm_timing_collect synchronises the device and returns, per stage, the summed elapsed milliseconds and the

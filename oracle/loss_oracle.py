@@ -25,9 +25,10 @@ EPS = 1e-6
 
 
 def gaussian_window_1d(size=11, sigma=1.5):
-    """loss_utils.py:49-51: float32 tensor of exp values, normalised in float32."""
+    """loss_utils.py:49-51: float32 tensor of exp values, normalised in float32 (torch's sum of 11 floats is the
+    correctly rounded one, which a float64 accumulation reproduces bit for bit)."""
     g = np.array([math.exp(-(x - size // 2) ** 2 / float(2 * sigma ** 2)) for x in range(size)], dtype=np.float32)
-    return g / g.sum(dtype=np.float32)
+    return g / np.float32(g.astype(np.float64).sum())
 
 
 def window_2d(size=11):

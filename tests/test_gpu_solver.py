@@ -204,3 +204,44 @@ def test_lm_step_reduces_validation_loss():
     assert out["best_alpha"] in (2.0, 1.0, 0.5, 0.25, 0.125, 0.0625)
     first = lm_step(loss_func, model, cams[:4], val_cams=cams, param_mask=pm, cg_iters=3, batch_size=2)
     assert first["val_loss"] <= out["val_loss"] * 1.0001     # a second step does not make things worse
+
+
+@pytest.mark.parametrize("P,M", [(1001, 16), (257, 1), (4096, 4)])
+def test_activation_layer_kernels_match_torch_autograd(P, M):
+    """csrc/param_space.cu against PyTorch differentiating the reference's activations
+    (scene/gaussian_model.py:192-220: exp, normalize, sigmoid, cat): forward AD for the tangent, autograd for the
+    pull-back, odd P (unaligned quaternion block inside the packed state) and M = 1 (no features_rest) included."""
+    import torch.autograd.forward_ad as fwAD
+    from diff_gaussian_rasterization import _C
+    from solver.gaussian_model_state import GaussianModelDampMatrix, GaussianModelState
+    gen = torch.Generator(device="cuda").manual_seed(P + M)
+    rn = lambda *s: torch.randn(*s, device="cuda", generator=gen)
+    raw = [rn(P, 3), rn(P, 1, 3), rn(P, M - 1, 3), rn(P, 3) * 0.3, rn(P, 4), rn(P, 1), torch.zeros(2, 3, 4, device="cuda")]
+
+    def activate(xyz, dc, rest, sc, rot, op):
+        return xyz, torch.cat((dc, rest), dim=1), torch.exp(sc), torch.nn.functional.normalize(rot), torch.sigmoid(op)
+
+    v = GaussianModelState._from_shapes(raw)
+    v.packed().copy_(rn(v.packed().numel()))
+    norm = raw[4].norm(dim=1, keepdim=True)
+    layer = _C.Activations(torch.exp(raw[3]), raw[4] / norm, norm, torch.sigmoid(raw[5]), M)
+    t = [torch.empty(P, M, 3, device="cuda"), torch.empty(P, 3, device="cuda"), torch.empty(P, 4, device="cuda"),
+         torch.empty(P, 1, device="cuda")]
+    layer.jvp(v, *t)
+    with torch.no_grad(), fwAD.dual_level():
+        duals = [fwAD.make_dual(p, tv) for p, tv in zip(raw[:6], v.tensors()[:6])]
+        ref_t = [fwAD.unpack_dual(o).tangent for o in activate(*duals)]
+    for a, b in zip(t, ref_t[1:]):
+        assert torch.allclose(a, b, rtol=1e-5, atol=1e-6)
+    g = [rn(P, 3), rn(P, M, 3), rn(P, 3), rn(P, 4), rn(P, 1)]
+    leaves = [p.clone().requires_grad_(True) for p in raw[:6]]
+    torch.autograd.backward(activate(*leaves), g)
+    out = GaussianModelState._from_shapes(raw)
+    layer.vjp(*g, out)
+    for a, leaf in zip(out.tensors()[:6], leaves):
+        assert torch.allclose(a, leaf.grad, rtol=1e-5, atol=1e-6)
+    D = GaussianModelDampMatrix(5e2, 5e-2, 3e-2, 7e-2, 2e-1, 4.0, 1e1)
+    out2 = GaussianModelState._from_shapes(raw)
+    layer.vjp(*g, out2, v, D.values()[:6])
+    for a, b, tv, d in zip(out2.tensors()[:6], out.tensors()[:6], v.tensors()[:6], D.values()):
+        assert torch.allclose(a, b + d * tv, rtol=1e-5, atol=1e-5)
