@@ -9,7 +9,7 @@
 //
 // Structure (HBM-bound): the window is separable, w2d = w w^T.  A CTA of 128 threads owns
 // a 128-column x 64-row strip of one image plane and STREAMS over its rows: per row the threads stage the NIN
-// pre-convolution quantities of 128 + 10 columns in shared memory (double buffered: one barrier per row), each
+// pre-convolution quantities of 128 + 10 columns in shared memory (an 8-row ring: one barrier per row), each
 // thread forms the horizontal 11-tap sums of its column and feeds them into 11 vertical partial sums held in
 // REGISTERS (a systolic chain: the shift is the FMA's destination, no ring indexing), and from the 11th row on
 // emits one finished output row per input row.  Every input element is read once per strip (+ 16 % vertical, 8 % horizontal halo,
@@ -26,8 +26,17 @@ namespace gslm {
 namespace {
 
 constexpr int LW = 11, LR = 5;          // window size / radius (loss_utils.py:91 window_size=11)
-constexpr int L_TW = 128;               // columns per CTA = threads per CTA
-constexpr int L_TH = 64;                // output rows per CTA
+#ifndef GSLM_LTW
+#define GSLM_LTW 128
+#endif
+#ifndef GSLM_LTH
+#define GSLM_LTH 64
+#endif
+#ifndef GSLM_VJP_PRE
+#define GSLM_VJP_PRE 1
+#endif
+constexpr int L_TW = GSLM_LTW;          // columns per CTA = threads per CTA
+constexpr int L_TH = GSLM_LTH;          // output rows per CTA
 constexpr float L_C1 = 0.01f * 0.01f, L_C2 = 0.03f * 0.03f, L_EPS = 1e-6f;
 
 // gaussian(11, 1.5) / sum, rounded to float32 exactly as loss_utils.py:49-51 produces it
@@ -52,11 +61,16 @@ __device__ __forceinline__ float sgn(float v) { return (v > 0.f) - (v < 0.f); }
 
 // The streaming separable-blur skeleton.  Op supplies
 //   load(plane, y, x, float (&v)[NIN])   pre-convolution quantities at an IN-RANGE pixel
-//   store(plane, y, x, const float (&c)[NIN])   epilogue on the NIN blurred values of an in-range pixel
+//   Pre pre(plane, y, x)                 the epilogue's own global operands, fetched one row ahead
+//   store(plane, y, x, c, center, pre)   epilogue on the NIN blurred values c of an in-range pixel; center = the
+//                                        pixel's own pre-convolution quantities (kept in the shared-memory history)
+//   kCenter      true: keep 8 staged rows in shared memory so `center` is available (else 2 rows, center = 0)
+//   kPrefetch    true: pre() is issued one row ahead (else at store time; measured per kernel, tools/variants_loss.sh)
 template <int NIN, class Op>
 __global__ void __launch_bounds__(L_TW) k_loss_stream(Op op, int H, int W)
 {
-    __shared__ float row[2][NIN][L_TW + 2 * LR];
+    constexpr int L_HIST = Op::kCenter ? 8 : 2;
+    __shared__ float row[L_HIST][NIN][L_TW + 2 * LR];
     const int t = threadIdx.x;
     const int x0 = blockIdx.x * L_TW, y0 = blockIdx.y * L_TH, plane = blockIdx.z;
     const int x = x0 + t;
@@ -76,6 +90,7 @@ __global__ void __launch_bounds__(L_TW) k_loss_stream(Op op, int H, int W)
 
     // software pipeline: the global loads of row rr + 1 are issued before the arithmetic of row rr
     float va[NIN], vb[NIN];
+    typename Op::Pre pre_next = {}, pre_cur = {};
     auto fetch = [&](int rr) {
         const int y = y0 - LR + rr;
         const bool yin = (rr < nrows) && (y >= 0) && (y < H);
@@ -83,12 +98,14 @@ __global__ void __launch_bounds__(L_TW) k_loss_stream(Op op, int H, int W)
         for (int k = 0; k < NIN; ++k) va[k] = vb[k] = 0.f;
         if (yin && x < W) op.load(plane, y, x, va);
         if (t < 2 * LR && yin && hx >= 0 && hx < W) op.load(plane, y, hx, vb);
+        if (Op::kPrefetch && rr >= 2 * LR && rr < nrows && x < W) pre_next = op.pre(plane, y - LR, x);
     };
     fetch(0);
 #pragma unroll 1
     for (int rr = 0; rr < nrows; ++rr) {
         const int y = y0 - LR + rr;
-        float(*buf)[L_TW + 2 * LR] = row[rr & 1];
+        float(*buf)[L_TW + 2 * LR] = row[rr & (L_HIST - 1)];
+        pre_cur = pre_next;
 #pragma unroll
         for (int k = 0; k < NIN; ++k) buf[k][t + LR] = va[k];
         if (t < 2 * LR) {
@@ -107,10 +124,14 @@ __global__ void __launch_bounds__(L_TW) k_loss_stream(Op op, int H, int W)
             acc[LW - 1][q] = win(0) * h;
         }
         if (rr >= 2 * LR && x < W) {
-            float c[NIN];
+            float c[NIN], center[NIN];
 #pragma unroll
-            for (int q = 0; q < NIN; ++q) c[q] = acc[0][q];
-            op.store(plane, y - LR, x, c);
+            for (int q = 0; q < NIN; ++q) {
+                c[q] = acc[0][q];
+                center[q] = Op::kCenter ? row[(rr - LR) & (L_HIST - 1)][q][t + LR] : 0.f;
+            }
+            if (!Op::kPrefetch) pre_cur = op.pre(plane, y - LR, x);
+            op.store(plane, y - LR, x, c, center, pre_cur);
         }
     }
 }
@@ -136,11 +157,14 @@ struct OpBlocks {
         const float a = __ldg(p.images + i) * mask_at(p, plane, y, x), b = __ldg(p.gt + i);
         v[0] = a; v[1] = b; v[2] = a * a; v[3] = b * b; v[4] = a * b;
     }
-    __device__ void store(int plane, int y, int x, const float (&c)[5]) const
+    static constexpr bool kCenter = true, kPrefetch = false;
+    struct Pre { float al, be; };
+    __device__ Pre pre(int plane, int, int) const { return Pre{__ldg(p.alphas + plane / 3), __ldg(p.betas + plane / 3)}; }
+    __device__ void store(int plane, int y, int x, const float (&c)[5], const float (&center)[5], const Pre& pr) const
     {
         const size_t i = pix(p, plane, y, x);
-        const float xv = __ldg(p.images + i) * mask_at(p, plane, y, x), yv = __ldg(p.gt + i);
-        const float al = __ldg(p.alphas + plane / 3), be = __ldg(p.betas + plane / 3);
+        const float xv = center[0], yv = center[1];
+        const float al = pr.al, be = pr.be;
         // Individually rounded operations in the reference's order (loss_utils.py:102-114), no FMA contraction:
         // where render == target over the whole window the reference gets numerator == denominator bit for bit,
         // hence ssim == 1 exactly, |1 - ssim| == 0 and a zero derivative (sign(0) = 0); so must we.
@@ -180,12 +204,14 @@ struct OpJvp {
         const float dx = __ldg(t_images + i) * mk;
         v[0] = dx; v[1] = __ldg(p.images + i) * mk * dx; v[2] = __ldg(p.gt + i) * dx;
     }
-    __device__ void store(int plane, int y, int x, const float (&c)[3]) const
+    static constexpr bool kCenter = true, kPrefetch = true;
+    struct Pre { float4 q; };
+    __device__ Pre pre(int plane, int y, int x) const { return Pre{__ldg(lin + pix(p, plane, y, x))}; }
+    __device__ void store(int plane, int y, int x, const float (&c)[3], const float (&center)[3], const Pre& pr) const
     {
         const size_t i = pix(p, plane, y, x);
-        const float4 q = __ldg(lin + i);
-        t1[i] = q.x * __ldg(t_images + i) * mask_at(p, plane, y, x);
-        t2[i] = q.y * c[0] + q.z * c[1] + q.w * c[2];
+        t1[i] = pr.q.x * center[0];
+        t2[i] = pr.q.y * c[0] + pr.q.z * c[1] + pr.q.w * c[2];
     }
 };
 
@@ -204,14 +230,18 @@ struct OpVjp {
         const float u = __ldg(u2 + i);
         v[0] = q.y * u; v[1] = q.z * u; v[2] = q.w * u;
     }
-    __device__ void store(int plane, int y, int x, const float (&c)[3]) const
+    static constexpr bool kCenter = false, kPrefetch = GSLM_VJP_PRE;
+    struct Pre { float d1u1, xv, yv, mk, g0; };
+    __device__ Pre pre(int plane, int y, int x) const
     {
         const size_t i = pix(p, plane, y, x);
         const float mk = mask_at(p, plane, y, x);
-        const float xv = __ldg(p.images + i) * mk, yv = __ldg(p.gt + i);
-        float r = (__ldg(&lin[i].x) * __ldg(u1 + i) + c[0] + xv * c[1] + yv * c[2]) * mk;
-        if (accumulate) r += g[i];
-        g[i] = r;
+        return Pre{__ldg(&lin[i].x) * __ldg(u1 + i), __ldg(p.images + i) * mk, __ldg(p.gt + i), mk,
+                   accumulate ? g[i] : 0.f};
+    }
+    __device__ void store(int plane, int y, int x, const float (&c)[3], const float (&)[3], const Pre& pr) const
+    {
+        g[pix(p, plane, y, x)] = (pr.d1u1 + c[0] + pr.xv * c[1] + pr.yv * c[2]) * pr.mk + pr.g0;
     }
 };
 

@@ -58,6 +58,7 @@ def main():
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--no-torch", action="store_true", help="skip the torch composition legs")
     a = ap.parse_args()
     B, H, W = a.views, a.height, a.width
     gen = torch.Generator(device="cuda").manual_seed(1)
@@ -92,7 +93,7 @@ def main():
         r1, r2 = reference_composition(x, masks, gt, al, be)
         torch.autograd.backward((r1, r2), (u1, u2))
 
-    for name, fn in (("blocks", ref_fwd), ("jvp", ref_jvp), ("vjp", ref_vjp)):
+    for name, fn in (() if a.no_torch else (("blocks", ref_fwd), ("jvp", ref_jvp), ("vjp", ref_vjp))):
         out[f"torch_{name}_ms"] = timed(fn, max(3, a.iters // 3), warm=1)
     print(json.dumps(out))
 
