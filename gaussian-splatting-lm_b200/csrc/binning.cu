@@ -168,21 +168,39 @@ __global__ void __launch_bounds__(256)
 k_duplicate_keys(int P, const uint32_t* __restrict__ perm, const float2* __restrict__ xy,
                  const uint32_t* __restrict__ offsets, const int32_t* __restrict__ radii, int gx, int gy,
                  uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= P) return;
-    const uint32_t idx = perm[i];
-    int rad = radii[idx];
-    if (rad <= 0) return;
-    uint32_t off = offsets[i];
-    float2 p = xy[idx];
-    int x0, y0, x1, y1;
-    tile_rect(p.x, p.y, rad, gx, gy, x0, y0, x1, y1);
-    for (int y = y0; y < y1; y++)
-        for (int x = x0; x < x1; x++) {
-            keys[off] = (uint32_t)(y * gx + x);
-            vals[off] = idx;
-            off++;
+    // A warp takes 32 consecutive Gaussians of the depth order; each lane works out its Gaussian's tile rectangle,
+    // then the WARP emits the rectangles one Gaussian at a time, lane t writing instance t, t + 32, ...: the stores
+    // of a Gaussian's run are contiguous (the reference's one-thread-per-Gaussian loop, rasterizer_impl.cu:84-110,
+    // writes 8-byte pieces at 32 unrelated addresses per instruction).  Same keys, same values, same positions.
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t idx = 0, off = 0;
+    int x0 = 0, y0 = 0, w = 0, cnt = 0;
+    if (i < P) {
+        idx = perm[i];
+        const int rad = radii[idx];
+        if (rad > 0) {
+            const float2 p = xy[idx];
+            int x1, y1;
+            tile_rect(p.x, p.y, rad, gx, gy, x0, y0, x1, y1);
+            w = x1 - x0;
+            cnt = w > 0 && y1 > y0 ? w * (y1 - y0) : 0;
+            off = offsets[i];
         }
+    }
+    uint32_t todo = __ballot_sync(0xffffffffu, cnt > 0);
+    while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const uint32_t g_idx = __shfl_sync(0xffffffffu, idx, src), g_off = __shfl_sync(0xffffffffu, off, src);
+        const int g_x0 = __shfl_sync(0xffffffffu, x0, src), g_y0 = __shfl_sync(0xffffffffu, y0, src);
+        const int g_w = __shfl_sync(0xffffffffu, w, src), g_cnt = __shfl_sync(0xffffffffu, cnt, src);
+        for (int t = lane; t < g_cnt; t += 32) {
+            const int ry = t / g_w, rx = t - ry * g_w;
+            keys[g_off + t] = (uint32_t)((g_y0 + ry) * gx + g_x0 + rx);
+            vals[g_off + t] = g_idx;
+        }
+    }
 }
 
 // rasterizer_impl.cu:116-138; ranges are zero-filled first (:356)

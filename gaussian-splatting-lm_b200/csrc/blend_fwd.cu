@@ -162,6 +162,139 @@ __global__ void __launch_bounds__(TILE_PIX) k_blend_fwd(FwdArgs a) {
     if (tid == 0) a.ccount[tile] = run;
 }
 
+// -----------------------------------------------------------------------------------------------------------------
+// Warp-per-tile primal sweep (default).  Same arithmetic, same instance order and therefore the same bits as
+// k_blend_fwd above, but with the pixel-to-thread mapping of the derivative sweeps (blend_sweeps.cuh): ONE warp owns
+// the 16x16 tile, lane l owns column l % 16 and the eight rows 2k + l / 16.  Per (tile, instance) the three record
+// loads, the column part of the exponent and the loop overhead are paid once instead of eight times, the eight
+// pixels of a thread are eight independent dependency chains, and there is no block barrier anywhere: the batch of
+// 32 instances is gathered by the warp itself (one instance per lane, the next batch in flight during the sweep),
+// the hit mask of instance j is eight ballots (word k = pixel slot k of every lane: exactly the layout of the
+// compact cache) collected by lane j, and the per-batch compaction is one ballot + popc.
+// -----------------------------------------------------------------------------------------------------------------
+#ifndef GSLM_FWD_MINB
+#define GSLM_FWD_MINB 16
+#endif
+__global__ void __launch_bounds__(32, GSLM_FWD_MINB) k_blend_fwd_warp(FwdArgs a) {
+    __shared__ __align__(16) float4 s_rec[WBATCH * REC_F4];
+    const int lane = threadIdx.x;
+    const int gx = (a.W + TILE_X - 1) / TILE_X;
+    const int tile = blockIdx.x;
+    const int px = (tile % gx) * TILE_X + (lane & 15);
+    const int pyb = (tile / gx) * TILE_Y + (lane >> 4);
+    const float pxf = (float)px;
+    const uint2 range = a.ranges[tile];
+    const int total = (int)(range.y - range.x);
+    const int rounds = (total + WBATCH - 1) / WBATCH;
+
+    float4 r0, r1, r2;
+    bool have = false;
+    auto fetch = [&](int b) {
+        const int k = b * WBATCH + lane;
+        have = k < total;
+        if (have) {
+            const uint32_t id = __ldg(a.point_list + range.x + k);
+            const float2 p = __ldg(a.xy + id);
+            const float4 co = __ldg(a.conic_opacity + id);
+            const float* f = a.features + 3 * (size_t)id;
+            r0 = make_float4(p.x, p.y, co.x, co.y);
+            r1 = make_float4(co.z, co.w, __ldg(f), __ldg(f + 1));
+            r2 = make_float4(__ldg(f + 2), 1.f / __ldg(a.depths + id), __uint_as_float(id), 0.f);   // forward.cu:380
+        }
+    };
+    if (rounds > 0) fetch(0);
+
+    float T[8], C0[8], C1[8], C2[8], D[8], pyf[8];
+    uint32_t last_contributor[8], last_c[8];
+    uint32_t live = 0;                       // bit k: pixel slot k still accumulating
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        T[k] = 1.0f; C0[k] = C1[k] = C2[k] = D[k] = 0.f;
+        last_contributor[k] = last_c[k] = 0;
+        const int py = pyb + 2 * k;
+        pyf[k] = (float)py;
+        if (px < a.W && py < a.H) live |= 1u << k;
+    }
+    const uint32_t inside = live;
+    uint32_t run = 0;                        // compact instances of this tile so far (warp-uniform)
+
+    for (int b = 0; b < rounds; b++) {
+        if (__all_sync(0xffffffffu, live == 0u)) break;
+        __syncwarp();                        // batch b-1 fully consumed
+        if (have) {
+            s_rec[REC_F4 * lane] = r0;
+            s_rec[REC_F4 * lane + 1] = r1;
+            s_rec[REC_F4 * lane + 2] = r2;
+        }
+        if (b + 1 < rounds) fetch(b + 1);    // in flight during the sweep below
+        __syncwarp();
+        const int n = min(WBATCH, total - b * WBATCH);
+        uint32_t mm[8];                      // lane j: hit mask of instance j of this batch
+        int last_j[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) { mm[k] = 0u; last_j[k] = -1; }
+        for (int j = 0; j < n; j++) {
+            if (__all_sync(0xffffffffu, live == 0u)) break;
+            const float4 q0 = s_rec[REC_F4 * j], q1 = s_rec[REC_F4 * j + 1], q2 = s_rec[REC_F4 * j + 2];
+            float dx, e, ff;
+            alpha_column(q0, pxf, dx, e, ff);
+            // branch-free per pixel slot: a non-blending slot adds w = 0 (C + c 0 = C exactly) and keeps T, so the
+            // bits equal the branching form while the eight slots stay independent straight-line chains
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                float dy, G = 0.f, alpha = 0.f;
+                const bool hit = alpha_pixel(q0, q1, e, ff, pyf[k], dy, G, alpha) && (live & (1u << k));
+                const float test_T = T[k] * (1.f - alpha);
+                const bool term = hit && (test_T < 0.0001f);
+                const bool blended = hit && !term;
+                if (term) live &= ~(1u << k);
+                const float w = blended ? alpha * T[k] : 0.f;
+                C0[k] += q1.z * w;
+                C1[k] += q1.w * w;
+                C2[k] += q2.x * w;
+                D[k] += q2.y * w;
+                T[k] = blended ? test_T : T[k];
+                last_contributor[k] = blended ? (uint32_t)(b * WBATCH + j + 1) : last_contributor[k];
+                last_j[k] = blended ? j : last_j[k];
+                const uint32_t bal = __ballot_sync(0xffffffffu, blended);
+                mm[k] = (lane == j) ? bal : mm[k];
+            }
+        }
+        // compaction of the batch: instances with a non-empty mask, densely and in order
+        const uint32_t f = mm[0] | mm[1] | mm[2] | mm[3] | mm[4] | mm[5] | mm[6] | mm[7];
+        const uint32_t bal = __ballot_sync(0xffffffffu, f != 0u);
+        if (f) {
+            const size_t pos = (size_t)range.x + run + __popc(bal & ((1u << lane) - 1u));
+            float4* dst = a.records_tmp + pos * REC_F4;
+            dst[0] = s_rec[REC_F4 * lane];
+            dst[1] = s_rec[REC_F4 * lane + 1];
+            dst[2] = s_rec[REC_F4 * lane + 2];
+            a.masks_tmp[2 * pos] = make_uint4(mm[0], mm[1], mm[2], mm[3]);
+            a.masks_tmp[2 * pos + 1] = make_uint4(mm[4], mm[5], mm[6], mm[7]);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++)          // the pixel's own last hit is flagged, so it is counted by the popc
+            if (last_j[k] >= 0) last_c[k] = run + __popc(bal & ((2u << last_j[k]) - 1u));
+        run += __popc(bal);
+    }
+
+    const size_t HW = (size_t)a.H * a.W;
+    const float bg0 = a.bg[0], bg1 = a.bg[1], bg2 = a.bg[2];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        if (!(inside & (1u << k))) continue;
+        const size_t pix = (size_t)(pyb + 2 * k) * a.W + px;
+        a.final_T[pix] = T[k];
+        a.n_contrib[pix] = last_contributor[k];
+        a.n_contrib_c[pix] = last_c[k];
+        a.out_color[pix] = C0[k] + T[k] * bg0;
+        a.out_color[HW + pix] = C1[k] + T[k] * bg1;
+        a.out_color[2 * HW + pix] = C2[k] + T[k] * bg2;
+        if (a.out_invdepth) a.out_invdepth[pix] = D[k];
+    }
+    if (lane == 0) a.ccount[tile] = run;
+}
+
 int launch_blend_fwd(const GeomView& gv, const BinningTemp& bt, const ImageView& iv, int W, int H,
                      const float* features, const float* bg, float* out_color, float* out_invdepth, cudaStream_t s) {
     const int tiles = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
@@ -172,7 +305,11 @@ int launch_blend_fwd(const GeomView& gv, const BinningTemp& bt, const ImageView&
     a.n_contrib = iv.n_contrib; a.n_contrib_c = iv.n_contrib_c; a.ccount = iv.ccount; a.records_tmp = bt.records_tmp; a.masks_tmp = bt.masks_tmp;
     a.out_color = out_color; a.out_invdepth = out_invdepth;
     StageScope ts(ST_BLEND_FWD, s);
+#ifdef GSLM_FWD_CTA
     k_blend_fwd<<<tiles, TILE_PIX, 0, s>>>(a);
+#else
+    k_blend_fwd_warp<<<tiles, 32, 0, s>>>(a);
+#endif
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
 }
