@@ -72,11 +72,11 @@ int32_t gslm_mark_visible(int32_t P, const float* means3D, const float* viewmatr
     return launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
 }
 
-int32_t gslm_forward(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn alloc, void* alloc_ctx,
-                     float* out_color, float* out_invdepth, int32_t* radii, int32_t* num_rendered,
-                     int32_t* num_cached, void* stream) {
+static int32_t forward_impl(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn alloc, void* alloc_ctx,
+                            float* out_color, float* out_invdepth, int32_t* radii, int32_t* num_rendered,
+                            int32_t* num_cached, bool record, void* stream) {
     if (check_inputs(g, cam)) return 1;
-    if (!alloc || !out_color || !num_rendered || !num_cached || (g->P > 0 && !radii)) {
+    if (!alloc || !out_color || !num_rendered || (record && !num_cached) || (g->P > 0 && !radii)) {
         set_error("null argument");
         return 1;
     }
@@ -104,8 +104,9 @@ int32_t gslm_forward(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn 
     if (run_binning(gv, radii, bt, iv, P, W, H, R, s)) return 1;
     if (debug_sync(cam, s, "binning")) return 1;
     const float* features = g->colors_precomp ? g->colors_precomp : gv.rgb;
-    if (launch_blend_fwd(gv, bt, iv, W, H, features, cam->bg, out_color, out_invdepth, s)) return 1;
+    if (launch_blend_fwd(gv, bt, iv, W, H, features, cam->bg, out_color, out_invdepth, record, s)) return 1;
     if (debug_sync(cam, s, "render")) return 1;
+    if (!record) return 0;      // render-only: no linearisation cache, no second read-back
     if (run_tile_scan(iv, W, H, s)) return 1;
     // host synchronisation #2: the compact cache is sized by what the forward pass actually blended
     GSLM_CUDA_OK(cudaMemcpyAsync(&Rc, iv.cstart + T, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
@@ -116,6 +117,19 @@ int32_t gslm_forward(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn 
     BinningView bv = carve_binning(bbuf, Rc);
     if (P > 0 && run_compaction(gv, bv, bt, iv, P, W, H, Rc, s)) return 1;
     return debug_sync(cam, s, "compaction");
+}
+
+int32_t gslm_forward(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn alloc, void* alloc_ctx,
+                     float* out_color, float* out_invdepth, int32_t* radii, int32_t* num_rendered,
+                     int32_t* num_cached, void* stream) {
+    return forward_impl(g, cam, alloc, alloc_ctx, out_color, out_invdepth, radii, num_rendered, num_cached, true,
+                        stream);
+}
+
+int32_t gslm_render(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn alloc, void* alloc_ctx,
+                    float* out_color, float* out_invdepth, int32_t* radii, int32_t* num_rendered, void* stream) {
+    return forward_impl(g, cam, alloc, alloc_ctx, out_color, out_invdepth, radii, num_rendered, nullptr, false,
+                        stream);
 }
 
 int32_t gslm_jvp_cached(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam, const int32_t* radii,

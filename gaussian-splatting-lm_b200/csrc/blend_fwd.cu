@@ -175,6 +175,9 @@ __global__ void __launch_bounds__(TILE_PIX) k_blend_fwd(FwdArgs a) {
 #ifndef GSLM_FWD_MINB
 #define GSLM_FWD_MINB 16
 #endif
+// RECORD = false is the render-only form (gslm_render: loss evaluations of the line search, inference): no hit
+// masks, no compaction, no n_contrib -- only the image, the inverse depth and final_T.
+template <bool RECORD>
 __global__ void __launch_bounds__(32, GSLM_FWD_MINB) k_blend_fwd_warp(FwdArgs a) {
     __shared__ __align__(16) float4 s_rec[WBATCH * REC_F4];
     const int lane = threadIdx.x;
@@ -254,12 +257,14 @@ __global__ void __launch_bounds__(32, GSLM_FWD_MINB) k_blend_fwd_warp(FwdArgs a)
                 C2[k] += q2.x * w;
                 D[k] += q2.y * w;
                 T[k] = blended ? test_T : T[k];
-                last_contributor[k] = blended ? (uint32_t)(b * WBATCH + j + 1) : last_contributor[k];
-                last_j[k] = blended ? j : last_j[k];
-                const uint32_t bal = __ballot_sync(0xffffffffu, blended);
-                mm[k] = (lane == j) ? bal : mm[k];
+                if (RECORD) {
+                    last_j[k] = blended ? j : last_j[k];
+                    const uint32_t bal = __ballot_sync(0xffffffffu, blended);
+                    mm[k] = (lane == j) ? bal : mm[k];
+                }
             }
         }
+        if (!RECORD) continue;
         // compaction of the batch: instances with a non-empty mask, densely and in order
         const uint32_t f = mm[0] | mm[1] | mm[2] | mm[3] | mm[4] | mm[5] | mm[6] | mm[7];
         const uint32_t bal = __ballot_sync(0xffffffffu, f != 0u);
@@ -274,7 +279,10 @@ __global__ void __launch_bounds__(32, GSLM_FWD_MINB) k_blend_fwd_warp(FwdArgs a)
         }
 #pragma unroll
         for (int k = 0; k < 8; k++)          // the pixel's own last hit is flagged, so it is counted by the popc
-            if (last_j[k] >= 0) last_c[k] = run + __popc(bal & ((2u << last_j[k]) - 1u));
+            if (last_j[k] >= 0) {
+                last_contributor[k] = (uint32_t)(b * WBATCH + last_j[k] + 1);
+                last_c[k] = run + __popc(bal & ((2u << last_j[k]) - 1u));
+            }
         run += __popc(bal);
     }
 
@@ -285,18 +293,21 @@ __global__ void __launch_bounds__(32, GSLM_FWD_MINB) k_blend_fwd_warp(FwdArgs a)
         if (!(inside & (1u << k))) continue;
         const size_t pix = (size_t)(pyb + 2 * k) * a.W + px;
         a.final_T[pix] = T[k];
-        a.n_contrib[pix] = last_contributor[k];
-        a.n_contrib_c[pix] = last_c[k];
+        if (RECORD) {
+            a.n_contrib[pix] = last_contributor[k];
+            a.n_contrib_c[pix] = last_c[k];
+        }
         a.out_color[pix] = C0[k] + T[k] * bg0;
         a.out_color[HW + pix] = C1[k] + T[k] * bg1;
         a.out_color[2 * HW + pix] = C2[k] + T[k] * bg2;
         if (a.out_invdepth) a.out_invdepth[pix] = D[k];
     }
-    if (lane == 0) a.ccount[tile] = run;
+    if (RECORD && lane == 0) a.ccount[tile] = run;
 }
 
 int launch_blend_fwd(const GeomView& gv, const BinningTemp& bt, const ImageView& iv, int W, int H,
-                     const float* features, const float* bg, float* out_color, float* out_invdepth, cudaStream_t s) {
+                     const float* features, const float* bg, float* out_color, float* out_invdepth, bool record,
+                     cudaStream_t s) {
     const int tiles = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
     if (tiles == 0) return 0;
     FwdArgs a;
@@ -306,9 +317,11 @@ int launch_blend_fwd(const GeomView& gv, const BinningTemp& bt, const ImageView&
     a.out_color = out_color; a.out_invdepth = out_invdepth;
     StageScope ts(ST_BLEND_FWD, s);
 #ifdef GSLM_FWD_CTA
-    k_blend_fwd<<<tiles, TILE_PIX, 0, s>>>(a);
+    if (record) k_blend_fwd<<<tiles, TILE_PIX, 0, s>>>(a);
+    else k_blend_fwd_warp<false><<<tiles, 32, 0, s>>>(a);
 #else
-    k_blend_fwd_warp<<<tiles, 32, 0, s>>>(a);
+    if (record) k_blend_fwd_warp<true><<<tiles, 32, 0, s>>>(a);
+    else k_blend_fwd_warp<false><<<tiles, 32, 0, s>>>(a);
 #endif
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;

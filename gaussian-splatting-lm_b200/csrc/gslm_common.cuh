@@ -155,7 +155,8 @@ int run_compaction(const GeomView& gv, const BinningView& bv, const BinningTemp&
                    int W, int H, int64_t Rc, cudaStream_t s);
 // blend.cu
 int launch_blend_fwd(const GeomView& gv, const BinningTemp& bt, const ImageView& iv, int W, int H,
-                     const float* features, const float* bg, float* out_color, float* out_invdepth, cudaStream_t s);
+                     const float* features, const float* bg, float* out_color, float* out_invdepth, bool record,
+                     cudaStream_t s);
 int launch_blend_jvp(const BinningView& bv, const ImageView& iv, int W, int H, const float4* tgeom, const float* bg,
                      const float* bg_tangent, float* out_color_t, float* out_invdepth_t, cudaStream_t s);
 int launch_blend_bwd(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg,

@@ -92,7 +92,7 @@ def _cached(R, imageBuffer=None, W=None, H=None):
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_int32, C.c_size_t)
 
 EXPORTS = ("gslm_last_error", "gslm_abi_version", "gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_binning_temp_bytes",
-           "gslm_mark_visible", "gslm_forward", "gslm_forward_jvp", "gslm_backward_scratch_bytes", "gslm_backward",
+           "gslm_mark_visible", "gslm_forward", "gslm_render", "gslm_forward_jvp", "gslm_backward_scratch_bytes", "gslm_backward",
            "gslm_jvp_scratch_bytes", "gslm_jvp_cached", "gslm_jtjv_scratch_bytes", "gslm_jtjv",
            "gslm_jtjv_batch_scratch_bytes", "gslm_jtjv_batch", "gslm_loss_lin_bytes", "gslm_loss_blocks",
            "gslm_loss_blocks_jvp", "gslm_loss_blocks_vjp", "gslm_activation_jvp", "gslm_activation_vjp",
@@ -122,6 +122,7 @@ def lib():
         vp = C.c_void_p
         L.gslm_mark_visible.argtypes = [C.c_int32, vp, vp, vp, vp, vp]
         L.gslm_forward.argtypes = [vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp, vp]
+        L.gslm_render.argtypes = [vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp]
         L.gslm_forward_jvp.argtypes = [vp, vp, vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         L.gslm_backward.argtypes = [vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
         L.gslm_jvp_cached.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp]
@@ -291,6 +292,31 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
                           out_invdepth.data_ptr(), radii.data_ptr(), C.addressof(n), C.addressof(nc), _stream()))
     _after_forward(al)
     return NumRendered(n.value, nc.value), out_color, radii, al.get(0), al.get(1), al.get(2), out_invdepth
+
+
+def render_only(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
+                antialiasing, debug):
+    """The forward pass without the linearisation cache (gslm_render): (num_rendered, color, radii, invdepth).
+    Same arguments as rasterize_gaussians; nothing that comes out of it can be differentiated."""
+    L = lib()
+    dev = means3D.device
+    g, k1 = _gaussians(means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, sh, degree)
+    cam, k2 = _camera(background, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, campos,
+                      prefiltered, antialiasing, debug)
+    P, H, W = g.P, int(image_height), int(image_width)
+    out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+    out_invdepth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+    radii = torch.zeros((P,), dtype=torch.int32, device=dev)
+    if P == 0:
+        out_color.zero_(); out_invdepth.zero_()
+        return 0, out_color, radii, out_invdepth
+    al = _Alloc(dev)
+    n = C.c_int32(0)
+    _check(L.gslm_render(C.addressof(g), C.addressof(cam), al.cb, None, out_color.data_ptr(),
+                         out_invdepth.data_ptr(), radii.data_ptr(), C.addressof(n), _stream()))
+    _after_forward(al)
+    return n.value, out_color, radii, out_invdepth
 
 
 def rasterize_gaussians_jvp(background, background_grad, means3D, means3D_grad, colors, colors_grad, opacity,

@@ -112,8 +112,7 @@ def lm_step(loss_func, gaussians, train_cams, val_cams=None, damp=None, param_ma
                               batch_size=batch_size)
 
     def val_loss():
-        V.evaluate_loss()
-        return V.loss_scalar
+        return V.loss_value()          # render-only passes: no linearisation cache for points that are only compared
 
     best_alpha, best_loss, trace = line_search(gaussians, s, val_loss, alpha0, halvings)
     final = float(val_loss())

@@ -211,7 +211,7 @@ class LinearSolverFunctions:
     def _kw(self, name, default=None):
         return self.loss_func.keywords.get(name, default)
 
-    def _activated(self):
+    def _activated(self, with_layer=True):
         """Kernel inputs at the linearisation point + what the activation JVP / VJP need."""
         g = self.gaussians
         with torch.no_grad():
@@ -221,6 +221,8 @@ class LinearSolverFunctions:
                    "scales": torch.exp(g._scaling.detach()), "rotations": raw_rot / norm, "rot_norm": norm,
                    "shs": torch.cat((g._features_dc.detach(), g._features_rest.detach()), dim=1).contiguous(),
                    "sh_degree": int(g.active_sh_degree)}
+            if not with_layer:
+                return act
             # the differentiated activation layer (csrc/param_space.cu) + its persistent tangent buffers
             act["layer"] = _C.Activations(act["scales"], act["rotations"], act["rot_norm"], act["opacities"],
                                           act["shs"].shape[1])
@@ -285,6 +287,43 @@ class LinearSolverFunctions:
                 losses.append(BatchLossImageState(resid, resid, depth_block, sizes, False))
         self.loss = MultiBatchLossImageState(losses)
         return self.loss
+
+    def loss_value(self):
+        """||r(theta)||^2 at the current parameters as a 0-dim device tensor, WITHOUT building a linearisation:
+        render-only forward passes (gslm_render) and the residual reduced on the fly.  What the back-tracking line
+        search needs (train_jvp.py:262-279 calls evaluate_loss + loss_scalar seven times per LM step)."""
+        if not self.cached:
+            self.evaluate_loss()
+            return self.loss_scalar
+        pipe, bg = self._kw("pipe"), self._kw("bg")
+        dev = self.gaussians._xyz.device
+        empty = torch.empty(0, device=dev)
+        a = self._activated(with_layer=False)
+        total = torch.zeros((), dtype=torch.float32, device=dev)
+        for start, end in self._batches():
+            cams = self.viewpoint_cams[start:end]
+            Hm, Wm = max(c.image_height for c in cams), max(c.image_width for c in cams)
+            images = torch.zeros((len(cams), 3, Hm, Wm), dtype=torch.float32, device=dev)
+            gt, masks = gather_targets(cams, images)
+            for i, cam in enumerate(cams):
+                H, W = int(cam.image_height), int(cam.image_width)
+                _, color, _, _ = _C.render_only(
+                    bg, a["means3D"], empty, a["opacities"], a["scales"], a["rotations"], 1.0, empty,
+                    cam.world_view_transform, cam.full_proj_transform, math.tan(cam.FoVx * 0.5),
+                    math.tan(cam.FoVy * 0.5), H, W, a["shs"], a["sh_degree"], cam.camera_center, False,
+                    pipe.antialiasing, pipe.debug)
+                images[i, :, :H, :W].copy_(color.clamp_(0, 1))
+            if self.ssim:
+                lam = self._kw("opt").lambda_dssim
+                sizes = [(c.image_height, c.image_width) for c in cams]
+                al = torch.tensor([math.sqrt((1.0 - lam) / (3 * h * w)) for h, w in sizes], device=dev)
+                be = torch.tensor([math.sqrt(lam / (3 * h * w)) for h, w in sizes], device=dev)
+                r1, r2 = _C.LossBatch(images, masks, gt, al, be).blocks(want_lin=False)
+                total = total + torch.linalg.vector_norm(r1) ** 2 + torch.linalg.vector_norm(r2) ** 2
+            else:
+                r = (images * masks if masks is not None else images) - gt
+                total = total + 2.0 * torch.linalg.vector_norm(r) ** 2     # two aliased blocks
+        return self._scalar(total)
 
     def _tangent_inputs(self, v):
         """Activation JVP: raw-parameter tangent -> tangents of the kernel inputs (scene/gaussian_model.py:192-220),

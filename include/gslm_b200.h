@@ -116,6 +116,15 @@ int32_t gslm_forward(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn 
                      float* out_color, float* out_invdepth, int32_t* radii, int32_t* num_rendered,
                      int32_t* num_cached, void* stream);
 
+/* The same forward pass WITHOUT the linearisation cache: image, inverse depth, radii and final_T only (the
+ * binning buffer is never requested from the allocator, n_contrib is not written, there is one host read-back
+ * instead of two).  For evaluations that are never differentiated -- the back-tracking line search of
+ * train_jvp.py:262-279 renders 7 x 50 views per LM step this way, and so does inference.  The reference has no
+ * such split (its forward always keeps the state for backward).  Buffers left by this call must NOT be handed to
+ * gslm_backward / gslm_jvp_cached / gslm_jtjv*. */
+int32_t gslm_render(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn alloc, void* alloc_ctx,
+                    float* out_color, float* out_invdepth, int32_t* radii, int32_t* num_rendered, void* stream);
+
 /* Replaces _C.rasterize_gaussians_jvp (DGR/rasterize_points.cu:143-298; forwardJvp,
  * DGR/cuda_rasterizer/rasterizer_jvp_impl.h:125-325).  `gt` holds the tangent pointers in
  * the same fields as `g` (NULL => zero tangent; P/sh_degree/M/scale_modifier ignored,

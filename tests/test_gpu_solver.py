@@ -245,3 +245,27 @@ def test_activation_layer_kernels_match_torch_autograd(P, M):
     layer.vjp(*g, out2, v, D.values()[:6])
     for a, b, tv, d in zip(out2.tensors()[:6], out.tensors()[:6], v.tensors()[:6], D.values()):
         assert torch.allclose(a, b + d * tv, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("ssim", [False, True])
+def test_render_only_loss_value_matches_linearised_loss(ssim):
+    """gslm_render (no linearisation cache) gives the same image bits as gslm_forward, and
+    LinearSolverFunctions.loss_value() -- the line-search evaluation -- the same ||r||^2 as evaluate_loss()."""
+    import math
+    from diff_gaussian_rasterization import _C
+    from solver.solver_functions import LinearSolverFunctions
+    model, cams, loss_func, pipe, bg = _setup()
+    if ssim:
+        loss_func = functools.partial(loss_func.func, **{**loss_func.keywords, "disable_ssim": False})
+    F = LinearSolverFunctions(loss_func, model, cams, batch_size=3)
+    F.evaluate_loss()
+    ref = float(F.loss_scalar)
+    val = float(F.loss_value())
+    assert abs(val - ref) <= 1e-5 * abs(ref)
+    a, cam, e = F._act, cams[0], torch.empty(0, device="cuda")
+    args = (bg, a["means3D"], e, a["opacities"], a["scales"], a["rotations"], 1.0, e, cam.world_view_transform,
+            cam.full_proj_transform, math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), cam.image_height,
+            cam.image_width, a["shs"], a["sh_degree"], cam.camera_center, False, False, False)
+    full = _C.rasterize_gaussians(*args)
+    n, color, radii, invd = _C.render_only(*args)
+    assert n == int(full[0]) and torch.equal(color, full[1]) and torch.equal(radii, full[2]) and torch.equal(invd, full[6])

@@ -82,8 +82,7 @@ def main():
             Vf = LinearSolverFunctions(loss_func, model, val, batch_size=bs)
 
             def val_loss():
-                Vf.evaluate_loss()
-                return Vf.loss_scalar
+                return Vf.loss_value()
 
             best_alpha, best_loss, trace = line_search(model, s, val_loss)
             t4 = tick()
