@@ -305,6 +305,112 @@ int32_t gslm_jtjv_batch(const GslmGaussians* g, const GslmGaussians* gt, int32_t
     return 0;
 }
 
+// ---- batched linear maps on cached linearisations (matvec / matvec_T of the solver) ----
+size_t gslm_jvp_batch_scratch_bytes(int32_t P, int32_t n_views) {
+    const int n = n_views < MAX_BATCH_VIEWS ? n_views : MAX_BATCH_VIEWS;
+    return (size_t)(n > 0 ? n : 0) * align_up((size_t)P * REC_F4 * sizeof(float4)) + 128;
+}
+
+int32_t gslm_jvp_batch(const GslmGaussians* g, const GslmGaussians* gt, int32_t n_views, const GslmCamera* cams,
+                       const void* const* geom_buffers, const void* const* binning_buffers,
+                       const void* const* image_buffers, const int32_t* num_cached, void* scratch, size_t scratch_bytes,
+                       float* const* out_color_tangent, void* stream) {
+    if (n_views < 0 || (n_views > 0 && (!cams || !geom_buffers || !binning_buffers || !image_buffers || !num_cached ||
+                                        !scratch || !out_color_tangent)) || !g) {
+        set_error("null argument");
+        return 1;
+    }
+    if (scratch_bytes < gslm_jvp_batch_scratch_bytes(g->P, n_views)) {
+        set_error("scratch too small: need %zu bytes", gslm_jvp_batch_scratch_bytes(g->P, n_views));
+        return 1;
+    }
+    for (int v = 0; v < n_views; v++)
+        if (check_inputs(g, &cams[v])) return 1;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int P = g->P;
+    TangentPtrs t = make_tangents(gt, nullptr);
+    for (int v0 = 0; v0 < n_views; v0 += MAX_BATCH_VIEWS) {
+        const int n = (n_views - v0) < MAX_BATCH_VIEWS ? (n_views - v0) : MAX_BATCH_VIEWS;
+        GeomView gv[MAX_BATCH_VIEWS];
+        ImageView iv[MAX_BATCH_VIEWS];
+        BinningView bv[MAX_BATCH_VIEWS];
+        float4* tgeom[MAX_BATCH_VIEWS];
+        char* p = reinterpret_cast<char*>(align_up((size_t)scratch));
+        for (int i = 0; i < n; i++) {
+            const int v = v0 + i;
+            gv[i] = carve_geom(const_cast<void*>(geom_buffers[v]), P);
+            iv[i] = carve_image(const_cast<void*>(image_buffers[v]), cams[v].width, cams[v].height);
+            bv[i] = carve_binning(const_cast<void*>(binning_buffers[v]), num_cached[v]);
+            tgeom[i] = reinterpret_cast<float4*>(p);
+            p += align_up((size_t)P * REC_F4 * sizeof(float4));
+        }
+        if (P > 0 && launch_preprocess_tangent_batch(*g, t, n, cams + v0, gv, tgeom, s)) return 1;
+        if (launch_blend_jvp_batch(n, bv, iv, cams + v0, tgeom, out_color_tangent + v0, s)) return 1;
+    }
+    return 0;
+}
+
+size_t gslm_backward_batch_scratch_bytes(int32_t n_views, const int32_t* num_cached) {
+    size_t worst = 0;
+    for (int v0 = 0; v0 < n_views; v0 += MAX_BATCH_VIEWS) {
+        size_t need = 0;
+        for (int v = v0; v < n_views && v < v0 + MAX_BATCH_VIEWS; v++)
+            need += gslm_backward_scratch_bytes(num_cached ? num_cached[v] : 0);
+        worst = need > worst ? need : worst;
+    }
+    return worst;
+}
+
+int32_t gslm_backward_batch(const GslmGaussians* g, int32_t n_views, const GslmCamera* cams,
+                            const int32_t* const* radii, const void* const* geom_buffers,
+                            const void* const* binning_buffers, const void* const* image_buffers,
+                            const int32_t* num_cached, const float* const* dL_dcolor, void* scratch,
+                            size_t scratch_bytes, GslmGrads* grads, void* stream) {
+    if (n_views < 0 || (n_views > 0 && (!cams || !radii || !geom_buffers || !binning_buffers || !image_buffers ||
+                                        !num_cached || !scratch || !dL_dcolor)) || !grads || !g) {
+        set_error("null argument");
+        return 1;
+    }
+    if (scratch_bytes < gslm_backward_batch_scratch_bytes(n_views, num_cached)) {
+        set_error("scratch too small: need %zu bytes", gslm_backward_batch_scratch_bytes(n_views, num_cached));
+        return 1;
+    }
+    for (int v = 0; v < n_views; v++)
+        if (check_inputs(g, &cams[v])) return 1;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int P = g->P;
+    if (P == 0) return 0;
+    GslmGrads acc = *grads;
+    if (!acc.accumulate) {   // overwrite semantics = clear, then accumulate every view
+        const size_t n = (size_t)P;
+        struct { float* p; size_t count; } sinks[8] = {
+            {acc.dL_dmeans2D, 3 * n}, {acc.dL_dcolors, 3 * n}, {acc.dL_dopacity, n}, {acc.dL_dmeans3D, 3 * n},
+            {acc.dL_dcov3D, 6 * n}, {acc.dL_dsh, 3 * n * (size_t)g->M}, {acc.dL_dscales, 3 * n}, {acc.dL_drotations, 4 * n}};
+        for (auto& k : sinks)
+            if (k.p && k.count) GSLM_CUDA_OK(cudaMemsetAsync(k.p, 0, k.count * sizeof(float), s));
+        acc.accumulate = 1;
+    }
+    for (int v0 = 0; v0 < n_views; v0 += MAX_BATCH_VIEWS) {
+        const int n = (n_views - v0) < MAX_BATCH_VIEWS ? (n_views - v0) : MAX_BATCH_VIEWS;
+        GeomView gv[MAX_BATCH_VIEWS];
+        ImageView iv[MAX_BATCH_VIEWS];
+        BinningView bv[MAX_BATCH_VIEWS];
+        float4* inst[MAX_BATCH_VIEWS];
+        char* p = reinterpret_cast<char*>(align_up((size_t)scratch));
+        for (int i = 0; i < n; i++) {
+            const int v = v0 + i;
+            gv[i] = carve_geom(const_cast<void*>(geom_buffers[v]), P);
+            iv[i] = carve_image(const_cast<void*>(image_buffers[v]), cams[v].width, cams[v].height);
+            bv[i] = carve_binning(const_cast<void*>(binning_buffers[v]), num_cached[v]);
+            inst[i] = reinterpret_cast<float4*>(p);
+            p += align_up((size_t)num_cached[v] * REC_F4 * sizeof(float4));
+        }
+        if (launch_blend_bwd_batch(n, bv, iv, cams + v0, dL_dcolor + v0, inst, s)) return 1;
+        if (launch_preprocess_bwd_views(*g, n, cams + v0, radii + v0, gv, inst, acc, s)) return 1;
+    }
+    return 0;
+}
+
 int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_rendered, int64_t num_cached,
                          const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
                          const void* binning_temp_buffer, GslmBufferView* out) {

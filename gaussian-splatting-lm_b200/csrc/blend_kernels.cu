@@ -65,9 +65,9 @@ __device__ __forceinline__ void init_ring(WarpRing& ring, const WTile& c, const 
 }
 
 template <bool WITH_D>
-__global__ void __launch_bounds__(DTHREADS)
-k_blend_jvp(TileArgs a, const float4* __restrict__ tgeom, const float* __restrict__ bg_t,
-            float* __restrict__ out_color_t, float* __restrict__ out_invdepth_t) {
+__device__ __forceinline__ void
+blend_jvp_body(const TileArgs& a, const float4* __restrict__ tgeom, const float* __restrict__ bg_t,
+               float* __restrict__ out_color_t, float* __restrict__ out_invdepth_t) {
     __shared__ __align__(128) float4 s_rec[DWARPS][RING_F4];
     __shared__ __align__(128) uint4 s_msk[DWARPS][RING_U4];
     __shared__ __align__(16) float4 s_tan[DWARPS][RING_F4];
@@ -96,12 +96,34 @@ k_blend_jvp(TileArgs a, const float4* __restrict__ tgeom, const float* __restric
     }
 }
 
+template <bool WITH_D>
+__global__ void __launch_bounds__(DTHREADS)
+k_blend_jvp(TileArgs a, const float4* __restrict__ tgeom, const float* __restrict__ bg_t,
+            float* __restrict__ out_color_t, float* __restrict__ out_invdepth_t) {
+    blend_jvp_body<WITH_D>(a, tgeom, bg_t, out_color_t, out_invdepth_t);
+}
+
+// Up to MAX_BATCH_VIEWS linearised views per launch (blockIdx.y), colour only: what LinearSolverFunctions.matvec /
+// matvec_T issue per chunk of views (the reference's CGLS path, solver/conjugate_gradient.py:51-127, calls both
+// every iteration), and the two tile passes of the L1 + SSIM normal product.
+struct ViewBatch {
+    TileArgs t[MAX_BATCH_VIEWS];
+    const float4* tgeom[MAX_BATCH_VIEWS];      // JVP: per-Gaussian tangent records
+    float* out_color_t[MAX_BATCH_VIEWS];       // JVP: image tangent [3,H,W]
+    const float* dL_dcolor[MAX_BATCH_VIEWS];   // VJP: image cotangent [3,H,W]
+    float4* inst_grads[MAX_BATCH_VIEWS];       // VJP: per-instance gradient records
+};
+
+__global__ void __launch_bounds__(DTHREADS) k_blend_jvp_batch(const __grid_constant__ ViewBatch vb) {
+    blend_jvp_body<false>(vb.t[blockIdx.y], vb.tgeom[blockIdx.y], nullptr, vb.out_color_t[blockIdx.y], nullptr);
+}
+
 __device__ __forceinline__ void set_lane(f2& v, bool hi, float x) { if (hi) v.y = x; else v.x = x; }
 
 template <bool WITH_D>
-__global__ void __launch_bounds__(DTHREADS)
-k_blend_bwd(TileArgs a, const float* __restrict__ dL_dcolor, const float* __restrict__ dL_dinvdepth,
-            float4* __restrict__ inst_grads) {
+__device__ __forceinline__ void
+blend_bwd_body(const TileArgs& a, const float* __restrict__ dL_dcolor, const float* __restrict__ dL_dinvdepth,
+               float4* __restrict__ inst_grads) {
     __shared__ __align__(128) float4 s_rec[DWARPS][RING_F4];
     __shared__ __align__(128) uint4 s_msk[DWARPS][RING_U4];
     __shared__ float s_acc[DWARPS][(WBATCH + 1) * ACC_STRIDE];
@@ -126,6 +148,17 @@ k_blend_bwd(TileArgs a, const float* __restrict__ dL_dcolor, const float* __rest
     }
     const float bgv[3] = {a.bg[0], a.bg[1], a.bg[2]};
     adjoint_sweep<WITH_D>(c, ring, s_acc[warp], bgv, sa, a.g_inv, inst_grads);
+}
+
+template <bool WITH_D>
+__global__ void __launch_bounds__(DTHREADS)
+k_blend_bwd(TileArgs a, const float* __restrict__ dL_dcolor, const float* __restrict__ dL_dinvdepth,
+            float4* __restrict__ inst_grads) {
+    blend_bwd_body<WITH_D>(a, dL_dcolor, dL_dinvdepth, inst_grads);
+}
+
+__global__ void __launch_bounds__(DTHREADS) k_blend_bwd_batch(const __grid_constant__ ViewBatch vb) {
+    blend_bwd_body<false>(vb.t[blockIdx.y], vb.dL_dcolor[blockIdx.y], nullptr, vb.inst_grads[blockIdx.y]);
 }
 
 // Up to MAX_BATCH_VIEWS linearised views per launch (blockIdx.y): the tail of one view's tiles overlaps the next
@@ -246,6 +279,44 @@ int launch_blend_jtjv_batch(int n_views, const BinningView* bvs, const ImageView
     if (max_tiles == 0 || n_views == 0) return 0;
     StageScope ts(ST_BLEND_JTJV, s);
     k_blend_jtjv<<<dim3(grid_of(max_tiles), n_views), DTHREADS, 0, s>>>(vb, out_vJJv);
+    GSLM_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int launch_blend_jvp_batch(int n_views, const BinningView* bvs, const ImageView* ivs, const GslmCamera* cams,
+                           const float4* const* tgeoms, float* const* out_color_t, cudaStream_t s) {
+    if (n_views > MAX_BATCH_VIEWS) { set_error("too many views in one batch"); return 1; }
+    ViewBatch vb;
+    memset(&vb, 0, sizeof(vb));
+    int max_tiles = 0;
+    for (int i = 0; i < n_views; i++) {
+        vb.t[i] = tile_args(bvs[i], ivs[i], cams[i].width, cams[i].height, cams[i].bg);
+        vb.tgeom[i] = tgeoms[i];
+        vb.out_color_t[i] = out_color_t[i];
+        max_tiles = max_tiles > vb.t[i].tiles ? max_tiles : vb.t[i].tiles;
+    }
+    if (max_tiles == 0 || n_views == 0) return 0;
+    StageScope ts(ST_BLEND_JVP, s);
+    k_blend_jvp_batch<<<dim3(grid_of(max_tiles), n_views), DTHREADS, 0, s>>>(vb);
+    GSLM_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int launch_blend_bwd_batch(int n_views, const BinningView* bvs, const ImageView* ivs, const GslmCamera* cams,
+                           const float* const* dL_dcolor, float4* const* inst_grads, cudaStream_t s) {
+    if (n_views > MAX_BATCH_VIEWS) { set_error("too many views in one batch"); return 1; }
+    ViewBatch vb;
+    memset(&vb, 0, sizeof(vb));
+    int max_tiles = 0;
+    for (int i = 0; i < n_views; i++) {
+        vb.t[i] = tile_args(bvs[i], ivs[i], cams[i].width, cams[i].height, cams[i].bg);
+        vb.dL_dcolor[i] = dL_dcolor[i];
+        vb.inst_grads[i] = inst_grads[i];
+        max_tiles = max_tiles > vb.t[i].tiles ? max_tiles : vb.t[i].tiles;
+    }
+    if (max_tiles == 0 || n_views == 0) return 0;
+    StageScope ts(ST_BLEND_BWD, s);
+    k_blend_bwd_batch<<<dim3(grid_of(max_tiles), n_views), DTHREADS, 0, s>>>(vb);
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
 }

@@ -163,6 +163,10 @@ int launch_blend_bwd(const BinningView& bv, const ImageView& iv, int W, int H, c
                      const float* dL_dcolor, const float* dL_dinvdepth, float4* inst_grads, cudaStream_t s);
 int launch_blend_jtjv(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg,
                       const float4* tgeom, const float* weight, float4* inst_grads, float* out_vJJv, cudaStream_t s);
+int launch_blend_jvp_batch(int n_views, const BinningView* bvs, const ImageView* ivs, const GslmCamera* cams,
+                           const float4* const* tgeoms, float* const* out_color_t, cudaStream_t s);
+int launch_blend_bwd_batch(int n_views, const BinningView* bvs, const ImageView* ivs, const GslmCamera* cams,
+                           const float* const* dL_dcolor, float4* const* inst_grads, cudaStream_t s);
 // up to MAX_BATCH_VIEWS views in one launch; weights may be null (all ones) or hold null entries
 int launch_blend_jtjv_batch(int n_views, const BinningView* bvs, const ImageView* ivs, const GslmCamera* cams,
                             const float4* const* tgeoms, const float* const* weights, float4* const* inst_grads,

@@ -94,7 +94,8 @@ ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_int32, C.c_size_t)
 EXPORTS = ("gslm_last_error", "gslm_abi_version", "gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_binning_temp_bytes",
            "gslm_mark_visible", "gslm_forward", "gslm_render", "gslm_forward_jvp", "gslm_backward_scratch_bytes", "gslm_backward",
            "gslm_jvp_scratch_bytes", "gslm_jvp_cached", "gslm_jtjv_scratch_bytes", "gslm_jtjv",
-           "gslm_jtjv_batch_scratch_bytes", "gslm_jtjv_batch", "gslm_loss_lin_bytes", "gslm_loss_blocks",
+           "gslm_jtjv_batch_scratch_bytes", "gslm_jtjv_batch", "gslm_jvp_batch_scratch_bytes", "gslm_jvp_batch",
+           "gslm_backward_batch_scratch_bytes", "gslm_backward_batch", "gslm_loss_lin_bytes", "gslm_loss_blocks",
            "gslm_loss_blocks_jvp", "gslm_loss_blocks_vjp", "gslm_activation_jvp", "gslm_activation_vjp",
            "gslm_buffer_view", "gslm_timing_num_stages",
            "gslm_timing_stage_name", "gslm_timing_enable", "gslm_timing_collect")
@@ -110,7 +111,8 @@ def lib():
         L.gslm_last_error.restype = C.c_char_p
         for n in ("gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_binning_temp_bytes",
                   "gslm_backward_scratch_bytes",
-                  "gslm_jvp_scratch_bytes", "gslm_jtjv_scratch_bytes", "gslm_jtjv_batch_scratch_bytes"):
+                  "gslm_jvp_scratch_bytes", "gslm_jtjv_scratch_bytes", "gslm_jtjv_batch_scratch_bytes",
+                  "gslm_jvp_batch_scratch_bytes", "gslm_backward_batch_scratch_bytes"):
             getattr(L, n).restype = C.c_size_t
         L.gslm_geom_bytes.argtypes = [C.c_int32]
         L.gslm_image_bytes.argtypes = [C.c_int32, C.c_int32]
@@ -129,6 +131,10 @@ def lib():
         L.gslm_jtjv.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
         L.gslm_jtjv_batch_scratch_bytes.argtypes = [C.c_int32, C.c_int32, vp]
         L.gslm_jtjv_batch.argtypes = [vp, vp, C.c_int32, vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, vp, vp, vp]
+        L.gslm_jvp_batch_scratch_bytes.argtypes = [C.c_int32, C.c_int32]
+        L.gslm_jvp_batch.argtypes = [vp, vp, C.c_int32, vp, vp, vp, vp, vp, vp, C.c_size_t, vp, vp]
+        L.gslm_backward_batch_scratch_bytes.argtypes = [C.c_int32, vp]
+        L.gslm_backward_batch.argtypes = [vp, C.c_int32, vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, vp, vp]
         L.gslm_loss_lin_bytes.restype = C.c_size_t
         L.gslm_loss_lin_bytes.argtypes = [C.c_int32, C.c_int32, C.c_int32]
         L.gslm_loss_blocks.argtypes = [vp, vp, vp, vp, vp]
@@ -510,6 +516,35 @@ def jtjv_batch(gauss_args, tangent_args, plan, outs, out_vJJv=None, accumulate=T
                              vp(plan.binning), vp(plan.image), vp(plan.num_cached),
                              vp(plan.weights) if plan.any_weight else None, scratch.data_ptr(), scratch.numel(),
                              C.addressof(gr), _ptr(out_vJJv), _stream()))
+
+
+def jvp_batch(gauss_args, tangent_args, plan, out_images):
+    """out_images[v] ([3,H_v,W_v] contiguous fp32 CUDA tensors, one per view of the plan) <- J_v v."""
+    L = lib()
+    g, k1 = _gaussians(*gauss_args)
+    gt, k3 = _tangent_gaussians(*tangent_args)
+    scratch = plan.scratch_for(g.P)            # the J^T J v scratch is a superset of what this call needs
+    outs = (C.c_void_p * max(plan.n, 1))(*[_ptr(t) for t in out_images])
+    vp = lambda a: C.cast(a, C.c_void_p)
+    _check(L.gslm_jvp_batch(C.addressof(g), C.addressof(gt), plan.n, vp(plan.cams), vp(plan.geom), vp(plan.binning),
+                            vp(plan.image), vp(plan.num_cached), scratch.data_ptr(), scratch.numel(), vp(outs),
+                            _stream()))
+
+
+def backward_batch(gauss_args, plan, cot_images, outs, accumulate=True):
+    """outs (8-tuple like rasterize_gaussians_backward) (+)= sum over the plan's views of J_v^T cot_images[v]."""
+    L = lib()
+    g, k1 = _gaussians(*gauss_args)
+    scratch = plan.scratch_for(g.P)
+    cots = (C.c_void_p * max(plan.n, 1))(*[_ptr(t) for t in cot_images])
+    gr = GslmGrads()
+    (gr.dL_dmeans2D, gr.dL_dcolors, gr.dL_dopacity, gr.dL_dmeans3D, gr.dL_dcov3D, gr.dL_dsh, gr.dL_dscales,
+     gr.dL_drotations) = [_ptr(o) for o in outs]
+    gr.accumulate = 1 if accumulate else 0
+    vp = lambda a: C.cast(a, C.c_void_p)
+    _check(L.gslm_backward_batch(C.addressof(g), plan.n, vp(plan.cams), vp(plan.radii), vp(plan.geom),
+                                 vp(plan.binning), vp(plan.image), vp(plan.num_cached), vp(cots), scratch.data_ptr(),
+                                 scratch.numel(), C.addressof(gr), _stream()))
 
 
 def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer, sortScratch=None):

@@ -372,71 +372,89 @@ class LinearSolverFunctions:
         if self._views is None:
             self.linearize()
 
-    def _matvec_cached(self, v):
-        self._require_linearized()
-        targs = self._tangent_inputs(v)
-        gargs = self._gauss_args()
-        out, k = [], 0
+    def _get_plan(self):
+        if self._plan is None:
+            self._plan = _C.JtjvBatchPlan([(vc.cam_args, vc.radii, vc.geom, vc.R, vc.binning, vc.img, vc.weight)
+                                           for vc in self._views], self._act["means3D"].device)
+        return self._plan
+
+    def _image_tangents(self, gargs, targs):
+        """J_r v for every local view in ONE library call (16 views per kernel launch): per batch of views a padded
+        [n,3,Hmax,Wmax] tensor holding mask * (J v)."""
+        dev = self._act["means3D"].device
+        tens, dests, staged, k = [], [], [], 0
         for start, end in self._batches():
             cams = self.viewpoint_cams[start:end]
             Hm, Wm = max(c.image_height for c in cams), max(c.image_width for c in cams)
-            t = torch.zeros((len(cams), 3, Hm, Wm), dtype=torch.float32, device=v.xyz_grad.device)
+            uniform = all((c.image_height, c.image_width) == (Hm, Wm) for c in cams)
+            t = (torch.empty if uniform else torch.zeros)((len(cams), 3, Hm, Wm), dtype=torch.float32, device=dev)
             for i in range(len(cams)):
-                vc = self._views[k]
-                k += 1
-                jv, _ = _C.jvp_cached(gargs, targs, vc.cam_args, vc.radii, vc.geom, vc.R, vc.binning, vc.img)
-                t[i, :, :vc.H, :vc.W] = jv * vc.mask
+                vc = self._views[k + i]
+                if (vc.H, vc.W) == (Hm, Wm):
+                    dests.append(t[i])                       # contiguous: the kernel writes in place
+                else:
+                    buf = torch.empty((3, vc.H, vc.W), dtype=torch.float32, device=dev)
+                    dests.append(buf)
+                    staged.append((t, i, buf, vc))
+            tens.append(t)
+            k += len(cams)
+        _C.jvp_batch(gargs, targs, self._get_plan(), dests)
+        for t, i, buf, vc in staged:
+            t[i, :, :vc.H, :vc.W] = buf
+        k = 0
+        for t in tens:
+            for i in range(t.shape[0]):
+                vc = self._views[k + i]
+                t[i, :, :vc.H, :vc.W].mul_(vc.mask)
+            k += t.shape[0]
+        return tens
+
+    def _pull_back(self, cots, sinks):
+        """sinks += sum over local views of J_r^T (mask * cot): ONE library call; cots = per-batch padded tensors."""
+        per_view, k = [], 0
+        for cot in cots:
+            for i in range(cot.shape[0]):
+                vc = self._views[k + i]
+                per_view.append(cot[i, :, :vc.H, :vc.W] * vc.mask)
+            k += cot.shape[0]
+        _C.backward_batch(self._gauss_args(), self._get_plan(), per_view, sinks)
+
+    def _matvec_cached(self, v):
+        self._require_linearized()
+        tens = self._image_tangents(self._gauss_args(), self._tangent_inputs(v))
+        out = []
+        for idx, ((start, end), t) in enumerate(zip(self._batches(), tens)):
+            cams = self.viewpoint_cams[start:end]
             depth_block = torch.zeros((0,), dtype=torch.float32, device=t.device)
-            t1, t2 = self._loss_batches[len(out)].jvp(t) if self.ssim else (t, t)
+            t1, t2 = self._loss_batches[idx].jvp(t) if self.ssim else (t, t)
             out.append(BatchLossImageState(t1, t2, depth_block, [(c.image_height, c.image_width) for c in cams], False))
         return MultiBatchLossImageState(out)
-
-    def _backward_view(self, vc, g, sinks):
-        a = self._act
-        bg, vm, pm, tfx, tfy, H, W, campos, aa, dbg = vc.cam_args
-        _C.rasterize_gaussians_backward(bg, a["means3D"], vc.radii, self._empty, a["opacities"], a["scales"],
-                                        a["rotations"], 1.0, self._empty, vm, pm, tfx, tfy, g, None, a["shs"],
-                                        a["sh_degree"], campos, vc.geom, vc.R, vc.binning, vc.img, aa, dbg,
-                                        accumulate_into=sinks)
 
     def _matvec_T_cached(self, vs):
         self._require_linearized()
         flat, views, sinks = self._act_accumulators()
-        a = self._act
-        k = 0
-        for idx, (start, end) in enumerate(self._batches()):
+        cots = []
+        for idx, _ in enumerate(self._batches()):
             u = vs.batch_losses[idx]
             if self.ssim:
-                cot = self._loss_batches[idx].vjp(u.Ll1_per_pixel, u.ssim_loss_per_pixel)
+                cots.append(self._loss_batches[idx].vjp(u.Ll1_per_pixel, u.ssim_loss_per_pixel))
             else:
-                cot = u.Ll1_per_pixel + u.ssim_loss_per_pixel     # J^T of the two aliased blocks
-            for i in range(end - start):
-                vc = self._views[k]
-                k += 1
-                self._backward_view(vc, cot[i, :, :vc.H, :vc.W] * vc.mask, sinks)
+                cots.append(u.Ll1_per_pixel + u.ssim_loss_per_pixel)     # J^T of the two aliased blocks
+        self._pull_back(cots, sinks)
         if self.dist:
             self.dist.all_reduce(flat)
         return self._to_state(views)
 
     def _normal_matvec_ssim(self, gargs, targs, sinks, quad):
-        """J_r^T (L^T L) J_r v per batch of views: image tangents from the tangent tile kernel, the loss-block JVP and
-        VJP kernels in image space, then the adjoint tile kernel."""
-        k = 0
-        for idx, (start, end) in enumerate(self._batches()):
-            lb = self._loss_batches[idx]
-            t = torch.zeros((lb.B, 3, lb.H, lb.W), dtype=torch.float32, device=lb.images.device)
-            for i in range(end - start):
-                vc = self._views[k + i]
-                jv, _ = _C.jvp_cached(gargs, targs, vc.cam_args, vc.radii, vc.geom, vc.R, vc.binning, vc.img)
-                t[i, :, :vc.H, :vc.W] = jv * vc.mask
+        """J_r^T (L^T L) J_r v: image tangents from the batched tangent tile kernel, the loss-block JVP and VJP
+        kernels in image space, then the batched adjoint tile kernel."""
+        cots = []
+        for lb, t in zip(self._loss_batches, self._image_tangents(gargs, targs)):
             t1, t2 = lb.jvp(t)
             if quad is not None:
                 quad += (t1 * t1).sum() + (t2 * t2).sum()
-            cot = lb.vjp(t1, t2)
-            for i in range(end - start):
-                vc = self._views[k + i]
-                self._backward_view(vc, cot[i, :, :vc.H, :vc.W] * vc.mask, sinks)
-            k += end - start
+            cots.append(lb.vjp(t1, t2))
+        self._pull_back(cots, sinks)
 
     def normal_matvec(self, v, damp=None, return_quad=False):
         """J^T J v (+ damp * v): the Gauss-Newton product CG needs, one fused tile kernel per view.
@@ -456,10 +474,7 @@ class LinearSolverFunctions:
         if self.ssim:
             self._normal_matvec_ssim(gargs, targs, sinks, quad)
         else:
-            if self._plan is None:
-                self._plan = _C.JtjvBatchPlan([(vc.cam_args, vc.radii, vc.geom, vc.R, vc.binning, vc.img, vc.weight)
-                                               for vc in self._views], flat.device)
-            _C.jtjv_batch(gargs, targs, self._plan, sinks, out_vJJv=quad)
+            _C.jtjv_batch(gargs, targs, self._get_plan(), sinks, out_vJJv=quad)
         if self.dist:
             self.dist.all_reduce(flat)
             if quad is not None:

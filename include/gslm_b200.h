@@ -186,6 +186,23 @@ int32_t gslm_jtjv_batch(const GslmGaussians* g, const GslmGaussians* gt, int32_t
                         const int32_t* num_cached, const float* const* weights, void* scratch, size_t scratch_bytes,
                         GslmGrads* grads, float* out_vJJv, void* stream);
 
+/* J v and J^T u for n_views linearised views per call (colour only), <= 16 views per kernel launch: what
+ * LinearSolverFunctions.matvec / matvec_T issue (solver/solver_functions.py:75-113; the reference's CGLS,
+ * solver/conjugate_gradient.py:51-127, calls both every iteration, and the L1 + SSIM normal product needs the
+ * image-space vector between them).  out_color_tangent[v] / dL_dcolor[v]: [3,H_v,W_v] device images.
+ * gslm_backward_batch sums the views' gradients into `grads` in view order (deterministic). */
+size_t gslm_jvp_batch_scratch_bytes(int32_t P, int32_t n_views);
+int32_t gslm_jvp_batch(const GslmGaussians* g, const GslmGaussians* gt, int32_t n_views, const GslmCamera* cams,
+                       const void* const* geom_buffers, const void* const* binning_buffers,
+                       const void* const* image_buffers, const int32_t* num_cached, void* scratch, size_t scratch_bytes,
+                       float* const* out_color_tangent, void* stream);
+size_t gslm_backward_batch_scratch_bytes(int32_t n_views, const int32_t* num_cached);
+int32_t gslm_backward_batch(const GslmGaussians* g, int32_t n_views, const GslmCamera* cams,
+                            const int32_t* const* radii, const void* const* geom_buffers,
+                            const void* const* binning_buffers, const void* const* image_buffers,
+                            const int32_t* num_cached, const float* const* dL_dcolor, void* scratch,
+                            size_t scratch_bytes, GslmGrads* grads, void* stream);
+
 /* ---- residual side: the two per-pixel loss blocks and their derivatives --------------------------------------
  * Replaces compute_batch_loss_block (solver/batch_training_loss.py:10-31) with the SSIM map of ssim_per_pixel /
  * _ssim_per_pixel (utils/loss_utils.py:91-117; 11x11 Gaussian window, sigma 1.5, zero padding, C1 = 0.01^2,

@@ -269,3 +269,51 @@ def test_render_only_loss_value_matches_linearised_loss(ssim):
     full = _C.rasterize_gaussians(*args)
     n, color, radii, invd = _C.render_only(*args)
     assert n == int(full[0]) and torch.equal(color, full[1]) and torch.equal(radii, full[2]) and torch.equal(invd, full[6])
+
+
+def test_batched_cached_maps_with_mixed_view_sizes():
+    """gslm_jvp_batch / gslm_backward_batch through LinearSolverFunctions.matvec / matvec_T on views of two different
+    sizes in one padded batch == the per-view entry points (gslm_jvp_cached, gslm_backward) view by view."""
+    from diff_gaussian_rasterization import _C
+    from scene.gaussian_model import GaussianModel
+    from solver.batch_training_loss import batch_training_loss
+    from solver.solver_functions import LinearSolverFunctions
+    model, _, loss_func, pipe, bg = _setup(P=3000, V=2)
+    gen = torch.Generator().manual_seed(5)
+    cams = []
+    for (W, H) in ((128, 96), (80, 64)):
+        for c in ss.hemisphere_rig(2, W, H):
+            cams.append(ss.torch_camera(c, "cuda", original_image=torch.rand(3, H, W, generator=gen).cuda(),
+                                        uid=len(cams)))
+    cams = [cams[0], cams[2], cams[1], cams[3]]          # sizes interleaved inside the batches
+    F = LinearSolverFunctions(loss_func, model, cams, batch_size=3)
+    F.evaluate_loss()
+    v = _rand_state(model, 9)
+    Jv = F.matvec(v)
+    gargs, targs = F._gauss_args(), F._tangent_inputs(v)
+    k = 0
+    for b in Jv.batch_losses:
+        for i in range(b.Ll1_per_pixel.shape[0]):
+            vc = F._views[k]
+            k += 1
+            ref, _ = _C.jvp_cached(gargs, targs, vc.cam_args, vc.radii, vc.geom, vc.R, vc.binning, vc.img)
+            got = b.Ll1_per_pixel[i]
+            assert torch.allclose(got[:, :vc.H, :vc.W], ref * vc.mask, rtol=1e-5, atol=1e-7)
+            assert float(got[:, vc.H:, :].abs().sum()) == 0.0 and float(got[:, :, vc.W:].abs().sum()) == 0.0
+    u = Jv * 0.5 + F.loss * 1.0
+    T = F.matvec_T(u)
+    flat, views, sinks = F._act_accumulators()
+    a, e = F._act, torch.empty(0, device="cuda")
+    k = 0
+    for b in u.batch_losses:
+        cot = b.Ll1_per_pixel + b.ssim_loss_per_pixel
+        for i in range(cot.shape[0]):
+            vc = F._views[k]
+            k += 1
+            bgc, vm, pm, tfx, tfy, H, W, campos, aa, dbg = vc.cam_args
+            _C.rasterize_gaussians_backward(bgc, a["means3D"], vc.radii, e, a["opacities"], a["scales"], a["rotations"],
+                                            1.0, e, vm, pm, tfx, tfy, (cot[i, :, :H, :W] * vc.mask).contiguous(), None,
+                                            a["shs"], a["sh_degree"], campos, vc.geom, vc.R, vc.binning, vc.img, aa, dbg,
+                                            accumulate_into=sinks)
+    ref = F._to_state(views)
+    assert h.rel_l2(T.packed().cpu().numpy(), ref.packed().cpu().numpy()) < 1e-5
