@@ -97,7 +97,7 @@ blend_jvp_body(const TileArgs& a, const float4* __restrict__ tgeom, const float*
 }
 
 template <bool WITH_D>
-__global__ void __launch_bounds__(DTHREADS)
+__global__ void __launch_bounds__(DTHREADS, WITH_D ? 16 : GSLM_DMINB)
 k_blend_jvp(TileArgs a, const float4* __restrict__ tgeom, const float* __restrict__ bg_t,
             float* __restrict__ out_color_t, float* __restrict__ out_invdepth_t) {
     blend_jvp_body<WITH_D>(a, tgeom, bg_t, out_color_t, out_invdepth_t);
@@ -114,7 +114,7 @@ struct ViewBatch {
     float4* inst_grads[MAX_BATCH_VIEWS];       // VJP: per-instance gradient records
 };
 
-__global__ void __launch_bounds__(DTHREADS) k_blend_jvp_batch(const __grid_constant__ ViewBatch vb) {
+__global__ void __launch_bounds__(DTHREADS, GSLM_DMINB) k_blend_jvp_batch(const __grid_constant__ ViewBatch vb) {
     blend_jvp_body<false>(vb.t[blockIdx.y], vb.tgeom[blockIdx.y], nullptr, vb.out_color_t[blockIdx.y], nullptr);
 }
 
@@ -151,13 +151,13 @@ blend_bwd_body(const TileArgs& a, const float* __restrict__ dL_dcolor, const flo
 }
 
 template <bool WITH_D>
-__global__ void __launch_bounds__(DTHREADS)
+__global__ void __launch_bounds__(DTHREADS, WITH_D ? 16 : GSLM_DMINB)
 k_blend_bwd(TileArgs a, const float* __restrict__ dL_dcolor, const float* __restrict__ dL_dinvdepth,
             float4* __restrict__ inst_grads) {
     blend_bwd_body<WITH_D>(a, dL_dcolor, dL_dinvdepth, inst_grads);
 }
 
-__global__ void __launch_bounds__(DTHREADS) k_blend_bwd_batch(const __grid_constant__ ViewBatch vb) {
+__global__ void __launch_bounds__(DTHREADS, GSLM_DMINB) k_blend_bwd_batch(const __grid_constant__ ViewBatch vb) {
     blend_bwd_body<false>(vb.t[blockIdx.y], vb.dL_dcolor[blockIdx.y], nullptr, vb.inst_grads[blockIdx.y]);
 }
 
