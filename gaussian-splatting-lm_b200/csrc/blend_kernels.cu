@@ -98,7 +98,7 @@ blend_jvp_body(const TileArgs& a, const float4* __restrict__ tgeom, const float*
 
 template <bool WITH_D>
 __global__ void __launch_bounds__(DTHREADS, WITH_D ? 16 : GSLM_DMINB)
-k_blend_jvp(TileArgs a, const float4* __restrict__ tgeom, const float* __restrict__ bg_t,
+k_blend_jvp(const __grid_constant__ TileArgs a, const float4* __restrict__ tgeom, const float* __restrict__ bg_t,
             float* __restrict__ out_color_t, float* __restrict__ out_invdepth_t) {
     blend_jvp_body<WITH_D>(a, tgeom, bg_t, out_color_t, out_invdepth_t);
 }
@@ -152,8 +152,8 @@ blend_bwd_body(const TileArgs& a, const float* __restrict__ dL_dcolor, const flo
 
 template <bool WITH_D>
 __global__ void __launch_bounds__(DTHREADS, WITH_D ? 16 : GSLM_DMINB)
-k_blend_bwd(TileArgs a, const float* __restrict__ dL_dcolor, const float* __restrict__ dL_dinvdepth,
-            float4* __restrict__ inst_grads) {
+k_blend_bwd(const __grid_constant__ TileArgs a, const float* __restrict__ dL_dcolor,
+            const float* __restrict__ dL_dinvdepth, float4* __restrict__ inst_grads) {
     blend_bwd_body<WITH_D>(a, dL_dcolor, dL_dinvdepth, inst_grads);
 }
 

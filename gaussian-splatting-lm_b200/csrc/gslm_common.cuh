@@ -17,7 +17,10 @@ constexpr int TILE_X = 16, TILE_Y = 16;          // DGR/cuda_rasterizer/config.h
 constexpr int TILE_PIX = TILE_X * TILE_Y;        // 256 threads per tile CTA, one pixel each
 constexpr int BATCH = 256;                       // instances staged in shared memory per round
 constexpr int MAX_BATCH_VIEWS = 16;              // linearised views per batched launch (descriptors travel as kernel parameters)
-constexpr int ACT_RANGE = 256;                   // Gaussian ids per warp in the multi-view adjoint stage
+#ifndef GSLM_ACT_RANGE
+#define GSLM_ACT_RANGE 256
+#endif
+constexpr int ACT_RANGE = GSLM_ACT_RANGE;                   // Gaussian ids per warp in the multi-view adjoint stage
 constexpr int REC_F4 = 3;                        // one instance record = 3 x float4 = 48 bytes
 
 // Instance record (one per (tile, Gaussian) pair, stored in tile|depth order so that a

@@ -327,7 +327,10 @@ struct BwdView {
 };
 struct BwdBatch { BwdView v[MAX_BATCH_VIEWS]; int n; };
 
-__global__ void __launch_bounds__(128) k_preprocess_bwd_views(BwdArgs a, const __grid_constant__ BwdBatch vb, int nranges) {
+#ifndef GSLM_BWDV_MINB
+#define GSLM_BWDV_MINB 4   // 128 registers: the per-Gaussian chain needs the ILP (96 registers: 1.52 ms per 16-view launch, 128: 0.95; profiles/r1i_adjoint_variants.txt)
+#endif
+__global__ void __launch_bounds__(128, GSLM_BWDV_MINB) k_preprocess_bwd_views(BwdArgs a, const __grid_constant__ BwdBatch vb, int nranges) {
     __shared__ float sCamAll[MAX_BATCH_VIEWS][36];   // V[16] | PV[16] | campos[3]
     for (int t = threadIdx.x; t < vb.n * 36; t += blockDim.x) {
         const int v = t / 36, k = t % 36;
