@@ -205,6 +205,18 @@ def main():
     R_total = sum(int(vc.R) for vc in F._views)
     R_cached = sum(vc.R.cached for vc in F._views)     # instances some pixel blended: what every CG iteration sweeps
     pix = sum(vc.W * vc.H for vc in F._views)
+    # workload statistics: visible Gaussians per view and the distribution of per-tile list lengths
+    p_vis = [int((vc.radii > 0).sum()) for vc in F._views]
+    tile_q = None
+    if F._views:
+        lens = []
+        for vc in F._views[:8]:
+            rg = _C.buffer_view(P, vc.W, vc.H, vc.R, None, None, vc.img).get("ranges")
+            if rg is not None:
+                lens.append((rg[:, 1] - rg[:, 0]).float())
+        if lens:
+            q = torch.quantile(torch.cat(lens), torch.tensor([0.5, 0.9, 0.99, 1.0], device=dev))
+            tile_q = {"p50": int(q[0]), "p90": int(q[1]), "p99": int(q[2]), "max": int(q[3]), "views_sampled": len(lens)}
 
     tan = ss.random_tangent(g, seed=2001, mask_xyz=a.mask_xyz)
     v = GaussianModelState.from_gaussians(model)
@@ -313,6 +325,8 @@ def main():
         "data": "synthetic",
         "config": {"workload": workload_name(a, P, V, W, H), "views_per_rank": len(F._views),
                    "instances_total_rank0": R_total, "instances_cached_rank0": R_cached,
+                   "visible_gaussians_per_view_mean_rank0": (sum(p_vis) / len(p_vis)) if p_vis else 0,
+                   "tile_list_length_rank0": tile_q,
                    "l2_policy": "inputs larger than L2 (per-view records + gradients >> 126 MB)",
                    "linearize_ms": round(linearize_ms, 2), "mask_xyz": bool(a.mask_xyz)},
         "e2e": {"value": 1e3 / ms_e2e, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": 4 * n_flat,

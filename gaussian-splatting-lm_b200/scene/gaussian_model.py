@@ -1,6 +1,10 @@
 """GaussianModel: raw parameters + activations + make_dual / zero_grad / update_step
 (scene/gaussian_model.py:42-50,71-139,192-224 of the reference).  Everything else the reference class does
-(point-cloud init, densify/prune, PLY IO, Adam) is out of scope of the LM hot path."""
+(point-cloud init, densify/prune, Adam) is out of scope of the LM hot path.  save_ply / load_ply read and write the
+reference's checkpoint format (scene/gaussian_model.py:315-404: one binary little-endian PLY `vertex` element with
+float properties x y z nx ny nz f_dc_* f_rest_* opacity scale_* rot_*, SH stored channel-major) with numpy only --
+the reference goes through the `plyfile` package -- so scenes trained by the reference load here and vice versa."""
+import os
 from contextlib import contextmanager
 
 import numpy as np
@@ -51,6 +55,94 @@ class GaussianModel:
         for n, v in raw.items():
             setattr(m, n, nn.Parameter(v.requires_grad_(requires_grad)) if requires_grad else v)
         return m
+
+    # ---- checkpoint format (reference :315-404) ----
+    def construct_list_of_attributes(self):
+        names = ["x", "y", "z", "nx", "ny", "nz"]
+        names += [f"f_dc_{i}" for i in range(self._features_dc.shape[1] * self._features_dc.shape[2])]
+        names += [f"f_rest_{i}" for i in range(self._features_rest.shape[1] * self._features_rest.shape[2])]
+        names.append("opacity")
+        names += [f"scale_{i}" for i in range(self._scaling.shape[1])]
+        names += [f"rot_{i}" for i in range(self._rotation.shape[1])]
+        return names
+
+    def save_ply(self, path):
+        d = os.path.dirname(path)
+        if d:
+            os.makedirs(d, exist_ok=True)
+        cpu = lambda t: t.detach().cpu().numpy().astype(np.float32)
+        xyz = cpu(self._xyz)
+        cols = np.concatenate((xyz, np.zeros_like(xyz),
+                               cpu(self._features_dc.detach().transpose(1, 2).flatten(start_dim=1)),
+                               cpu(self._features_rest.detach().transpose(1, 2).flatten(start_dim=1)),
+                               cpu(self._opacity), cpu(self._scaling), cpu(self._rotation)), axis=1)
+        names = self.construct_list_of_attributes()
+        assert cols.shape[1] == len(names)
+        header = "ply\nformat binary_little_endian 1.0\nelement vertex %d\n" % cols.shape[0]
+        header += "".join(f"property float {n}\n" for n in names) + "end_header\n"
+        with open(path, "wb") as f:
+            f.write(header.encode("ascii"))
+            f.write(np.ascontiguousarray(cols, dtype="<f4").tobytes())
+
+    @staticmethod
+    def _read_ply_vertices(path):
+        """{property name: float64 column} of the first element of a PLY file (binary little/big endian or ascii)."""
+        types = {"char": "i1", "int8": "i1", "uchar": "u1", "uint8": "u1", "short": "i2", "int16": "i2",
+                 "ushort": "u2", "uint16": "u2", "int": "i4", "int32": "i4", "uint": "u4", "uint32": "u4",
+                 "float": "f4", "float32": "f4", "double": "f8", "float64": "f8"}
+        with open(path, "rb") as f:
+            if f.readline().strip() != b"ply":
+                raise ValueError(f"{path}: not a PLY file")
+            fmt, count, props, in_first, seen = None, 0, [], False, 0
+            while True:
+                line = f.readline()
+                if not line:
+                    raise ValueError(f"{path}: truncated PLY header")
+                tok = line.decode("ascii").split()
+                if not tok or tok[0] == "comment":
+                    continue
+                if tok[0] == "format":
+                    fmt = tok[1]
+                elif tok[0] == "element":
+                    seen += 1
+                    in_first = seen == 1
+                    if in_first:
+                        count = int(tok[2])
+                elif tok[0] == "property" and in_first:
+                    if tok[1] == "list":
+                        raise ValueError(f"{path}: list properties are not supported in the vertex element")
+                    props.append((tok[2], types[tok[1]]))
+                elif tok[0] == "end_header":
+                    break
+            if fmt == "ascii":
+                data = np.loadtxt(f, max_rows=count, ndmin=2)
+                return {n: data[:, i].astype(np.float64) for i, (n, _) in enumerate(props)}
+            order = "<" if fmt == "binary_little_endian" else ">"
+            rec = np.dtype([(n, order + t) for n, t in props])
+            data = np.frombuffer(f.read(rec.itemsize * count), dtype=rec, count=count)
+            return {n: data[n].astype(np.float64) for n, _ in props}
+
+    def load_ply(self, path, use_train_test_exp=False, device="cuda", requires_grad=True):
+        v = self._read_ply_vertices(path)
+        by_index = lambda prefix: sorted((k for k in v if k.startswith(prefix)), key=lambda k: int(k.split("_")[-1]))
+        xyz = np.stack((v["x"], v["y"], v["z"]), axis=1)
+        P = xyz.shape[0]
+        f_dc = np.stack((v["f_dc_0"], v["f_dc_1"], v["f_dc_2"]), axis=1).reshape(P, 3, 1)
+        rest_names = by_index("f_rest_")
+        assert len(rest_names) == 3 * (self.max_sh_degree + 1) ** 2 - 3
+        f_rest = np.stack([v[k] for k in rest_names], axis=1).reshape(P, 3, (self.max_sh_degree + 1) ** 2 - 1) \
+            if rest_names else np.zeros((P, 3, 0))
+        scales = np.stack([v[k] for k in by_index("scale_")], axis=1)
+        rots = np.stack([v[k] for k in by_index("rot")], axis=1)
+        T = lambda a: torch.tensor(a, dtype=torch.float, device=device)
+        raw = {"_xyz": T(xyz), "_features_dc": T(f_dc).transpose(1, 2).contiguous(),
+               "_features_rest": T(f_rest).transpose(1, 2).contiguous(), "_opacity": T(v["opacity"][:, None]),
+               "_scaling": T(scales), "_rotation": T(rots)}
+        for n, t in raw.items():
+            setattr(self, n, nn.Parameter(t.requires_grad_(True)) if requires_grad else t)
+        if self._exposure.numel() == 0:
+            self._exposure = torch.eye(3, 4, device=device)[None].clone()
+        self.active_sh_degree = self.max_sh_degree
 
     # ---- forward-AD plumbing (reference :71-139) ----
     @contextmanager

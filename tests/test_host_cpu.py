@@ -181,3 +181,42 @@ def test_view_sharding_over_gloo_world2():
                          capture_output=True, text=True, env=env, timeout=280)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert "DIST_OK" in out.stdout
+
+
+def test_ply_checkpoint_roundtrip_and_reference_layout(tmp_path):
+    """save_ply / load_ply (reference scene/gaussian_model.py:315-404): header and column order as plyfile writes them
+    for the reference (binary little endian, float properties x y z nx ny nz f_dc_* f_rest_* opacity scale_* rot_*,
+    SH channel-major), exact round trip, and a big-endian / double file of the same content loads identically."""
+    import scene_synth as ss
+    from scene.gaussian_model import GaussianModel
+    g = ss.make_gaussians(257, sh_degree=2, seed=21)
+    m = GaussianModel.from_activated(g, device="cpu")
+    path = str(tmp_path / "point_cloud" / "iteration_7" / "point_cloud.ply")
+    m.save_ply(path)
+    raw = open(path, "rb").read()
+    head, body = raw.split(b"end_header\n", 1)
+    lines = head.decode().splitlines()
+    assert lines[:3] == ["ply", "format binary_little_endian 1.0", "element vertex 257"]
+    names = [ln.split()[2] for ln in lines[3:]]
+    assert all(ln.startswith("property float ") for ln in lines[3:])
+    assert names == (["x", "y", "z", "nx", "ny", "nz", "f_dc_0", "f_dc_1", "f_dc_2"] + [f"f_rest_{i}" for i in range(24)]
+                     + ["opacity", "scale_0", "scale_1", "scale_2", "rot_0", "rot_1", "rot_2", "rot_3"])
+    cols = np.frombuffer(body, dtype="<f4").reshape(257, len(names))
+    # channel-major SH: f_rest_0..7 are the 8 red coefficients (features_rest[:, :, 0])
+    assert np.array_equal(cols[:, 9:17], m._features_rest.detach().numpy()[:, :, 0])
+    assert np.array_equal(cols[:, 3:6], np.zeros((257, 3), np.float32))
+    m2 = GaussianModel(2)
+    m2.load_ply(path, device="cpu")
+    for n in ("_xyz", "_features_dc", "_features_rest", "_scaling", "_rotation", "_opacity"):
+        assert torch.equal(getattr(m2, n).detach(), getattr(m, n).detach()), n
+    assert m2.active_sh_degree == 2
+    # the same content as big-endian doubles with a comment line and a second element after the vertices
+    be = str(tmp_path / "be.ply")
+    with open(be, "wb") as f:
+        f.write(("ply\nformat binary_big_endian 1.0\ncomment made by a test\nelement vertex 257\n"
+                 + "".join(f"property double {n}\n" for n in names)
+                 + "element face 0\nproperty list uchar int vertex_indices\nend_header\n").encode())
+        f.write(cols.astype(">f8").tobytes())
+    m3 = GaussianModel(2)
+    m3.load_ply(be, device="cpu", requires_grad=False)
+    assert torch.equal(m3._features_rest, m._features_rest.detach()) and torch.equal(m3._rotation, m._rotation.detach())
