@@ -55,6 +55,7 @@ struct Planes {          // one batch of image planes [B,3,H,W]; alpha_masks [B,
     const float* gt;
     const float* alphas;   // [B]
     const float* betas;    // [B]
+    const float* tmask;    // [B,3,H,W] or null: d images / d (upstream image), applied to tangents in and gradients out
 };
 
 __device__ __forceinline__ float sgn(float v) { return (v > 0.f) - (v < 0.f); }
@@ -201,7 +202,7 @@ struct OpJvp {
     {
         const size_t i = pix(p, plane, y, x);
         const float mk = mask_at(p, plane, y, x);
-        const float dx = __ldg(t_images + i) * mk;
+        const float dx = __ldg(t_images + i) * (p.tmask ? mk * __ldg(p.tmask + i) : mk);
         v[0] = dx; v[1] = __ldg(p.images + i) * mk * dx; v[2] = __ldg(p.gt + i) * dx;
     }
     static constexpr bool kCenter = true, kPrefetch = true;
@@ -231,13 +232,13 @@ struct OpVjp {
         v[0] = q.y * u; v[1] = q.z * u; v[2] = q.w * u;
     }
     static constexpr bool kCenter = false, kPrefetch = GSLM_VJP_PRE;
-    struct Pre { float d1u1, xv, yv, mk, g0; };
+    struct Pre { float d1u1, xv, yv, mk, g0; };     // mk: the full output factor alpha_mask * tangent_mask
     __device__ Pre pre(int plane, int y, int x) const
     {
         const size_t i = pix(p, plane, y, x);
         const float mk = mask_at(p, plane, y, x);
-        return Pre{__ldg(&lin[i].x) * __ldg(u1 + i), __ldg(p.images + i) * mk, __ldg(p.gt + i), mk,
-                   accumulate ? g[i] : 0.f};
+        return Pre{__ldg(&lin[i].x) * __ldg(u1 + i), __ldg(p.images + i) * mk, __ldg(p.gt + i),
+                   p.tmask ? mk * __ldg(p.tmask + i) : mk, accumulate ? g[i] : 0.f};
     }
     __device__ void store(int plane, int y, int x, const float (&c)[3], const float (&)[3], const Pre& pr) const
     {
@@ -257,7 +258,7 @@ int check(const GslmLossBatch* b, const char* who)
 }
 Planes planes(const GslmLossBatch* b)
 {
-    return Planes{b->B, b->H, b->W, b->images, b->alpha_masks, b->gt, b->alphas, b->betas};
+    return Planes{b->B, b->H, b->W, b->images, b->alpha_masks, b->gt, b->alphas, b->betas, b->tangent_masks};
 }
 dim3 grid_of(const GslmLossBatch* b)
 {

@@ -41,7 +41,8 @@ class GslmGrads(C.Structure):
 
 class GslmLossBatch(C.Structure):
     _fields_ = [("B", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("images", C.c_void_p),
-                ("alpha_masks", C.c_void_p), ("gt", C.c_void_p), ("alphas", C.c_void_p), ("betas", C.c_void_p)]
+                ("alpha_masks", C.c_void_p), ("gt", C.c_void_p), ("alphas", C.c_void_p), ("betas", C.c_void_p),
+                ("tangent_masks", C.c_void_p)]
 
 
 class GslmActivations(C.Structure):
@@ -600,7 +601,7 @@ class LossBatch:
     """One batch of image planes [B,3,H,W] at a fixed linearisation point: holds the contiguous fp32 tensors the
     three loss-block calls share (images, alpha masks [B,1,H,W] or None, targets, per-image alphas / betas [B])."""
 
-    def __init__(self, images, alpha_masks, gt_images, per_image_alphas, per_image_betas):
+    def __init__(self, images, alpha_masks, gt_images, per_image_alphas, per_image_betas, tangent_masks=None):
         if images.dim() != 4 or images.shape[1] != 3:
             raise ValueError("images must be [B,3,H,W]")
         if not images.is_cuda:
@@ -615,8 +616,10 @@ class LossBatch:
         self.alphas = _f32(torch.as_tensor(per_image_alphas, device=dev).detach().reshape(-1).expand(self.B))
         self.betas = _f32(torch.as_tensor(per_image_betas, device=dev).detach().reshape(-1).expand(self.B))
         self.lin = None
+        # [B,3,H,W] factor between the caller's tangent / gradient and the images (clamp mask), fused into jvp / vjp
+        self.tmask = None if tangent_masks is None else _f32(tangent_masks.detach().expand_as(self.images))
         self.c = GslmLossBatch(self.B, self.H, self.W, _ptr(self.images), _ptr(self.masks), _ptr(self.gt),
-                               _ptr(self.alphas), _ptr(self.betas))
+                               _ptr(self.alphas), _ptr(self.betas), _ptr(self.tmask))
 
     def blocks(self, want_lin=True):
         """(Ll1_per_pixel, ssim_loss_per_pixel) of compute_batch_loss_block (disable_ssim=False); keeps the

@@ -250,6 +250,7 @@ class LinearSolverFunctions:
             resid = torch.zeros((len(cams), 3, Hm, Wm), dtype=torch.float32, device=dev)
             gt, masks = gather_targets(cams, resid)
             images = resid if self.ssim else None      # ssim mode: `resid` first collects the clamped renders
+            cmask = torch.zeros_like(resid) if self.ssim else None   # d clamp / d colour, fused into the loss kernels
             for i, cam in enumerate(cams):
                 H, W = int(cam.image_height), int(cam.image_width)
                 vc = _ViewCache()
@@ -265,6 +266,7 @@ class LinearSolverFunctions:
                 m = ((color >= 0) & (color <= 1)).to(torch.float32)
                 if self.ssim:
                     images[i, :, :H, :W] = color.clamp(0, 1)     # the alpha mask is applied inside the loss kernels
+                    cmask[i, :, :H, :W] = m
                 elif masks is not None:
                     m = m * masks[i, :, :H, :W]
                     resid[i, :, :H, :W] = color.clamp(0, 1) * masks[i, :, :H, :W] - gt[i, :, :H, :W]
@@ -279,7 +281,7 @@ class LinearSolverFunctions:
                 lam = self._kw("opt").lambda_dssim
                 al = torch.tensor([math.sqrt((1.0 - lam) / (3 * h * w)) for h, w in sizes], device=dev)
                 be = torch.tensor([math.sqrt(lam / (3 * h * w)) for h, w in sizes], device=dev)
-                lb = _C.LossBatch(images, masks, gt, al, be)
+                lb = _C.LossBatch(images, masks, gt, al, be, tangent_masks=cmask)
                 r1, r2 = lb.blocks(want_lin=True)
                 self._loss_batches.append(lb)
                 losses.append(BatchLossImageState(r1, r2, depth_block, sizes, False))
@@ -401,6 +403,8 @@ class LinearSolverFunctions:
         _C.jvp_batch(gargs, targs, self._get_plan(), dests)
         for t, i, buf, vc in staged:
             t[i, :, :vc.H, :vc.W] = buf
+        if self.ssim:                     # the clamp mask is applied inside the loss-block kernels (tangent_masks)
+            return tens
         k = 0
         for t in tens:
             for i in range(t.shape[0]):
@@ -415,7 +419,8 @@ class LinearSolverFunctions:
         for cot in cots:
             for i in range(cot.shape[0]):
                 vc = self._views[k + i]
-                per_view.append(cot[i, :, :vc.H, :vc.W] * vc.mask)
+                c = cot[i, :, :vc.H, :vc.W]
+                per_view.append(c.contiguous() if self.ssim else c * vc.mask)     # ssim: already masked by the VJP kernel
             k += cot.shape[0]
         _C.backward_batch(self._gauss_args(), self._get_plan(), per_view, sinks)
 

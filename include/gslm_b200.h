@@ -223,6 +223,10 @@ typedef struct GslmLossBatch {
     const float* gt;           /* [B,3,H,W]                                                          */
     const float* alphas;       /* [B] device                                                         */
     const float* betas;        /* [B] device                                                         */
+    const float* tangent_masks;/* [B,3,H,W] or NULL: d images / d (what the caller differentiates), e.g. the 0/1 mask of
+                                * the renderer's clamp(0,1) (gaussian_renderer/batch_render.py:118): multiplies
+                                * t_images on the way into gslm_loss_blocks_jvp and g_images on the way out of
+                                * gslm_loss_blocks_vjp; ignored by gslm_loss_blocks                       */
 } GslmLossBatch;
 size_t gslm_loss_lin_bytes(int32_t B, int32_t H, int32_t W);       /* 16 B per pixel and channel */
 int32_t gslm_loss_blocks(const GslmLossBatch* batch, float* r1, float* r2, void* lin, void* stream);
