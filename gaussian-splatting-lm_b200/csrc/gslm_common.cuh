@@ -123,6 +123,20 @@ struct StageScope {
     ~StageScope() { stage_end(st, s); }
 };
 
+// SH rows [M,3] of 12 M bytes are 16-byte aligned when M % 4 == 0 (M = 4, 16): element f of a row through a float4
+// load.  With a compile-time f the compiler keeps one LDG.128 per four coefficients floats (identical read-only loads
+// are merged) instead of four LDG.32 -- the per-Gaussian kernels are latency-bound gathers, bytes per instruction count.
+#ifdef __CUDACC__
+__device__ __forceinline__ float sh_elem4(const float* row, int f) {
+    const float4 q = __ldg(reinterpret_cast<const float4*>(row) + (f >> 2));
+    const int c = f & 3;
+    return c == 0 ? q.x : (c == 1 ? q.y : (c == 2 ? q.z : q.w));
+}
+__host__ __device__ inline bool sh_rows_aligned(const float* shs, int M) {
+    return shs != nullptr && (M & 3) == 0 && (reinterpret_cast<size_t>(shs) & 15u) == 0;
+}
+#endif
+
 // ---- stage launchers (each one = one reference stage; see the .cu that defines it) ----
 struct TangentPtrs {   // tangent inputs of the forward-mode preprocess; any pointer may be null
     const float *means3D, *opacities, *scales, *rotations, *cov3D_precomp, *shs, *colors_precomp;

@@ -99,6 +99,8 @@ __global__ void __launch_bounds__(256) k_preprocess(PreArgs a, GeomView gv, int3
         const float* sh = a.shs + (size_t)idx * a.M * 3;
         uint8_t cl;
         v3<float> campos = {sc.campos[0], sc.campos[1], sc.campos[2]};
+        // scalar fetches on purpose: the image is compared bit for bit with the reference's kernels, and the float4
+        // fetch used by the tangent / adjoint kernels (sh_elem4) changes how nvcc contracts this expression
         v3<float> col = color_from_sh<float>(
             a.D, mean, campos, [&](int k) { return v3<float>{__ldg(sh + 3 * k), __ldg(sh + 3 * k + 1), __ldg(sh + 3 * k + 2)}; },
             cl);
@@ -206,9 +208,12 @@ k_preprocess_tangent(PreTanArgs a, const __grid_constant__ PreTanBatch vb) {
         uint8_t cl;
         v3<dualf> campos = {dualf(sc.campos[0], CAMT ? sc.campos_t[0] : 0.f), dualf(sc.campos[1], CAMT ? sc.campos_t[1] : 0.f),
                             dualf(sc.campos[2], CAMT ? sc.campos_t[2] : 0.f)};
-        v3<dualf> col = color_from_sh<dualf>(
-            a.p.D, mean, campos,
-            [&](int k) { return v3<dualf>{ldd(sh, sht, 3 * k), ldd(sh, sht, 3 * k + 1), ldd(sh, sht, 3 * k + 2)}; }, cl);
+        auto dd4 = [&](int f) { return dualf(sh_elem4(sh, f), sht ? sh_elem4(sht, f) : 0.f); };
+        v3<dualf> col = (sh_rows_aligned(a.p.shs, a.p.M) && (!sht || sh_rows_aligned(a.t.shs, a.p.M)))
+            ? color_from_sh<dualf>(a.p.D, mean, campos,
+                  [&](int k) { return v3<dualf>{dd4(3 * k), dd4(3 * k + 1), dd4(3 * k + 2)}; }, cl)
+            : color_from_sh<dualf>(a.p.D, mean, campos,
+                  [&](int k) { return v3<dualf>{ldd(sh, sht, 3 * k), ldd(sh, sht, 3 * k + 1), ldd(sh, sht, 3 * k + 2)}; }, cl);
         cr_t = col.x.d; cg_t = col.y.d; cb_t = col.z.d;
     } else {
         const float* ct = a.t.colors_precomp;

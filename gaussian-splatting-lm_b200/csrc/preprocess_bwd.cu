@@ -180,14 +180,15 @@ __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __re
         const float* sh = a.shs + (size_t)3 * a.M * i;
         float* dsh = a.g.dL_dsh ? a.g.dL_dsh + (size_t)3 * a.M * i : nullptr;
         float ddx = 0.f, ddy = 0.f, ddz = 0.f;   // dL/d(dir)
+        int used = 1;
+        auto sh_section = [&](auto fetch) {
         // basis value b and its partials (bx,by,bz) per coefficient; dsh_k = b * g, ddir += partial * <sh_k, g>
         auto coef = [&](int k, float b, float bx, float by, float bz) {
             if (dsh) { put<ACC>(dsh, 3 * k, b * gr); put<ACC>(dsh, 3 * k + 1, b * gg); put<ACC>(dsh, 3 * k + 2, b * gb); }
-            const float sg = __ldg(sh + 3 * k) * gr + __ldg(sh + 3 * k + 1) * gg + __ldg(sh + 3 * k + 2) * gb;
+            const float sg = fetch(3 * k) * gr + fetch(3 * k + 1) * gg + fetch(3 * k + 2) * gb;
             ddx += bx * sg; ddy += by * sg; ddz += bz * sg;
         };
         coef(0, GS_SH_C0, 0.f, 0.f, 0.f);
-        int used = 1;
         if (a.D > 0) {
             coef(1, -GS_SH_C1 * y, 0.f, -GS_SH_C1, 0.f);
             coef(2, GS_SH_C1 * z, 0.f, 0.f, GS_SH_C1);
@@ -216,6 +217,9 @@ __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __re
                 }
             }
         }
+        };
+        if (sh_rows_aligned(a.shs, a.M)) sh_section([&](int f) { return sh_elem4(sh, f); });   // one LDG.128 per 4 floats
+        else sh_section([&](int f) { return __ldg(sh + f); });
         if (!ACC && dsh)
             for (int k = 3 * used; k < 3 * a.M; k++) dsh[k] = 0.f;
         // dnormvdv, auxiliary.h:153-164
