@@ -181,10 +181,17 @@ __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __re
         float* dsh = a.g.dL_dsh ? a.g.dL_dsh + (size_t)3 * a.M * i : nullptr;
         float ddx = 0.f, ddy = 0.f, ddz = 0.f;   // dL/d(dir)
         int used = 1;
+        // accumulate mode with 16-byte aligned gradient rows (M = 4, 16): the basis values are kept and the row is
+        // updated by float4 read-modify-writes after the sweep (12 instead of 48 load + store pairs at degree 3)
+        const bool vecd = ACC && dsh != nullptr && (a.M & 3) == 0 && (reinterpret_cast<size_t>(a.g.dL_dsh) & 15u) == 0;
+        float bv[16];
+#pragma unroll
+        for (int k = 0; k < 16; k++) bv[k] = 0.f;
         auto sh_section = [&](auto fetch) {
         // basis value b and its partials (bx,by,bz) per coefficient; dsh_k = b * g, ddir += partial * <sh_k, g>
         auto coef = [&](int k, float b, float bx, float by, float bz) {
-            if (dsh) { put<ACC>(dsh, 3 * k, b * gr); put<ACC>(dsh, 3 * k + 1, b * gg); put<ACC>(dsh, 3 * k + 2, b * gb); }
+            bv[k] = b;
+            if (dsh && !vecd) { put<ACC>(dsh, 3 * k, b * gr); put<ACC>(dsh, 3 * k + 1, b * gg); put<ACC>(dsh, 3 * k + 2, b * gb); }
             const float sg = fetch(3 * k) * gr + fetch(3 * k + 1) * gg + fetch(3 * k + 2) * gb;
             ddx += bx * sg; ddy += by * sg; ddz += bz * sg;
         };
@@ -220,6 +227,21 @@ __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __re
         };
         if (sh_rows_aligned(a.shs, a.M)) sh_section([&](int f) { return sh_elem4(sh, f); });   // one LDG.128 per 4 floats
         else sh_section([&](int f) { return __ldg(sh + f); });
+        if (vecd) {
+            float4* d4 = reinterpret_cast<float4*>(dsh);
+            const float g3[3] = {gr, gg, gb};
+#pragma unroll
+            for (int c = 0; c < 12; c++) {
+                if (4 * c < 3 * used && 4 * c < 3 * a.M) {     // coefficients >= used have bv = 0: adds exact zeros
+                    float4 q = d4[c];
+                    q.x += bv[(4 * c) / 3] * g3[(4 * c) % 3];
+                    q.y += bv[(4 * c + 1) / 3] * g3[(4 * c + 1) % 3];
+                    q.z += bv[(4 * c + 2) / 3] * g3[(4 * c + 2) % 3];
+                    q.w += bv[(4 * c + 3) / 3] * g3[(4 * c + 3) % 3];
+                    d4[c] = q;
+                }
+            }
+        }
         if (!ACC && dsh)
             for (int k = 3 * used; k < 3 * a.M; k++) dsh[k] = 0.f;
         // dnormvdv, auxiliary.h:153-164
