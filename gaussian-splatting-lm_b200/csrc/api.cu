@@ -5,6 +5,7 @@
 // =============================================================================
 #include "gslm_common.cuh"
 #include <cstring>
+#include <vector>
 
 using namespace gslm;
 
@@ -48,6 +49,13 @@ static int debug_sync(const GslmCamera* cam, cudaStream_t s, const char* what) {
         if (e != cudaSuccess) { set_error("%s: %s", what, cudaGetErrorString(e)); return 1; }
     }
     return 0;
+}
+
+// point_offsets[P-1] (the instance count) of each view of a render batch, gathered for one read-back
+static __global__ void k_gather_totals(const char* geom_base, size_t view_stride, size_t offset_of_last, int n_views,
+                                       uint32_t* totals) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < n_views) totals[v] = *reinterpret_cast<const uint32_t*>(geom_base + v * view_stride + offset_of_last);
 }
 
 extern "C" {
@@ -130,6 +138,69 @@ int32_t gslm_render(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn a
                     float* out_color, float* out_invdepth, int32_t* radii, int32_t* num_rendered, void* stream) {
     return forward_impl(g, cam, alloc, alloc_ctx, out_color, out_invdepth, radii, num_rendered, nullptr, false,
                         stream);
+}
+
+int32_t gslm_render_batch(const GslmGaussians* g, int32_t n_views, const GslmCamera* cams, GslmAllocFn alloc,
+                          void* alloc_ctx, float* const* out_color, float* const* out_invdepth, int32_t* const* radii,
+                          int32_t* num_rendered, void* stream) {
+    if (n_views < 0 || (n_views > 0 && (!cams || !out_color || !num_rendered)) || !alloc) {
+        set_error("null argument");
+        return 1;
+    }
+    if (n_views == 0) return 0;
+    for (int v = 0; v < n_views; v++) {
+        if (check_inputs(g, &cams[v])) return 1;
+        if (!out_color[v]) { set_error("null argument"); return 1; }
+        num_rendered[v] = 0;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    const int P = g->P;
+    // one geometry allocation: n_views per-view states, the radii of views the caller does not want back, the totals
+    const size_t gstride = align_up(gslm_geom_bytes(P)), rstride = align_up((size_t)P * sizeof(int32_t));
+    size_t ibytes = 0;
+    for (int v = 0; v < n_views; v++) {
+        const size_t b = gslm_image_bytes(cams[v].width, cams[v].height);
+        ibytes = b > ibytes ? b : ibytes;
+    }
+    char* gbase = (char*)alloc(alloc_ctx, GSLM_BUF_GEOM,
+                               128 + (size_t)n_views * (gstride + rstride) + align_up(n_views * sizeof(uint32_t)));
+    void* ibuf = alloc(alloc_ctx, GSLM_BUF_IMAGE, ibytes);      // reused view after view (stream order)
+    if (!gbase || !ibuf) { set_error("allocator returned null"); return 1; }
+    gbase = (char*)align_up((size_t)gbase);
+    char* rbase = gbase + (size_t)n_views * gstride;
+    uint32_t* totals = reinterpret_cast<uint32_t*>(rbase + (size_t)n_views * rstride);
+    auto radii_of = [&](int v) { return (radii && radii[v]) ? radii[v] : reinterpret_cast<int32_t*>(rbase + v * rstride); };
+    std::vector<uint32_t> R(n_views, 0u);
+    if (P > 0) {
+        for (int v = 0; v < n_views; v++) {
+            GeomView gv = carve_geom(gbase + v * gstride, P);
+            if (launch_preprocess(*g, cams[v], gv, radii_of(v), s)) return 1;
+            if (run_scan(gv, P, s)) return 1;
+        }
+        GeomView g0 = carve_geom(gbase, P);
+        const size_t off = (size_t)((const char*)(g0.point_offsets + (P - 1)) - gbase);
+        k_gather_totals<<<(n_views + 127) / 128, 128, 0, s>>>(gbase, gstride, off, n_views, totals);
+        GSLM_CUDA_OK(cudaGetLastError());
+        // the ONE host synchronisation of the batch (rasterizer_impl.cu:325 has one per view)
+        GSLM_CUDA_OK(cudaMemcpyAsync(R.data(), totals, n_views * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        GSLM_CUDA_OK(cudaStreamSynchronize(s));
+    }
+    uint32_t Rmax = 0;
+    for (int v = 0; v < n_views; v++) { num_rendered[v] = (int32_t)R[v]; Rmax = R[v] > Rmax ? R[v] : Rmax; }
+    void* tbuf = alloc(alloc_ctx, GSLM_BUF_BINNING_TEMP, gslm_binning_temp_bytes(P, Rmax));
+    if (!tbuf) { set_error("allocator returned null"); return 1; }
+    for (int v = 0; v < n_views; v++) {
+        const GslmCamera& cam = cams[v];
+        GeomView gv = carve_geom(gbase + v * gstride, P);
+        ImageView iv = carve_image(ibuf, cam.width, cam.height);
+        BinningTemp bt = carve_binning_temp(tbuf, R[v], P);
+        if (run_binning(gv, radii_of(v), bt, iv, P, cam.width, cam.height, R[v], s)) return 1;
+        const float* features = g->colors_precomp ? g->colors_precomp : gv.rgb;
+        if (launch_blend_fwd(gv, bt, iv, cam.width, cam.height, features, cam.bg, out_color[v],
+                             out_invdepth ? out_invdepth[v] : nullptr, false, s)) return 1;
+        if (debug_sync(&cam, s, "render_batch")) return 1;
+    }
+    return 0;
 }
 
 int32_t gslm_jvp_cached(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam, const int32_t* radii,

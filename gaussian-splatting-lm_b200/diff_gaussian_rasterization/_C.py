@@ -93,7 +93,7 @@ def _cached(R, imageBuffer=None, W=None, H=None):
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_int32, C.c_size_t)
 
 EXPORTS = ("gslm_last_error", "gslm_abi_version", "gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_binning_temp_bytes",
-           "gslm_mark_visible", "gslm_forward", "gslm_render", "gslm_forward_jvp", "gslm_backward_scratch_bytes", "gslm_backward",
+           "gslm_mark_visible", "gslm_forward", "gslm_render", "gslm_render_batch", "gslm_forward_jvp", "gslm_backward_scratch_bytes", "gslm_backward",
            "gslm_jvp_scratch_bytes", "gslm_jvp_cached", "gslm_jtjv_scratch_bytes", "gslm_jtjv",
            "gslm_jtjv_batch_scratch_bytes", "gslm_jtjv_batch", "gslm_jvp_batch_scratch_bytes", "gslm_jvp_batch",
            "gslm_backward_batch_scratch_bytes", "gslm_backward_batch", "gslm_loss_lin_bytes", "gslm_loss_blocks",
@@ -126,6 +126,7 @@ def lib():
         L.gslm_mark_visible.argtypes = [C.c_int32, vp, vp, vp, vp, vp]
         L.gslm_forward.argtypes = [vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp, vp]
         L.gslm_render.argtypes = [vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp]
+        L.gslm_render_batch.argtypes = [vp, C.c_int32, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp]
         L.gslm_forward_jvp.argtypes = [vp, vp, vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         L.gslm_backward.argtypes = [vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
         L.gslm_jvp_cached.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp]
@@ -324,6 +325,42 @@ def render_only(background, means3D, colors, opacity, scales, rotations, scale_m
                          out_invdepth.data_ptr(), radii.data_ptr(), C.addressof(n), _stream()))
     _after_forward(al)
     return n.value, out_color, radii, out_invdepth
+
+
+def render_batch(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, views, sh,
+                 degree, antialiasing, debug, out=None):
+    """gslm_render_batch: render-only passes of one set of Gaussians from several cameras with one host
+    synchronisation for the whole batch.  views: sequence of (viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W,
+    campos).  out: optional list of [3,H,W] float32 CUDA tensors to render into (e.g. slices of a stacked batch).
+    Returns (num_rendered list, list of colour images)."""
+    L = lib()
+    dev = means3D.device
+    g, k1 = _gaussians(means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, sh, degree)
+    n = len(views)
+    cams = (GslmCamera * max(n, 1))()
+    keep = []
+    for i, (vm, pm, tfx, tfy, H, W, campos) in enumerate(views):
+        c, k = _camera(background, vm, pm, tfx, tfy, H, W, campos, False, antialiasing, debug)
+        C.memmove(C.addressof(cams[i]), C.addressof(c), C.sizeof(GslmCamera))
+        keep.append(k)
+    if out is None:
+        out = [torch.empty((3, int(v[4]), int(v[5])), dtype=torch.float32, device=dev) for v in views]
+    for o, v in zip(out, views):
+        if not (o.is_cuda and o.dtype == torch.float32 and o.is_contiguous() and o.numel() == 3 * int(v[4]) * int(v[5])):
+            raise RuntimeError("gslm_b200: render_batch outputs must be contiguous float32 [3,H,W] CUDA tensors")
+    if n == 0:
+        return [], out
+    if g.P == 0:
+        for o in out:
+            o.zero_()
+        return [0] * n, out
+    ptrs = (C.c_void_p * n)(*[o.data_ptr() for o in out])
+    counts = (C.c_int32 * n)()
+    al = _Alloc(dev)
+    _check(L.gslm_render_batch(C.addressof(g), n, C.addressof(cams), al.cb, None, C.addressof(ptrs), None, None,
+                               C.addressof(counts), _stream()))
+    _after_forward(al)
+    return list(counts), out
 
 
 def rasterize_gaussians_jvp(background, background_grad, means3D, means3D_grad, colors, colors_grad, opacity,

@@ -290,6 +290,24 @@ class LinearSolverFunctions:
         self.loss = MultiBatchLossImageState(losses)
         return self.loss
 
+    def _render_chunks(self):
+        """(start, (end of batch 1, end of batch 2, ...)) of the view chunks loss_value() renders with one library
+        call: consecutive batches are merged while the chunk stays within RENDER_CHUNK views of ONE image size (the
+        residual of a padded batch depends on the padding, so batches of mixed sizes stay on their own)."""
+        chunk = None
+        for b0, b1 in self._batches():
+            sizes = {(int(c.image_height), int(c.image_width)) for c in self.viewpoint_cams[b0:b1]}
+            if chunk is not None and len(sizes) == 1 and sizes == chunk[2] and b1 - chunk[0] <= self.RENDER_CHUNK:
+                chunk[1].append(b1)
+                continue
+            if chunk is not None:
+                yield chunk[0], tuple(chunk[1])
+            chunk = [b0, [b1], sizes]
+        if chunk is not None:
+            yield chunk[0], tuple(chunk[1])
+
+    RENDER_CHUNK = 16      # views per gslm_render_batch call in loss_value()
+
     def loss_value(self):
         """||r(theta)||^2 at the current parameters as a 0-dim device tensor, WITHOUT building a linearisation:
         render-only forward passes (gslm_render) and the residual reduced on the fly.  What the back-tracking line
@@ -302,22 +320,38 @@ class LinearSolverFunctions:
         empty = torch.empty(0, device=dev)
         a = self._activated(with_layer=False)
         total = torch.zeros((), dtype=torch.float32, device=dev)
-        for start, end in self._batches():
-            cams = self.viewpoint_cams[start:end]
-            Hm, Wm = max(c.image_height for c in cams), max(c.image_width for c in cams)
-            images = torch.zeros((len(cams), 3, Hm, Wm), dtype=torch.float32, device=dev)
-            gt, masks = gather_targets(cams, images)
-            for i, cam in enumerate(cams):
-                H, W = int(cam.image_height), int(cam.image_width)
-                _, color, _, _ = _C.render_only(
-                    bg, a["means3D"], empty, a["opacities"], a["scales"], a["rotations"], 1.0, empty,
-                    cam.world_view_transform, cam.full_proj_transform, math.tan(cam.FoVx * 0.5),
-                    math.tan(cam.FoVy * 0.5), H, W, a["shs"], a["sh_degree"], cam.camera_center, False,
-                    pipe.antialiasing, pipe.debug)
-                images[i, :, :H, :W].copy_(color.clamp_(0, 1))
+        if not hasattr(self, "_eval_cache"):
+            self._eval_cache = {}       # targets and the render buffer of each chunk: constant over a line search
+        for start, bounds in self._render_chunks():
+            cams = self.viewpoint_cams[start:bounds[-1]]
+            sizes = [(int(c.image_height), int(c.image_width)) for c in cams]
+            Hm, Wm = max(h for h, _ in sizes), max(w for _, w in sizes)
+            uniform = all(sz == (Hm, Wm) for sz in sizes)
+            if start not in self._eval_cache:
+                images = torch.zeros((len(cams), 3, Hm, Wm), dtype=torch.float32, device=dev)
+                # targets are gathered batch by batch: a view without an alpha mask is zeroed when another view of
+                # its BATCH has one (solver/batch_training_loss.py:61-67 of the reference), so the masks of a chunk
+                # of several batches are assembled from the per-batch results
+                parts = [gather_targets(self.viewpoint_cams[b0:b1], images[b0 - start:b1 - start])
+                         for b0, b1 in zip((start,) + bounds[:-1], bounds)]
+                gt = torch.cat([p[0] for p in parts])
+                masks = None
+                if any(p[1] is not None for p in parts):
+                    masks = torch.cat([p[1] if p[1] is not None else torch.ones_like(p[0][:, :1]) for p in parts])
+                self._eval_cache[start] = (images, gt, masks)
+            images, gt, masks = self._eval_cache[start]
+            views = [(c.world_view_transform, c.full_proj_transform, math.tan(c.FoVx * 0.5), math.tan(c.FoVy * 0.5),
+                      h, w, c.camera_center) for c, (h, w) in zip(cams, sizes)]
+            # one library call and one host synchronisation per chunk of views (gslm_render_batch)
+            _, colors = _C.render_batch(bg, a["means3D"], empty, a["opacities"], a["scales"], a["rotations"], 1.0,
+                                        empty, views, a["shs"], a["sh_degree"], pipe.antialiasing, pipe.debug,
+                                        out=[images[i] for i in range(len(cams))] if uniform else None)
+            if not uniform:
+                for i, (h, w) in enumerate(sizes):
+                    images[i, :, :h, :w].copy_(colors[i])
+            images.clamp_(0, 1)
             if self.ssim:
                 lam = self._kw("opt").lambda_dssim
-                sizes = [(c.image_height, c.image_width) for c in cams]
                 al = torch.tensor([math.sqrt((1.0 - lam) / (3 * h * w)) for h, w in sizes], device=dev)
                 be = torch.tensor([math.sqrt(lam / (3 * h * w)) for h, w in sizes], device=dev)
                 r1, r2 = _C.LossBatch(images, masks, gt, al, be).blocks(want_lin=False)

@@ -125,6 +125,19 @@ int32_t gslm_forward(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn 
 int32_t gslm_render(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn alloc, void* alloc_ctx,
                     float* out_color, float* out_invdepth, int32_t* radii, int32_t* num_rendered, void* stream);
 
+/* n_views render-only passes of the same Gaussians in one call with ONE host read-back: every view is preprocessed
+ * and scanned first, the n_views instance counts come back together, then binning and blending run view after view
+ * with nothing but kernel launches in between (the reference's forward synchronises once per view,
+ * rasterizer_impl.cu:325, and its batch wrapper loops over views in Python,
+ * diff_gaussian_rasterization/batch_render.py:171-213).  This is the evaluation the back-tracking line search repeats
+ * for every step size (train_jvp.py:262-279).  cams / out_color / num_rendered: HOST arrays of n_views entries;
+ * out_invdepth and radii may be NULL (or hold NULL entries): the radii then live in the geometry allocation.
+ * The allocator is asked once for GSLM_BUF_GEOM (all views), once for GSLM_BUF_IMAGE (largest view, reused) and
+ * once for GSLM_BUF_BINNING_TEMP (largest view).  Results are bit-identical to n_views gslm_render calls. */
+int32_t gslm_render_batch(const GslmGaussians* g, int32_t n_views, const GslmCamera* cams, GslmAllocFn alloc,
+                          void* alloc_ctx, float* const* out_color, float* const* out_invdepth, int32_t* const* radii,
+                          int32_t* num_rendered, void* stream);
+
 /* Replaces _C.rasterize_gaussians_jvp (DGR/rasterize_points.cu:143-298; forwardJvp,
  * DGR/cuda_rasterizer/rasterizer_jvp_impl.h:125-325).  `gt` holds the tangent pointers in
  * the same fields as `g` (NULL => zero tangent; P/sh_degree/M/scale_modifier ignored,

@@ -271,6 +271,38 @@ def test_render_only_loss_value_matches_linearised_loss(ssim):
     assert n == int(full[0]) and torch.equal(color, full[1]) and torch.equal(radii, full[2]) and torch.equal(invd, full[6])
 
 
+def test_render_batch_equals_per_view_render_bit_for_bit():
+    """gslm_render_batch (one host synchronisation for all views) == one gslm_render per view: same instance counts,
+    same image bits, on views of different sizes; calling it twice must not depend on the reused scratch; an empty
+    view list and an empty scene are legal; loss_value() is a pure function of the parameters."""
+    import math
+    from diff_gaussian_rasterization import _C
+    from solver.solver_functions import LinearSolverFunctions
+    model, cams, loss_func, pipe, bg = _setup(P=6000, V=5)
+    small = ss.hemisphere_rig(5, 80, 56)[2]
+    cams[2] = ss.torch_camera(small, "cuda", original_image=torch.rand(3, 56, 80).cuda(), uid=2)
+    F = LinearSolverFunctions(loss_func, model, cams, batch_size=1)
+    a, e = F._activated(with_layer=False), torch.empty(0, device="cuda")
+    views = [(c.world_view_transform, c.full_proj_transform, math.tan(c.FoVx * 0.5), math.tan(c.FoVy * 0.5),
+              int(c.image_height), int(c.image_width), c.camera_center) for c in cams]
+    gargs = (bg, a["means3D"], e, a["opacities"], a["scales"], a["rotations"], 1.0, e)
+    counts, colors = _C.render_batch(*gargs, views, a["shs"], a["sh_degree"], False, False)
+    counts2, colors2 = _C.render_batch(*gargs, views, a["shs"], a["sh_degree"], False, False)
+    for v, n, col, col2 in zip(views, counts, colors, colors2):
+        n1, c1, _, _ = _C.render_only(*gargs, *v[:6], a["shs"], a["sh_degree"], v[6], False, False, False)
+        assert n == n1 and n > 0
+        assert torch.equal(col, c1) and torch.equal(col2, c1)
+    assert counts2 == counts
+    assert _C.render_batch(*gargs, [], a["shs"], a["sh_degree"], False, False) == ([], [])
+    z = torch.zeros((0, 3), device="cuda")
+    n0, c0 = _C.render_batch(bg, z, e, z[:, :1], z, torch.zeros((0, 4), device="cuda"), 1.0, e, views[:2],
+                             torch.zeros((0, 9, 3), device="cuda"), 2, False, False)
+    assert n0 == [0, 0] and all(float(c.abs().max()) == 0.0 for c in c0)
+    F.evaluate_loss()
+    assert abs(float(F.loss_value()) - float(F.loss_scalar)) <= 1e-5 * float(F.loss_scalar)
+    assert float(F.loss_value()) == float(F.loss_value())
+
+
 def test_batched_cached_maps_with_mixed_view_sizes():
     """gslm_jvp_batch / gslm_backward_batch through LinearSolverFunctions.matvec / matvec_T on views of two different
     sizes in one padded batch == the per-view entry points (gslm_jvp_cached, gslm_backward) view by view."""
