@@ -100,6 +100,7 @@ static int32_t forward_impl(const GslmGaussians* g, const GslmCamera* cam, GslmA
     if (P > 0) {
         if (launch_preprocess(*g, *cam, gv, radii, s)) return 1;
         if (debug_sync(cam, s, "preprocess")) return 1;
+        if (cam->tile_culling && run_tile_cull(gv, radii, P, W, H, s)) return 1;
         if (run_scan(gv, P, s)) return 1;
         // rasterizer_impl.cu:325 -- host synchronisation #1 of the uncached path (sizes the sort scratch)
         GSLM_CUDA_OK(cudaMemcpyAsync(&R, gv.point_offsets + (P - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
@@ -109,7 +110,7 @@ static int32_t forward_impl(const GslmGaussians* g, const GslmCamera* cam, GslmA
     void* tbuf = alloc(alloc_ctx, GSLM_BUF_BINNING_TEMP, gslm_binning_temp_bytes(P, R));
     if (!tbuf) { set_error("allocator returned null"); return 1; }
     BinningTemp bt = carve_binning_temp(tbuf, R, P);
-    if (run_binning(gv, radii, bt, iv, P, W, H, R, s)) return 1;
+    if (run_binning(gv, radii, bt, iv, P, W, H, R, cam->tile_culling != 0, s)) return 1;
     if (debug_sync(cam, s, "binning")) return 1;
     const float* features = g->colors_precomp ? g->colors_precomp : gv.rgb;
     if (launch_blend_fwd(gv, bt, iv, W, H, features, cam->bg, out_color, out_invdepth, record, s)) return 1;
@@ -175,6 +176,7 @@ int32_t gslm_render_batch(const GslmGaussians* g, int32_t n_views, const GslmCam
         for (int v = 0; v < n_views; v++) {
             GeomView gv = carve_geom(gbase + v * gstride, P);
             if (launch_preprocess(*g, cams[v], gv, radii_of(v), s)) return 1;
+            if (cams[v].tile_culling && run_tile_cull(gv, radii_of(v), P, cams[v].width, cams[v].height, s)) return 1;
             if (run_scan(gv, P, s)) return 1;
         }
         GeomView g0 = carve_geom(gbase, P);
@@ -194,7 +196,7 @@ int32_t gslm_render_batch(const GslmGaussians* g, int32_t n_views, const GslmCam
         GeomView gv = carve_geom(gbase + v * gstride, P);
         ImageView iv = carve_image(ibuf, cam.width, cam.height);
         BinningTemp bt = carve_binning_temp(tbuf, R[v], P);
-        if (run_binning(gv, radii_of(v), bt, iv, P, cam.width, cam.height, R[v], s)) return 1;
+        if (run_binning(gv, radii_of(v), bt, iv, P, cam.width, cam.height, R[v], cam.tile_culling != 0, s)) return 1;
         const float* features = g->colors_precomp ? g->colors_precomp : gv.rgb;
         if (launch_blend_fwd(gv, bt, iv, cam.width, cam.height, features, cam.bg, out_color[v],
                              out_invdepth ? out_invdepth[v] : nullptr, false, s)) return 1;

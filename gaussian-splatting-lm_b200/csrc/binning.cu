@@ -203,6 +203,150 @@ k_duplicate_keys(int P, const uint32_t* __restrict__ perm, const float2* __restr
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Exact tile culling (opt-in, GslmCamera::tile_culling; no reference counterpart).  The reference bins a Gaussian
+// into every tile of the square that bounds its 3-sigma circle (auxiliary.h:60-70), whatever its opacity and
+// orientation; most of those (tile, Gaussian) instances never reach alpha >= 1/255 at any pixel of the tile and are
+// skipped pixel by pixel in renderCUDA (forward.cu:362-364).  Here such an instance is not emitted at all when a
+// conservative bound proves it: with q(d) = (A dx^2 + C dy^2)/2 + B dx dy (so that power = -q), the blend test
+// alpha = o exp(-q) >= 1/255 needs q <= ln(255 o); q is a convex quadratic whose minimum over the tile's pixel box,
+// when the centre is outside the box, lies on one of the (at most two) box edges facing the centre, where it is a
+// clamped 1-D parabola.  The bound is relaxed by the rounding error of the fp32 evaluations on both sides, so a
+// culled instance is one renderCUDA would have skipped at every pixel: the image, final_T and the compact
+// linearisation cache are bit-identical with and without culling; only num_rendered / point_list get shorter.
+// Every operation is an explicitly rounded intrinsic: the count pass and the emission pass must agree bit for bit.
+// ---------------------------------------------------------------------------------------------
+struct CullGauss { float x, y, A, B, C, tau; };
+
+__device__ __forceinline__ CullGauss cull_setup(float2 xy, float4 co) {
+    CullGauss g;
+    g.x = xy.x; g.y = xy.y; g.A = co.x; g.B = co.y; g.C = co.z;
+    g.tau = co.w > 0.f ? logf(__fmul_rn(255.f, co.w)) : -INFINITY;
+    return g;
+}
+__device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
+// min over t in [lo, hi] of (K t^2)/2 + L t, K > 0
+__device__ __forceinline__ float parabola_min(float K, float L, float lo, float hi) {
+    const float t = clampf(__fdiv_rn(-L, K), lo, hi);
+    return __fmul_rn(t, __fmaf_rn(__fmul_rn(0.5f, K), t, L));
+}
+__device__ __forceinline__ bool tile_can_blend(const CullGauss& g, int tx, int ty, int W, int H) {
+    const float px0 = (float)(tx * TILE_X), px1 = (float)min(tx * TILE_X + TILE_X - 1, W - 1);
+    const float py0 = (float)(ty * TILE_Y), py1 = (float)min(ty * TILE_Y + TILE_Y - 1, H - 1);
+    const float dx_lo = __fsub_rn(g.x, px1), dx_hi = __fsub_rn(g.x, px0);     // d = centre - pixel (forward.cu:355)
+    const float dy_lo = __fsub_rn(g.y, py1), dy_hi = __fsub_rn(g.y, py0);
+    const float cx = clampf(0.f, dx_lo, dx_hi), cy = clampf(0.f, dy_lo, dy_hi);
+    if (!(g.A > 0.f) || !(g.C > 0.f)) return true;                           // degenerate conic: leave it to the blend
+    float qmin = 0.f;
+    if (cx != 0.f || cy != 0.f) {
+        qmin = INFINITY;
+        if (cx != 0.f)   // edge dx = cx: q = (C dy^2)/2 + (B cx) dy + (A cx^2)/2
+            qmin = __fadd_rn(parabola_min(g.C, __fmul_rn(g.B, cx), dy_lo, dy_hi), __fmul_rn(__fmul_rn(0.5f, g.A), __fmul_rn(cx, cx)));
+        if (cy != 0.f)
+            qmin = fminf(qmin, __fadd_rn(parabola_min(g.A, __fmul_rn(g.B, cy), dx_lo, dx_hi),
+                                         __fmul_rn(__fmul_rn(0.5f, g.C), __fmul_rn(cy, cy))));
+    }
+    // rounding slack: |fp32 error| of -power at any pixel of the box and of qmin is a few ulp of the term magnitudes
+    const float DX = fmaxf(fabsf(dx_lo), fabsf(dx_hi)), DY = fmaxf(fabsf(dy_lo), fabsf(dy_hi));
+    const float smax = __fmaf_rn(fabsf(g.B), __fmul_rn(DX, DY),
+                                 __fmul_rn(0.5f, __fmaf_rn(g.A, __fmul_rn(DX, DX), __fmul_rn(g.C, __fmul_rn(DY, DY)))));
+    const float slack = __fmaf_rn(4e-6f, smax, __fmaf_rn(1e-5f, fabsf(g.tau), 1e-3f));
+    return !(__fsub_rn(qmin, slack) > g.tau);
+}
+
+// tiles_touched[idx] <- number of tiles of the rect that can blend (replaces the rect area before the scan)
+__global__ void __launch_bounds__(256)
+k_cull_count(int P, const float2* __restrict__ xy, const float4* __restrict__ conic_opacity,
+             const int32_t* __restrict__ radii, int gx, int gy, int W, int H, uint32_t* __restrict__ tiles_touched) {
+    const int lane = threadIdx.x & 31;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    int x0 = 0, y0 = 0, w = 0, cnt = 0;
+    float2 p = make_float2(0.f, 0.f);
+    float4 co = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (idx < P) {
+        const int rad = radii[idx];
+        if (rad > 0) {
+            p = xy[idx];
+            co = conic_opacity[idx];
+            int x1, y1;
+            tile_rect(p.x, p.y, rad, gx, gy, x0, y0, x1, y1);
+            w = x1 - x0;
+            cnt = w > 0 && y1 > y0 ? w * (y1 - y0) : 0;
+        }
+    }
+    uint32_t mine = 0;
+    uint32_t todo = __ballot_sync(0xffffffffu, cnt > 0);
+    while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const CullGauss g = cull_setup(make_float2(__shfl_sync(0xffffffffu, p.x, src), __shfl_sync(0xffffffffu, p.y, src)),
+                                       make_float4(__shfl_sync(0xffffffffu, co.x, src), __shfl_sync(0xffffffffu, co.y, src),
+                                                   __shfl_sync(0xffffffffu, co.z, src), __shfl_sync(0xffffffffu, co.w, src)));
+        const int g_x0 = __shfl_sync(0xffffffffu, x0, src), g_y0 = __shfl_sync(0xffffffffu, y0, src);
+        const int g_w = __shfl_sync(0xffffffffu, w, src), g_cnt = __shfl_sync(0xffffffffu, cnt, src);
+        uint32_t n = 0;
+        for (int t0 = 0; t0 < g_cnt; t0 += 32) {
+            const int t = t0 + lane, ry = t / g_w, rx = t - ry * g_w;
+            const bool keep = t < g_cnt && tile_can_blend(g, g_x0 + rx, g_y0 + ry, W, H);
+            n += __popc(__ballot_sync(0xffffffffu, keep));
+        }
+        if (lane == src) mine = n;
+    }
+    if (idx < P && radii[idx] > 0) tiles_touched[idx] = mine;
+}
+
+// k_duplicate_keys with the same test: surviving tiles keep their row-major order inside the Gaussian's run
+__global__ void __launch_bounds__(256)
+k_duplicate_keys_culled(int P, const uint32_t* __restrict__ perm, const float2* __restrict__ xy,
+                        const float4* __restrict__ conic_opacity, const uint32_t* __restrict__ offsets,
+                        const uint32_t* __restrict__ tiles_sorted, const int32_t* __restrict__ radii, int gx, int gy,
+                        int W, int H, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t idx = 0, off = 0, kept = 0;
+    int x0 = 0, y0 = 0, w = 0, cnt = 0;
+    float2 p = make_float2(0.f, 0.f);
+    float4 co = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < P) {
+        idx = perm[i];
+        const int rad = radii[idx];
+        kept = tiles_sorted[i];
+        if (rad > 0 && kept > 0) {
+            p = xy[idx];
+            co = conic_opacity[idx];
+            int x1, y1;
+            tile_rect(p.x, p.y, rad, gx, gy, x0, y0, x1, y1);
+            w = x1 - x0;
+            cnt = w > 0 && y1 > y0 ? w * (y1 - y0) : 0;
+            off = offsets[i];
+        }
+    }
+    uint32_t todo = __ballot_sync(0xffffffffu, cnt > 0);
+    while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const CullGauss g = cull_setup(make_float2(__shfl_sync(0xffffffffu, p.x, src), __shfl_sync(0xffffffffu, p.y, src)),
+                                       make_float4(__shfl_sync(0xffffffffu, co.x, src), __shfl_sync(0xffffffffu, co.y, src),
+                                                   __shfl_sync(0xffffffffu, co.z, src), __shfl_sync(0xffffffffu, co.w, src)));
+        const uint32_t g_idx = __shfl_sync(0xffffffffu, idx, src), g_off = __shfl_sync(0xffffffffu, off, src);
+        const uint32_t g_kept = __shfl_sync(0xffffffffu, kept, src);
+        const int g_x0 = __shfl_sync(0xffffffffu, x0, src), g_y0 = __shfl_sync(0xffffffffu, y0, src);
+        const int g_w = __shfl_sync(0xffffffffu, w, src), g_cnt = __shfl_sync(0xffffffffu, cnt, src);
+        uint32_t base = 0;
+        for (int t0 = 0; t0 < g_cnt; t0 += 32) {
+            const int t = t0 + lane, ry = t / g_w, rx = t - ry * g_w;
+            const bool keep = t < g_cnt && tile_can_blend(g, g_x0 + rx, g_y0 + ry, W, H);
+            const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+            const uint32_t pos = base + __popc(bal & ((1u << lane) - 1u));
+            if (keep && pos < g_kept) {           // pos < g_kept always holds (same test as the count pass)
+                keys[g_off + pos] = (uint32_t)((g_y0 + ry) * gx + g_x0 + rx);
+                vals[g_off + pos] = g_idx;
+            }
+            base += __popc(bal);
+        }
+    }
+}
+
 // rasterizer_impl.cu:116-138; ranges are zero-filled first (:356)
 __global__ void __launch_bounds__(256)
 k_tile_ranges(uint32_t L, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges) {
@@ -233,8 +377,17 @@ static int sort_pairs_u32(const BinningTemp& bt, const uint32_t* kin, uint32_t* 
     return 0;
 }
 
+int run_tile_cull(const GeomView& gv, const int32_t* radii, int P, int W, int H, cudaStream_t s) {
+    if (P == 0) return 0;
+    const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    StageScope ts(ST_KEYS, s);
+    k_cull_count<<<(P + 255) / 256, 256, 0, s>>>(P, gv.means2D, gv.conic_opacity, radii, gx, gy, W, H, gv.tiles_touched);
+    GSLM_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
 int run_binning(const GeomView& gv, const int32_t* radii, const BinningTemp& bt, const ImageView& iv, int P, int W,
-                int H, int64_t R, cudaStream_t s) {
+                int H, int64_t R, bool culled, cudaStream_t s) {
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     GSLM_CUDA_OK(cudaMemsetAsync(iv.ranges, 0, sizeof(uint2) * (size_t)gx * gy, s));
     if (R == 0 || P == 0) return 0;
@@ -255,8 +408,13 @@ int run_binning(const GeomView& gv, const int32_t* radii, const BinningTemp& bt,
     GSLM_CUDA_OK(cudaGetLastError());
     size_t have = gv.scan_temp_bytes;
     GSLM_CUDA_OK(cub::DeviceScan::ExclusiveSum(gv.scan_temp, have, tt_sorted, toff, P, s));
-    k_duplicate_keys<<<(P + 255) / 256, 256, 0, s>>>(P, gv.depth_perm, gv.means2D, toff, radii, gx, gy,
-                                                     bt.keys_unsorted, bt.vals_unsorted);
+    if (culled)
+        k_duplicate_keys_culled<<<(P + 255) / 256, 256, 0, s>>>(P, gv.depth_perm, gv.means2D, gv.conic_opacity, toff,
+                                                                tt_sorted, radii, gx, gy, W, H, bt.keys_unsorted,
+                                                                bt.vals_unsorted);
+    else
+        k_duplicate_keys<<<(P + 255) / 256, 256, 0, s>>>(P, gv.depth_perm, gv.means2D, toff, radii, gx, gy,
+                                                         bt.keys_unsorted, bt.vals_unsorted);
     stage_end(ST_KEYS, s);
     GSLM_CUDA_OK(cudaGetLastError());
     const int bit = (int)higher_msb((uint32_t)(gx * gy));

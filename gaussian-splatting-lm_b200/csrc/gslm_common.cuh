@@ -164,7 +164,10 @@ int launch_preprocess_bwd_views(const GslmGaussians& g, int n_views, const GslmC
 // binning.cu
 int run_scan(const GeomView& gv, int P, cudaStream_t s);
 int run_binning(const GeomView& gv, const int32_t* radii, const BinningTemp& bt, const ImageView& iv, int P, int W,
-                int H, int64_t R, cudaStream_t s);
+                int H, int64_t R, bool culled, cudaStream_t s);
+// exact tile culling (GslmCamera::tile_culling): rewrites tiles_touched before the scan; run_binning(culled = true)
+// then emits only the surviving (tile, Gaussian) instances
+int run_tile_cull(const GeomView& gv, const int32_t* radii, int P, int W, int H, cudaStream_t s);
 // after k_blend_fwd: cstart = exclusive scan of ccount (device only)
 int run_tile_scan(const ImageView& iv, int W, int H, cudaStream_t s);
 // tile-local compact records -> dense compact arrays + per-Gaussian CSR

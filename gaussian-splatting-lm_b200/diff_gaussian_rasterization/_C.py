@@ -25,7 +25,8 @@ class GslmGaussians(C.Structure):
 class GslmCamera(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("tan_fovx", C.c_float), ("tan_fovy", C.c_float),
                 ("bg", C.c_void_p), ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("campos", C.c_void_p),
-                ("prefiltered", C.c_int32), ("antialiasing", C.c_int32), ("debug", C.c_int32)]
+                ("prefiltered", C.c_int32), ("antialiasing", C.c_int32), ("debug", C.c_int32),
+                ("tile_culling", C.c_int32)]
 
 
 class GslmCameraTangent(C.Structure):
@@ -260,13 +261,18 @@ def _tangent_gaussians(means3D, colors_precomp, opacities, scales, rotations, co
     return g, keep
 
 
-def _camera(bg, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, campos, prefiltered, antialiasing, debug):
+TILE_CULLING = False     # default of the reference-shaped entry points: bin like the reference (bit-exact point_list)
+
+
+def _camera(bg, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, campos, prefiltered, antialiasing, debug,
+            tile_culling=None):
     keep = [_f32(bg), _f32(viewmatrix), _f32(projmatrix), _f32(campos)]
     c = GslmCamera()
     c.width, c.height = int(W), int(H)
     c.tan_fovx, c.tan_fovy = float(tan_fovx), float(tan_fovy)
     c.bg, c.viewmatrix, c.projmatrix, c.campos = [_ptr(k) for k in keep]
     c.prefiltered, c.antialiasing, c.debug = int(bool(prefiltered)), int(bool(antialiasing)), int(bool(debug))
+    c.tile_culling = int(bool(TILE_CULLING if tile_culling is None else tile_culling))
     return c, keep
 
 
@@ -279,13 +285,13 @@ def _as_float(x):
 # ---------------------------------------------------------------------------------------
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
-                        prefiltered, antialiasing, debug):
+                        prefiltered, antialiasing, debug, tile_culling=None):
     """DGR/rasterize_points.cu:36-141 -> (num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepth)"""
     L = lib()
     dev = means3D.device
     g, k1 = _gaussians(means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, sh, degree)
     cam, k2 = _camera(background, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, campos,
-                      prefiltered, antialiasing, debug)
+                      prefiltered, antialiasing, debug, tile_culling)
     P, H, W = g.P, int(image_height), int(image_width)
     out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
     out_invdepth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
@@ -304,14 +310,14 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 
 def render_only(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
                 projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
-                antialiasing, debug):
+                antialiasing, debug, tile_culling=None):
     """The forward pass without the linearisation cache (gslm_render): (num_rendered, color, radii, invdepth).
     Same arguments as rasterize_gaussians; nothing that comes out of it can be differentiated."""
     L = lib()
     dev = means3D.device
     g, k1 = _gaussians(means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, sh, degree)
     cam, k2 = _camera(background, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, campos,
-                      prefiltered, antialiasing, debug)
+                      prefiltered, antialiasing, debug, tile_culling)
     P, H, W = g.P, int(image_height), int(image_width)
     out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
     out_invdepth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
@@ -328,7 +334,7 @@ def render_only(background, means3D, colors, opacity, scales, rotations, scale_m
 
 
 def render_batch(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, views, sh,
-                 degree, antialiasing, debug, out=None):
+                 degree, antialiasing, debug, out=None, tile_culling=None):
     """gslm_render_batch: render-only passes of one set of Gaussians from several cameras with one host
     synchronisation for the whole batch.  views: sequence of (viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W,
     campos).  out: optional list of [3,H,W] float32 CUDA tensors to render into (e.g. slices of a stacked batch).
@@ -340,7 +346,7 @@ def render_batch(background, means3D, colors, opacity, scales, rotations, scale_
     cams = (GslmCamera * max(n, 1))()
     keep = []
     for i, (vm, pm, tfx, tfy, H, W, campos) in enumerate(views):
-        c, k = _camera(background, vm, pm, tfx, tfy, H, W, campos, False, antialiasing, debug)
+        c, k = _camera(background, vm, pm, tfx, tfy, H, W, campos, False, antialiasing, debug, tile_culling)
         C.memmove(C.addressof(cams[i]), C.addressof(c), C.sizeof(GslmCamera))
         keep.append(k)
     if out is None:

@@ -49,8 +49,11 @@ class _ViewCache:
 class LinearSolverFunctions:
 
     def __init__(self, loss_func, gaussians, viewpoint_cams, batch_size=-1, param_mask=None, splat_mask=None,
-                 cached=None, shard_views=True):
+                 cached=None, shard_views=True, tile_culling=True):
         self.loss_func = loss_func
+        # exact tile culling in the cached mode's own forward passes (include/gslm_b200.h, GslmCamera::tile_culling):
+        # residuals, linearisation cache and every product are bit-identical with and without it
+        self.tile_culling = bool(tile_culling)
         self.gaussians = gaussians
         self.all_cams = list(viewpoint_cams)
         d = _dist() if shard_views else None
@@ -259,7 +262,7 @@ class LinearSolverFunctions:
                 (vc.R, color, vc.radii, vc.geom, vc.binning, vc.img, _) = _C.rasterize_gaussians(
                     bg, a["means3D"], self._empty, a["opacities"], a["scales"], a["rotations"], 1.0, self._empty,
                     cam.world_view_transform, cam.full_proj_transform, tfx, tfy, H, W, a["shs"], a["sh_degree"],
-                    cam.camera_center, False, pipe.antialiasing, pipe.debug)
+                    cam.camera_center, False, pipe.antialiasing, pipe.debug, tile_culling=self.tile_culling)
                 vc.cam_args = (bg, cam.world_view_transform, cam.full_proj_transform, tfx, tfy, H, W,
                                cam.camera_center, pipe.antialiasing, pipe.debug)
                 # d clamp(x,0,1)/dx as torch defines it (inclusive bounds) times the alpha mask
@@ -345,7 +348,8 @@ class LinearSolverFunctions:
             # one library call and one host synchronisation per chunk of views (gslm_render_batch)
             _, colors = _C.render_batch(bg, a["means3D"], empty, a["opacities"], a["scales"], a["rotations"], 1.0,
                                         empty, views, a["shs"], a["sh_degree"], pipe.antialiasing, pipe.debug,
-                                        out=[images[i] for i in range(len(cams))] if uniform else None)
+                                        out=[images[i] for i in range(len(cams))] if uniform else None,
+                                        tile_culling=self.tile_culling)
             if not uniform:
                 for i, (h, w) in enumerate(sizes):
                     images[i, :, :h, :w].copy_(colors[i])

@@ -56,6 +56,12 @@ typedef struct GslmCamera {
     const float* projmatrix;     /* [16] */
     const float* campos;         /* [3]  */
     int32_t prefiltered, antialiasing, debug;
+    /* 0: bin every tile of the 3-sigma bounding square like the reference (auxiliary.h:60-70): num_rendered, point_list
+     *    and ranges match rasterizer_impl.cu:321-364 bit for bit.
+     * 1: exact tile culling -- a (tile, Gaussian) instance that provably stays below alpha = 1/255 at every pixel of
+     *    the tile is not emitted.  Image, inverse depth, radii, final_T, the compact linearisation cache and hence every
+     *    derivative are bit-identical to mode 0; num_rendered, the sort and the blend's list walk shrink. */
+    int32_t tile_culling;
 } GslmCamera;
 
 /* Tangents of the camera-side inputs for the forward-mode entry points
