@@ -78,6 +78,7 @@ GeomView carve_geom(void* base, int P) {
     v.active_ids = v.g_cursor;
     v.n_active = v.num_rendered + 1;
     v.act_range = take<uint32_t>(p, n / ACT_RANGE + 2);
+    v.cull_mask = take<uint2>(p, n);
     v.scan_temp_bytes = scan_temp_bytes(P);
     v.scan_temp = take<char>(p, v.scan_temp_bytes);
     v.total = (size_t)(p - reinterpret_cast<char*>(base));
@@ -216,18 +217,20 @@ k_duplicate_keys(int P, const uint32_t* __restrict__ perm, const float2* __restr
 // linearisation cache are bit-identical with and without culling; only num_rendered / point_list get shorter.
 // Every operation is an explicitly rounded intrinsic: the count pass and the emission pass must agree bit for bit.
 // ---------------------------------------------------------------------------------------------
-struct CullGauss { float x, y, A, B, C, tau; };
+struct CullGauss { float x, y, A, B, C, rA, rC, tau; };
 
 __device__ __forceinline__ CullGauss cull_setup(float2 xy, float4 co) {
     CullGauss g;
     g.x = xy.x; g.y = xy.y; g.A = co.x; g.B = co.y; g.C = co.z;
+    g.rA = __frcp_rn(co.x); g.rC = __frcp_rn(co.z);
     g.tau = co.w > 0.f ? logf(__fmul_rn(255.f, co.w)) : -INFINITY;
     return g;
 }
 __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
-// min over t in [lo, hi] of (K t^2)/2 + L t, K > 0
-__device__ __forceinline__ float parabola_min(float K, float L, float lo, float hi) {
-    const float t = clampf(__fdiv_rn(-L, K), lo, hi);
+// min over t in [lo, hi] of (K t^2)/2 + L t, K > 0 (rK = 1/K; the value is flat around its minimiser, so the rounding
+// of the minimiser itself is a second-order effect, far inside the slack below)
+__device__ __forceinline__ float parabola_min(float K, float rK, float L, float lo, float hi) {
+    const float t = clampf(__fmul_rn(-L, rK), lo, hi);
     return __fmul_rn(t, __fmaf_rn(__fmul_rn(0.5f, K), t, L));
 }
 __device__ __forceinline__ bool tile_can_blend(const CullGauss& g, int tx, int ty, int W, int H) {
@@ -241,9 +244,10 @@ __device__ __forceinline__ bool tile_can_blend(const CullGauss& g, int tx, int t
     if (cx != 0.f || cy != 0.f) {
         qmin = INFINITY;
         if (cx != 0.f)   // edge dx = cx: q = (C dy^2)/2 + (B cx) dy + (A cx^2)/2
-            qmin = __fadd_rn(parabola_min(g.C, __fmul_rn(g.B, cx), dy_lo, dy_hi), __fmul_rn(__fmul_rn(0.5f, g.A), __fmul_rn(cx, cx)));
+            qmin = __fadd_rn(parabola_min(g.C, g.rC, __fmul_rn(g.B, cx), dy_lo, dy_hi),
+                             __fmul_rn(__fmul_rn(0.5f, g.A), __fmul_rn(cx, cx)));
         if (cy != 0.f)
-            qmin = fminf(qmin, __fadd_rn(parabola_min(g.A, __fmul_rn(g.B, cy), dx_lo, dx_hi),
+            qmin = fminf(qmin, __fadd_rn(parabola_min(g.A, g.rA, __fmul_rn(g.B, cy), dx_lo, dx_hi),
                                          __fmul_rn(__fmul_rn(0.5f, g.C), __fmul_rn(cy, cy))));
     }
     // rounding slack: |fp32 error| of -power at any pixel of the box and of qmin is a few ulp of the term magnitudes
@@ -254,28 +258,35 @@ __device__ __forceinline__ bool tile_can_blend(const CullGauss& g, int tx, int t
     return !(__fsub_rn(qmin, slack) > g.tau);
 }
 
-// tiles_touched[idx] <- number of tiles of the rect that can blend (replaces the rect area before the scan)
+// tiles_touched[idx] <- number of tiles of the rect that can blend (replaces the rect area before the scan), and the
+// survivors of the first 64 tiles of the rect (row-major) as a bit mask for the emission pass.  Rects of up to 32
+// tiles (the typical Gaussian has ~20) are walked by their own thread; the larger ones of a warp's 32 Gaussians are
+// then tested by the whole warp, one tile per lane.
 __global__ void __launch_bounds__(256)
 k_cull_count(int P, const float2* __restrict__ xy, const float4* __restrict__ conic_opacity,
-             const int32_t* __restrict__ radii, int gx, int gy, int W, int H, uint32_t* __restrict__ tiles_touched) {
+             const int32_t* __restrict__ radii, int gx, int gy, int W, int H, uint32_t* __restrict__ tiles_touched,
+             uint2* __restrict__ cull_mask) {
     const int lane = threadIdx.x & 31;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    int x0 = 0, y0 = 0, w = 0, cnt = 0;
+    int x0 = 0, y0 = 0, x1 = 0, y1 = 0, w = 0, cnt = 0;
     float2 p = make_float2(0.f, 0.f);
     float4 co = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (idx < P) {
-        const int rad = radii[idx];
-        if (rad > 0) {
-            p = xy[idx];
-            co = conic_opacity[idx];
-            int x1, y1;
-            tile_rect(p.x, p.y, rad, gx, gy, x0, y0, x1, y1);
-            w = x1 - x0;
-            cnt = w > 0 && y1 > y0 ? w * (y1 - y0) : 0;
-        }
+    if (idx < P && radii[idx] > 0) {
+        p = xy[idx];
+        co = conic_opacity[idx];
+        tile_rect(p.x, p.y, radii[idx], gx, gy, x0, y0, x1, y1);
+        w = x1 - x0;
+        cnt = w > 0 && y1 > y0 ? w * (y1 - y0) : 0;
     }
-    uint32_t mine = 0;
-    uint32_t todo = __ballot_sync(0xffffffffu, cnt > 0);
+    uint32_t n = 0, m0 = 0, m1 = 0;
+    if (cnt > 0 && cnt <= 32) {
+        const CullGauss g = cull_setup(p, co);
+        int t = 0;
+        for (int ty = y0; ty < y1; ++ty)
+            for (int tx = x0; tx < x1; ++tx, ++t)
+                if (tile_can_blend(g, tx, ty, W, H)) { n++; m0 |= 1u << t; }
+    }
+    uint32_t todo = __ballot_sync(0xffffffffu, cnt > 32);
     while (todo) {
         const int src = __ffs(todo) - 1;
         todo &= todo - 1;
@@ -284,54 +295,80 @@ k_cull_count(int P, const float2* __restrict__ xy, const float4* __restrict__ co
                                                    __shfl_sync(0xffffffffu, co.z, src), __shfl_sync(0xffffffffu, co.w, src)));
         const int g_x0 = __shfl_sync(0xffffffffu, x0, src), g_y0 = __shfl_sync(0xffffffffu, y0, src);
         const int g_w = __shfl_sync(0xffffffffu, w, src), g_cnt = __shfl_sync(0xffffffffu, cnt, src);
-        uint32_t n = 0;
+        uint32_t gn = 0, b0 = 0, b1 = 0;
         for (int t0 = 0; t0 < g_cnt; t0 += 32) {
             const int t = t0 + lane, ry = t / g_w, rx = t - ry * g_w;
-            const bool keep = t < g_cnt && tile_can_blend(g, g_x0 + rx, g_y0 + ry, W, H);
-            n += __popc(__ballot_sync(0xffffffffu, keep));
+            const uint32_t bal = __ballot_sync(0xffffffffu, t < g_cnt && tile_can_blend(g, g_x0 + rx, g_y0 + ry, W, H));
+            gn += __popc(bal);
+            if (t0 == 0) b0 = bal;
+            if (t0 == 32) b1 = bal;
         }
-        if (lane == src) mine = n;
+        if (lane == src) { n = gn; m0 = b0; m1 = b1; }
     }
-    if (idx < P && radii[idx] > 0) tiles_touched[idx] = mine;
+    if (cnt > 0) {
+        tiles_touched[idx] = n;
+        cull_mask[idx] = make_uint2(m0, m1);
+    }
 }
 
-// k_duplicate_keys with the same test: surviving tiles keep their row-major order inside the Gaussian's run
+// k_duplicate_keys with the culled counts: surviving tiles keep their row-major order inside the Gaussian's run.
+// Rects of up to 64 tiles (nearly all) are emitted from the count pass's bit mask; larger ones repeat the test.
 __global__ void __launch_bounds__(256)
 k_duplicate_keys_culled(int P, const uint32_t* __restrict__ perm, const float2* __restrict__ xy,
-                        const float4* __restrict__ conic_opacity, const uint32_t* __restrict__ offsets,
-                        const uint32_t* __restrict__ tiles_sorted, const int32_t* __restrict__ radii, int gx, int gy,
-                        int W, int H, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+                        const float4* __restrict__ conic_opacity, const uint2* __restrict__ cull_mask,
+                        const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ tiles_sorted,
+                        const int32_t* __restrict__ radii, int gx, int gy, int W, int H, uint32_t* __restrict__ keys,
+                        uint32_t* __restrict__ vals) {
     const int lane = threadIdx.x & 31;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t idx = 0, off = 0, kept = 0;
     int x0 = 0, y0 = 0, w = 0, cnt = 0;
     float2 p = make_float2(0.f, 0.f);
     float4 co = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint2 m = make_uint2(0u, 0u);
     if (i < P) {
         idx = perm[i];
         const int rad = radii[idx];
         kept = tiles_sorted[i];
         if (rad > 0 && kept > 0) {
             p = xy[idx];
-            co = conic_opacity[idx];
             int x1, y1;
             tile_rect(p.x, p.y, rad, gx, gy, x0, y0, x1, y1);
             w = x1 - x0;
             cnt = w > 0 && y1 > y0 ? w * (y1 - y0) : 0;
             off = offsets[i];
+            if (cnt > 64) co = conic_opacity[idx];
+            else m = cull_mask[idx];
         }
     }
     uint32_t todo = __ballot_sync(0xffffffffu, cnt > 0);
     while (todo) {
         const int src = __ffs(todo) - 1;
         todo &= todo - 1;
+        const uint32_t g_idx = __shfl_sync(0xffffffffu, idx, src), g_off = __shfl_sync(0xffffffffu, off, src);
+        const int g_x0 = __shfl_sync(0xffffffffu, x0, src), g_y0 = __shfl_sync(0xffffffffu, y0, src);
+        const int g_w = __shfl_sync(0xffffffffu, w, src), g_cnt = __shfl_sync(0xffffffffu, cnt, src);
+        if (g_cnt <= 64) {
+            const uint32_t m0 = __shfl_sync(0xffffffffu, m.x, src), m1 = __shfl_sync(0xffffffffu, m.y, src);
+            const uint32_t below = (1u << lane) - 1u;
+            if ((m0 >> lane) & 1u) {
+                const int ry = lane / g_w, rx = lane - ry * g_w;
+                const uint32_t pos = __popc(m0 & below);
+                keys[g_off + pos] = (uint32_t)((g_y0 + ry) * gx + g_x0 + rx);
+                vals[g_off + pos] = g_idx;
+            }
+            if ((m1 >> lane) & 1u) {
+                const int t = lane + 32, ry = t / g_w, rx = t - ry * g_w;
+                const uint32_t pos = __popc(m0) + __popc(m1 & below);
+                keys[g_off + pos] = (uint32_t)((g_y0 + ry) * gx + g_x0 + rx);
+                vals[g_off + pos] = g_idx;
+            }
+            continue;
+        }
         const CullGauss g = cull_setup(make_float2(__shfl_sync(0xffffffffu, p.x, src), __shfl_sync(0xffffffffu, p.y, src)),
                                        make_float4(__shfl_sync(0xffffffffu, co.x, src), __shfl_sync(0xffffffffu, co.y, src),
                                                    __shfl_sync(0xffffffffu, co.z, src), __shfl_sync(0xffffffffu, co.w, src)));
-        const uint32_t g_idx = __shfl_sync(0xffffffffu, idx, src), g_off = __shfl_sync(0xffffffffu, off, src);
         const uint32_t g_kept = __shfl_sync(0xffffffffu, kept, src);
-        const int g_x0 = __shfl_sync(0xffffffffu, x0, src), g_y0 = __shfl_sync(0xffffffffu, y0, src);
-        const int g_w = __shfl_sync(0xffffffffu, w, src), g_cnt = __shfl_sync(0xffffffffu, cnt, src);
         uint32_t base = 0;
         for (int t0 = 0; t0 < g_cnt; t0 += 32) {
             const int t = t0 + lane, ry = t / g_w, rx = t - ry * g_w;
@@ -381,7 +418,8 @@ int run_tile_cull(const GeomView& gv, const int32_t* radii, int P, int W, int H,
     if (P == 0) return 0;
     const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     StageScope ts(ST_KEYS, s);
-    k_cull_count<<<(P + 255) / 256, 256, 0, s>>>(P, gv.means2D, gv.conic_opacity, radii, gx, gy, W, H, gv.tiles_touched);
+    k_cull_count<<<(P + 255) / 256, 256, 0, s>>>(P, gv.means2D, gv.conic_opacity, radii, gx, gy, W, H, gv.tiles_touched,
+                                                  gv.cull_mask);
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
 }
@@ -409,7 +447,8 @@ int run_binning(const GeomView& gv, const int32_t* radii, const BinningTemp& bt,
     size_t have = gv.scan_temp_bytes;
     GSLM_CUDA_OK(cub::DeviceScan::ExclusiveSum(gv.scan_temp, have, tt_sorted, toff, P, s));
     if (culled)
-        k_duplicate_keys_culled<<<(P + 255) / 256, 256, 0, s>>>(P, gv.depth_perm, gv.means2D, gv.conic_opacity, toff,
+        k_duplicate_keys_culled<<<(P + 255) / 256, 256, 0, s>>>(P, gv.depth_perm, gv.means2D, gv.conic_opacity,
+                                                                gv.cull_mask, toff,
                                                                 tt_sorted, radii, gx, gy, W, H, bt.keys_unsorted,
                                                                 bt.vals_unsorted);
     else

@@ -51,6 +51,7 @@ struct GeomView {   // per-Gaussian state, SoA
     float* cov3D;             // [6P]
     uint8_t* clamped;         // [P] bit c = channel c clamped (forward.cu:66-72)
     uint32_t* tiles_touched;  // [P]
+    uint2* cull_mask;         // [P] tile_culling: survivors among the first 64 tiles of the rect (row-major bits)
     uint32_t* point_offsets;  // [P] inclusive scan
     uint32_t* num_rendered;   // [1] device copy of R (tail of the scan)
     uint32_t* g_off;          // [P+1] CSR offsets: compact instances of Gaussian i are g_list[g_off[i] .. g_off[i+1])
