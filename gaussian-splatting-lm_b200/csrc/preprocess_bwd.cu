@@ -52,7 +52,15 @@ __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __re
             put<false>(a.g.dL_dopacity, i, 0.f);
             for (int k = 0; k < 6; k++) put<false>(a.g.dL_dcov3D, 6 * i + k, 0.f);
             for (int k = 0; k < 4; k++) put<false>(a.g.dL_drotations, 4 * i + k, 0.f);
-            for (int k = 0; k < 3 * ncoef; k++) put<false>(a.g.dL_dsh, (size_t)3 * ncoef * i + k, 0.f);
+            if (a.g.dL_dsh && ncoef) {
+                float* row = a.g.dL_dsh + (size_t)3 * ncoef * i;
+                if ((ncoef & 3) == 0 && (reinterpret_cast<size_t>(a.g.dL_dsh) & 15u) == 0) {   // 16-byte aligned rows
+                    float4* r4 = reinterpret_cast<float4*>(row);
+                    for (int c = 0; c < 3 * ncoef / 4; c++) r4[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+                } else {
+                    for (int k = 0; k < 3 * ncoef; k++) row[k] = 0.f;
+                }
+            }
         }
         return;
     }
@@ -181,9 +189,9 @@ __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __re
         float* dsh = a.g.dL_dsh ? a.g.dL_dsh + (size_t)3 * a.M * i : nullptr;
         float ddx = 0.f, ddy = 0.f, ddz = 0.f;   // dL/d(dir)
         int used = 1;
-        // accumulate mode with 16-byte aligned gradient rows (M = 4, 16): the basis values are kept and the row is
-        // updated by float4 read-modify-writes after the sweep (12 instead of 48 load + store pairs at degree 3)
-        const bool vecd = ACC && dsh != nullptr && (a.M & 3) == 0 && (reinterpret_cast<size_t>(a.g.dL_dsh) & 15u) == 0;
+        // 16-byte aligned gradient rows (M = 4, 16): the basis values are kept and the row is written (or, in
+        // accumulate mode, updated by read-modify-write) as float4 after the sweep: 12 instead of 48 accesses at degree 3
+        const bool vecd = dsh != nullptr && (a.M & 3) == 0 && (reinterpret_cast<size_t>(a.g.dL_dsh) & 15u) == 0;
         float bv[16];
 #pragma unroll
         for (int k = 0; k < 16; k++) bv[k] = 0.f;
@@ -232,8 +240,9 @@ __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __re
             const float g3[3] = {gr, gg, gb};
 #pragma unroll
             for (int c = 0; c < 12; c++) {
-                if (4 * c < 3 * used && 4 * c < 3 * a.M) {     // coefficients >= used have bv = 0: adds exact zeros
-                    float4 q = d4[c];
+                // coefficients >= used have bv = 0: accumulate mode skips those chunks, overwrite mode stores zeros
+                if ((!ACC || 4 * c < 3 * used) && 4 * c < 3 * a.M) {
+                    float4 q = ACC ? d4[c] : make_float4(0.f, 0.f, 0.f, 0.f);
                     q.x += bv[(4 * c) / 3] * g3[(4 * c) % 3];
                     q.y += bv[(4 * c + 1) / 3] * g3[(4 * c + 1) % 3];
                     q.z += bv[(4 * c + 2) / 3] * g3[(4 * c + 2) % 3];
@@ -242,7 +251,7 @@ __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __re
                 }
             }
         }
-        if (!ACC && dsh)
+        if (!ACC && dsh && !vecd)
             for (int k = 3 * used; k < 3 * a.M; k++) dsh[k] = 0.f;
         // dnormvdv, auxiliary.h:153-164
         const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);

@@ -48,7 +48,10 @@ def main():
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--tile-culling", action="store_true",
+                    help="GslmCamera::tile_culling = 1 (same image / cache bits, shorter lists) for our forward pass")
     a = ap.parse_args()
+    C.TILE_CULLING = a.tile_culling
     rows = []
     have_ref = gs_ref.available()
     for P in [int(x) for x in a.points.split(",")]:
@@ -61,7 +64,8 @@ def main():
                 fwd = h.c_forward(C, gd, ct, antialiasing=aa)
                 R, color, radii, geom, binning, img, invd = fwd
                 u = torch.randn_like(color)
-                row = {"P": P, "sh_degree": deg, "antialiasing": aa, "W": a.width, "H": a.height, "R": int(R),
+                row = {"P": P, "sh_degree": deg, "antialiasing": aa, "tile_culling": a.tile_culling, "W": a.width,
+                       "H": a.height, "R": int(R),
                        "Rc": int(R.cached)}
                 row["ours_fwd_ms"] = timed(lambda: h.c_forward(C, gd, ct, antialiasing=aa), a.iters)
                 row["ours_bwd_ms"] = timed(lambda: h.c_backward(C, gd, ct, fwd, u, antialiasing=aa), a.iters)
