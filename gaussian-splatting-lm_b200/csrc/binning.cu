@@ -280,11 +280,37 @@ k_cull_count(int P, const float2* __restrict__ xy, const float4* __restrict__ co
     }
     uint32_t n = 0, m0 = 0, m1 = 0;
     if (cnt > 0 && cnt <= 32) {
+        // same bound as tile_can_blend with the row terms hoisted; its verdicts travel to the emission pass in the
+        // mask, so this loop need not round like tile_can_blend, only be as conservative
         const CullGauss g = cull_setup(p, co);
-        int t = 0;
-        for (int ty = y0; ty < y1; ++ty)
-            for (int tx = x0; tx < x1; ++tx, ++t)
-                if (tile_can_blend(g, tx, ty, W, H)) { n++; m0 |= 1u << t; }
+        if (!(g.A > 0.f) || !(g.C > 0.f)) { n = cnt; m0 = cnt == 32 ? 0xffffffffu : (1u << cnt) - 1u; }
+        else {
+            const float hA = 0.5f * g.A, hC = 0.5f * g.C, aB = fabsf(g.B);
+            const float thr = g.tau + fmaf(1e-5f, fabsf(g.tau), 1e-3f);
+            int t = 0;
+            for (int ty = y0; ty < y1; ++ty) {
+                const float py0 = (float)(ty * TILE_Y), py1 = (float)min(ty * TILE_Y + TILE_Y - 1, H - 1);
+                const float dy_lo = g.y - py1, dy_hi = g.y - py0;
+                const float cy = clampf(0.f, dy_lo, dy_hi), DY = fmaxf(fabsf(dy_lo), fabsf(dy_hi));
+                const float ty_c = hC * cy * cy, ty_L = g.B * cy, ty_s = hC * DY * DY;
+                for (int tx = x0; tx < x1; ++tx, ++t) {
+                    const float px0 = (float)(tx * TILE_X), px1 = (float)min(tx * TILE_X + TILE_X - 1, W - 1);
+                    const float dx_lo = g.x - px1, dx_hi = g.x - px0;
+                    const float cx = clampf(0.f, dx_lo, dx_hi), DX = fmaxf(fabsf(dx_lo), fabsf(dx_hi));
+                    float qmin = 0.f;
+                    if (cx != 0.f || cy != 0.f) {
+                        // edge dx = cx (skipped when cx == 0: the other edge then holds the minimum) and edge dy = cy
+                        const float L = g.B * cx, u = clampf(-L * g.rC, dy_lo, dy_hi);
+                        const float e1 = cx != 0.f ? fmaf(u, fmaf(hC, u, L), hA * cx * cx) : INFINITY;
+                        const float v = clampf(-ty_L * g.rA, dx_lo, dx_hi);
+                        const float e2 = cy != 0.f ? fmaf(v, fmaf(hA, v, ty_L), ty_c) : INFINITY;
+                        qmin = fminf(e1, e2);
+                    }
+                    const float smax = fmaf(aB * DX, DY, fmaf(hA * DX, DX, ty_s));
+                    if (!(qmin - 4e-6f * smax > thr)) { n++; m0 |= 1u << t; }
+                }
+            }
+        }
     }
     uint32_t todo = __ballot_sync(0xffffffffu, cnt > 32);
     while (todo) {
@@ -351,14 +377,17 @@ k_duplicate_keys_culled(int P, const uint32_t* __restrict__ perm, const float2* 
         if (g_cnt <= 64) {
             const uint32_t m0 = __shfl_sync(0xffffffffu, m.x, src), m1 = __shfl_sync(0xffffffffu, m.y, src);
             const uint32_t below = (1u << lane) - 1u;
+            // t / w for t < 64, w <= 64 without an integer division: (t + 1/2) / w is at least 1/(2w) away from
+            // every integer, far more than the rounding of the reciprocal
+            const float rw = __frcp_rn((float)g_w);
             if ((m0 >> lane) & 1u) {
-                const int ry = lane / g_w, rx = lane - ry * g_w;
+                const int ry = (int)(((float)lane + 0.5f) * rw), rx = lane - ry * g_w;
                 const uint32_t pos = __popc(m0 & below);
                 keys[g_off + pos] = (uint32_t)((g_y0 + ry) * gx + g_x0 + rx);
                 vals[g_off + pos] = g_idx;
             }
             if ((m1 >> lane) & 1u) {
-                const int t = lane + 32, ry = t / g_w, rx = t - ry * g_w;
+                const int t = lane + 32, ry = (int)(((float)t + 0.5f) * rw), rx = t - ry * g_w;
                 const uint32_t pos = __popc(m0) + __popc(m1 & below);
                 keys[g_off + pos] = (uint32_t)((g_y0 + ry) * gx + g_x0 + rx);
                 vals[g_off + pos] = g_idx;
