@@ -4,6 +4,7 @@
 // No device memory is allocated here; no torch types anywhere.
 // =============================================================================
 #include "gslm_common.cuh"
+#include <cstddef>
 #include <cstring>
 #include <vector>
 
@@ -61,7 +62,25 @@ static __global__ void k_gather_totals(const char* geom_base, size_t view_stride
 extern "C" {
 
 const char* gslm_last_error(void) { return last_error(); }
-int32_t gslm_abi_version(void) { return 1; }
+int32_t gslm_abi_version(void) { return 2; }    // 2: GslmCamera::tile_culling, gslm_render_batch, gslm_sizeof
+
+size_t gslm_sizeof(const char* n) {
+    if (!n) return 0;
+#define GSLM_SZ(T) if (!strcmp(n, #T)) return sizeof(T);
+    GSLM_SZ(GslmGaussians) GSLM_SZ(GslmCamera) GSLM_SZ(GslmCameraTangent) GSLM_SZ(GslmGrads) GSLM_SZ(GslmLossBatch)
+    GSLM_SZ(GslmActivations) GSLM_SZ(GslmRawVector) GSLM_SZ(GslmActVector) GSLM_SZ(GslmBufferView)
+#undef GSLM_SZ
+    return 0;
+}
+size_t gslm_camera_offsetof(const char* n) {
+    if (!n) return (size_t)-1;
+#define GSLM_OFF(F) if (!strcmp(n, #F)) return offsetof(GslmCamera, F);
+    GSLM_OFF(width) GSLM_OFF(height) GSLM_OFF(tan_fovx) GSLM_OFF(tan_fovy) GSLM_OFF(bg) GSLM_OFF(viewmatrix)
+    GSLM_OFF(projmatrix) GSLM_OFF(campos) GSLM_OFF(prefiltered) GSLM_OFF(antialiasing) GSLM_OFF(debug)
+    GSLM_OFF(tile_culling)
+#undef GSLM_OFF
+    return (size_t)-1;
+}
 
 size_t gslm_geom_bytes(int32_t P) { return carve_geom(nullptr, P).total; }
 size_t gslm_image_bytes(int32_t width, int32_t height) { return carve_image(nullptr, width, height).total; }

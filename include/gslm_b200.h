@@ -103,6 +103,11 @@ enum { GSLM_BUF_GEOM = 0, GSLM_BUF_BINNING = 1, GSLM_BUF_IMAGE = 2, GSLM_BUF_BIN
 
 const char* gslm_last_error(void);
 int32_t gslm_abi_version(void);
+/* sizeof() of an ABI struct by name ("GslmCamera", ...; 0 for an unknown name) and the byte offset of a field of
+ * GslmCamera: lets a binding written in another language check its mirror of the layouts before the first call
+ * (tests/test_abi.py does it for the ctypes mirrors). */
+size_t gslm_sizeof(const char* struct_name);
+size_t gslm_camera_offsetof(const char* field_name);
 
 /* Buffer sizes (bytes) -- replaces required<GeometryState/ImageState/BinningState>
  * (DGR/cuda_rasterizer/rasterizer_impl.h:29-43). */

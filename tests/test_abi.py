@@ -39,6 +39,24 @@ def test_binding_lists_the_same_symbols():
     assert sorted(_C.EXPORTS) == _declared_symbols()
 
 
+def test_ctypes_mirrors_match_the_compiled_struct_layouts(lib):
+    """The ctypes Structures of the binding against sizeof / offsetof as the library was compiled."""
+    from diff_gaussian_rasterization import _C
+    lib.gslm_sizeof.restype = ctypes.c_size_t
+    lib.gslm_sizeof.argtypes = [ctypes.c_char_p]
+    lib.gslm_camera_offsetof.restype = ctypes.c_size_t
+    lib.gslm_camera_offsetof.argtypes = [ctypes.c_char_p]
+    src = re.sub(r"/\*.*?\*/", "", open(HEADER).read(), flags=re.S)
+    names = re.findall(r"typedef struct (Gslm[A-Za-z]+)", src)
+    assert len(names) >= 9
+    for n in names:
+        assert lib.gslm_sizeof(n.encode()) == ctypes.sizeof(getattr(_C, n)) > 0, n
+    assert lib.gslm_sizeof(b"NoSuchStruct") == 0
+    for f, _ in _C.GslmCamera._fields_:
+        assert lib.gslm_camera_offsetof(f.encode()) == getattr(_C.GslmCamera, f).offset, f
+    assert lib.gslm_abi_version() >= 2
+
+
 def test_size_queries(lib):
     for n in ("gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_backward_scratch_bytes",
               "gslm_jvp_scratch_bytes", "gslm_jtjv_scratch_bytes", "gslm_binning_temp_bytes"):

@@ -220,3 +220,27 @@ def test_ply_checkpoint_roundtrip_and_reference_layout(tmp_path):
     m3 = GaussianModel(2)
     m3.load_ply(be, device="cpu", requires_grad=False)
     assert torch.equal(m3._features_rest, m._features_rest.detach()) and torch.equal(m3._rotation, m._rotation.detach())
+
+
+def test_render_chunks_merge_whole_batches_of_one_size():
+    """loss_value() renders chunks that are unions of WHOLE batches (the alpha-mask rule of the reference is per
+    batch, solver/batch_training_loss.py:61-67) of ONE image size (a padded batch's residual depends on the
+    padding), at most RENDER_CHUNK views each -- host logic only."""
+    from types import SimpleNamespace
+    from solver.solver_functions import LinearSolverFunctions
+
+    def chunks(sizes, batch_size):
+        cams = [SimpleNamespace(image_height=h, image_width=w) for h, w in sizes]
+        F = LinearSolverFunctions(lambda **k: None, SimpleNamespace(), cams, batch_size=batch_size, cached=False,
+                                  shard_views=False)
+        return list(F._render_chunks())
+
+    a, b = (96, 128), (56, 80)
+    assert chunks([a] * 5, 1) == [(0, (1, 2, 3, 4, 5))]
+    assert chunks([a] * 40, 3)[0] == (0, (3, 6, 9, 12, 15)) and chunks([a] * 40, 3)[-1] == (30, (33, 36, 39, 40))
+    assert chunks([a, a, b, a, a], 1) == [(0, (1, 2)), (2, (3,)), (3, (4, 5))]
+    assert chunks([a, b, a, a], 2) == [(0, (2,)), (2, (4,))]          # a mixed-size batch stays on its own
+    assert chunks([a] * 50, 20) == [(0, (20,)), (20, (40,)), (40, (50,))]   # batches larger than the chunk
+    assert chunks([], 4) == []
+    covered = [v for s, bounds in chunks([a] * 7 + [b] * 9 + [a] * 3, 2) for v in range(s, bounds[-1])]
+    assert covered == list(range(19))
