@@ -38,10 +38,30 @@ __global__ void __launch_bounds__(256) k_activation_jvp(Act a, GslmRawVector v, 
     const size_t n_sh = (size_t)a.P * 3 * a.M, stride = (size_t)gridDim.x * blockDim.x;
     const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int row = 3 * a.M;
-    for (size_t e = tid; e < n_sh; e += stride) {
-        const size_t i = e / row;
-        const int r = (int)(e - i * row);
-        t.shs[e] = r < 3 ? __ldg(v.features_dc + 3 * i + r) : __ldg(v.features_rest + i * (row - 3) + (r - 3));
+    if ((row & 3) == 0 && (reinterpret_cast<size_t>(t.shs) & 15u) == 0) {
+        // rows of 3 M floats with M % 4 == 0: one float4 store per thread and iteration (the two sources are read by
+        // scalars: inside a row they sit 3 floats off the 16-byte grid)
+        const int qrow = row >> 2;
+        const size_t n4 = n_sh >> 2;
+        for (size_t c = tid; c < n4; c += stride) {
+            const size_t i = c / qrow;
+            const int r = (int)(c - i * qrow) << 2;
+            const float* rest = v.features_rest + i * (row - 3) + (r - 3);
+            float4 o;
+            if (r == 0) {
+                const float* dc = v.features_dc + 3 * i;
+                o = make_float4(__ldg(dc), __ldg(dc + 1), __ldg(dc + 2), __ldg(rest + 3));
+            } else {
+                o = make_float4(__ldg(rest), __ldg(rest + 1), __ldg(rest + 2), __ldg(rest + 3));
+            }
+            reinterpret_cast<float4*>(t.shs)[c] = o;
+        }
+    } else {
+        for (size_t e = tid; e < n_sh; e += stride) {
+            const size_t i = e / row;
+            const int r = (int)(e - i * row);
+            t.shs[e] = r < 3 ? __ldg(v.features_dc + 3 * i + r) : __ldg(v.features_rest + i * (row - 3) + (r - 3));
+        }
     }
     for (size_t i = tid; i < (size_t)a.P; i += stride) {
 #pragma unroll
@@ -67,16 +87,37 @@ __global__ void __launch_bounds__(256) k_activation_vjp(Act a, GslmActVector g, 
     const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int row = 3 * a.M;
     const bool dv = v.xyz != nullptr;
-    for (size_t e = tid; e < n_sh; e += stride) {
-        const size_t i = e / row;
-        const int r = (int)(e - i * row);
-        const float gv = __ldg(g.shs + e);
-        if (r < 3) {
-            const size_t k = 3 * i + r;
-            out.features_dc[k] = dv ? fmaf(d.dc, __ldg(v.features_dc + k), gv) : gv;
-        } else {
-            const size_t k = i * (row - 3) + (r - 3);
-            out.features_rest[k] = dv ? fmaf(d.rest, __ldg(v.features_rest + k), gv) : gv;
+    if ((row & 3) == 0 && (reinterpret_cast<size_t>(g.shs) & 15u) == 0) {
+        const int qrow = row >> 2;
+        const size_t n4 = n_sh >> 2;
+        for (size_t c = tid; c < n4; c += stride) {
+            const size_t i = c / qrow;
+            const int r = (int)(c - i * qrow) << 2;
+            const float4 gq = __ldg(reinterpret_cast<const float4*>(g.shs) + c);
+            const float gv[4] = {gq.x, gq.y, gq.z, gq.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (r + j < 3) {
+                    const size_t k = 3 * i + r + j;
+                    out.features_dc[k] = dv ? fmaf(d.dc, __ldg(v.features_dc + k), gv[j]) : gv[j];
+                } else {
+                    const size_t k = i * (row - 3) + (r + j - 3);
+                    out.features_rest[k] = dv ? fmaf(d.rest, __ldg(v.features_rest + k), gv[j]) : gv[j];
+                }
+            }
+        }
+    } else {
+        for (size_t e = tid; e < n_sh; e += stride) {
+            const size_t i = e / row;
+            const int r = (int)(e - i * row);
+            const float gv = __ldg(g.shs + e);
+            if (r < 3) {
+                const size_t k = 3 * i + r;
+                out.features_dc[k] = dv ? fmaf(d.dc, __ldg(v.features_dc + k), gv) : gv;
+            } else {
+                const size_t k = i * (row - 3) + (r - 3);
+                out.features_rest[k] = dv ? fmaf(d.rest, __ldg(v.features_rest + k), gv) : gv;
+            }
         }
     }
     for (size_t i = tid; i < (size_t)a.P; i += stride) {

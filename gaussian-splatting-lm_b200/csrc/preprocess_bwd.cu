@@ -70,7 +70,23 @@ __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __re
     float2 s2 = make_float2(0.f, 0.f);
     {
         const float4* r = a.inst_grads + (size_t)REC_F4 * beg;
-        for (uint32_t slot = beg; slot < end; slot++, r += REC_F4) {
+        uint32_t slot = beg;
+        // four records in flight per round trip (the adds keep their order: same bits); the run of a Gaussian is
+        // ~13 records long and one dependent load per record made this loop the latency of the whole stage
+        for (; slot + 4 <= end; slot += 4, r += 4 * REC_F4) {
+            float4 q[4][3];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                q[j][0] = __ldg(r + REC_F4 * j); q[j][1] = __ldg(r + REC_F4 * j + 1); q[j][2] = __ldg(r + REC_F4 * j + 2);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                s0.x += q[j][0].x; s0.y += q[j][0].y; s0.z += q[j][0].z; s0.w += q[j][0].w;
+                s1.x += q[j][1].x; s1.y += q[j][1].y; s1.z += q[j][1].z; s1.w += q[j][1].w;
+                s2.x += q[j][2].x; s2.y += q[j][2].y;
+            }
+        }
+        for (; slot < end; slot++, r += REC_F4) {
             const float4 q0 = __ldg(r), q1 = __ldg(r + 1), q2 = __ldg(r + 2);
             s0.x += q0.x; s0.y += q0.y; s0.z += q0.z; s0.w += q0.w;
             s1.x += q1.x; s1.y += q1.y; s1.z += q1.z; s1.w += q1.w;
@@ -238,16 +254,21 @@ __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __re
         if (vecd) {
             float4* d4 = reinterpret_cast<float4*>(dsh);
             const float g3[3] = {gr, gg, gb};
+            // coefficients >= used have bv = 0: accumulate mode skips those chunks, overwrite mode stores zeros.
+            // All loads of the row are issued before its first store: the sinks are not __restrict__, a load placed
+            // after a store would wait for it (12 dependent round trips per Gaussian instead of one).
+            float4 q[12];
+#pragma unroll
+            for (int c = 0; c < 12; c++)
+                q[c] = (ACC && 4 * c < 3 * used && 4 * c < 3 * a.M) ? d4[c] : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
             for (int c = 0; c < 12; c++) {
-                // coefficients >= used have bv = 0: accumulate mode skips those chunks, overwrite mode stores zeros
                 if ((!ACC || 4 * c < 3 * used) && 4 * c < 3 * a.M) {
-                    float4 q = ACC ? d4[c] : make_float4(0.f, 0.f, 0.f, 0.f);
-                    q.x += bv[(4 * c) / 3] * g3[(4 * c) % 3];
-                    q.y += bv[(4 * c + 1) / 3] * g3[(4 * c + 1) % 3];
-                    q.z += bv[(4 * c + 2) / 3] * g3[(4 * c + 2) % 3];
-                    q.w += bv[(4 * c + 3) / 3] * g3[(4 * c + 3) % 3];
-                    d4[c] = q;
+                    q[c].x += bv[(4 * c) / 3] * g3[(4 * c) % 3];
+                    q[c].y += bv[(4 * c + 1) / 3] * g3[(4 * c + 1) % 3];
+                    q[c].z += bv[(4 * c + 2) / 3] * g3[(4 * c + 2) % 3];
+                    q[c].w += bv[(4 * c + 3) / 3] * g3[(4 * c + 3) % 3];
+                    d4[c] = q[c];
                 }
             }
         }
@@ -261,6 +282,7 @@ __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __re
     }
 
     // ---- 5. cov3D -> scale / quaternion     backward.cu:330-393 ----
+    float sr[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};     // d scale[3], d quaternion[4]
     if (a.scales) {
         const float4 q = reinterpret_cast<const float4*>(a.rotations)[i];
         const float r = q.x, x = q.y, y = q.z, z = q.w;
@@ -303,25 +325,44 @@ __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __re
         const float dq3 = 2.f * r * (Dm(0, 1) - Dm(1, 0)) + 2.f * x * (Dm(2, 0) + Dm(0, 2)) + 2.f * y * (Dm(1, 2) + Dm(2, 1)) -
                           4.f * z * (Dm(1, 1) + Dm(0, 0));
         // the reference writes the gradient w.r.t. the *modified* scale (no scale_modifier factor), backward.cu:371-375
-        for (int k = 0; k < 3; k++) put<ACC>(a.g.dL_dscales, 3 * i + k, dscale[k]);
-        put<ACC>(a.g.dL_drotations, 4 * i + 0, dq0);
-        put<ACC>(a.g.dL_drotations, 4 * i + 1, dq1);
-        put<ACC>(a.g.dL_drotations, 4 * i + 2, dq2);
-        put<ACC>(a.g.dL_drotations, 4 * i + 3, dq3);
-    } else if (!ACC) {
-        for (int k = 0; k < 3; k++) put<false>(a.g.dL_dscales, 3 * i + k, 0.f);
-        for (int k = 0; k < 4; k++) put<false>(a.g.dL_drotations, 4 * i + k, 0.f);
+        for (int k = 0; k < 3; k++) sr[k] = dscale[k];
+        sr[3] = dq0; sr[4] = dq1; sr[5] = dq2; sr[6] = dq3;
     }
     if (!a.shs && !ACC && a.g.dL_dsh)
         for (int k = 0; k < 3 * a.M; k++) a.g.dL_dsh[(size_t)3 * a.M * i + k] = 0.f;
 
-    put<ACC>(a.g.dL_dmeans2D, 3 * i + 0, g2x);
-    put<ACC>(a.g.dL_dmeans2D, 3 * i + 1, g2y);
-    put<ACC>(a.g.dL_dmeans2D, 3 * i + 2, 0.f);
-    for (int k = 0; k < 3; k++) put<ACC>(a.g.dL_dcolors, 3 * i + k, dcol[k]);
-    put<ACC>(a.g.dL_dopacity, i, dL_dop);
-    for (int k = 0; k < 3; k++) put<ACC>(a.g.dL_dmeans3D, 3 * i + k, dmean[k]);
-    for (int k = 0; k < 6; k++) put<ACC>(a.g.dL_dcov3D, 6 * i + k, dcov[k]);
+    // ---- 6. the 22 small sinks: in accumulate mode every old value is loaded before the first store (the sinks are
+    //         not __restrict__: interleaved read-modify-writes would be 22 dependent round trips) ----
+    const bool w_sr = a.scales != nullptr || !ACC;     // without scales the overwrite mode still stores zeros
+    float* const sc = w_sr ? a.g.dL_dscales : nullptr;
+    float* const rq = w_sr ? a.g.dL_drotations : nullptr;
+    auto ld = [&](const float* p, size_t j) { return (ACC && p) ? p[j] : 0.f; };
+    float o_sr[7], o_m2[2], o_col[3], o_m3[3], o_cov[6];
+#pragma unroll
+    for (int k = 0; k < 3; k++) o_sr[k] = ld(sc, 3 * i + k);
+#pragma unroll
+    for (int k = 0; k < 4; k++) o_sr[3 + k] = ld(rq, 4 * i + k);
+    o_m2[0] = ld(a.g.dL_dmeans2D, 3 * i); o_m2[1] = ld(a.g.dL_dmeans2D, 3 * i + 1);
+#pragma unroll
+    for (int k = 0; k < 3; k++) { o_col[k] = ld(a.g.dL_dcolors, 3 * i + k); o_m3[k] = ld(a.g.dL_dmeans3D, 3 * i + k); }
+    const float o_op = ld(a.g.dL_dopacity, i);
+#pragma unroll
+    for (int k = 0; k < 6; k++) o_cov[k] = ld(a.g.dL_dcov3D, 6 * i + k);
+    auto st = [&](float* p, size_t j, float old, float v) { if (p) p[j] = ACC ? old + v : v; };
+#pragma unroll
+    for (int k = 0; k < 3; k++) st(sc, 3 * i + k, o_sr[k], sr[k]);
+#pragma unroll
+    for (int k = 0; k < 4; k++) st(rq, 4 * i + k, o_sr[3 + k], sr[3 + k]);
+    st(a.g.dL_dmeans2D, 3 * i, o_m2[0], g2x);
+    st(a.g.dL_dmeans2D, 3 * i + 1, o_m2[1], g2y);
+    if (!ACC) st(a.g.dL_dmeans2D, 3 * i + 2, 0.f, 0.f);
+#pragma unroll
+    for (int k = 0; k < 3; k++) st(a.g.dL_dcolors, 3 * i + k, o_col[k], dcol[k]);
+    st(a.g.dL_dopacity, i, o_op, dL_dop);
+#pragma unroll
+    for (int k = 0; k < 3; k++) st(a.g.dL_dmeans3D, 3 * i + k, o_m3[k], dmean[k]);
+#pragma unroll
+    for (int k = 0; k < 6; k++) st(a.g.dL_dcov3D, 6 * i + k, o_cov[k], dcov[k]);
 }
 
 template <bool ACC>
