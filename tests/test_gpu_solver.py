@@ -303,6 +303,34 @@ def test_render_batch_equals_per_view_render_bit_for_bit():
     assert float(F.loss_value()) == float(F.loss_value())
 
 
+def test_normal_product_over_several_chunks_equals_sum_of_chunks():
+    """More than 16 views: gslm_jtjv_batch walks them in chunks of 16 (one tangent, one tile and one adjoint launch
+    per chunk).  The product over 37 views must equal the sum of the products over the three chunks taken alone
+    (same per-view arithmetic, same view order => same bits), repeated calls must be bit-identical, and the result
+    must be visible to the caller's stream when the call returns."""
+    from solver.solver_functions import LinearSolverFunctions
+    model, cams, loss_func, pipe, bg = _setup(P=5000, V=37, W=96, H=64)
+    with torch.no_grad():
+        F = LinearSolverFunctions(loss_func, model, cams, batch_size=8)
+        F.evaluate_loss()
+        v = _rand_state(model, 21)
+        ref, qref = F.normal_matvec(v, return_quad=True)
+        ref, qref = ref.packed().clone(), float(qref)
+        for _ in range(3):
+            assert torch.equal(F.normal_matvec(v).packed(), ref)
+        parts, quad = [], 0.0
+        for lo in (0, 16, 32):
+            G = LinearSolverFunctions(loss_func, model, cams[lo:lo + 16], batch_size=8)
+            G.evaluate_loss()
+            out, q = G.normal_matvec(v, return_quad=True)
+            parts.append(out.packed().clone())
+            quad += float(q)
+        total = parts[0] + parts[1] + parts[2]
+        assert float((total - ref).abs().max()) <= 1e-5 * float(ref.abs().max())   # regrouped fp32 sums
+        assert abs(quad - qref) <= 1e-4 * abs(qref)
+        assert float(ref.abs().max()) > 0
+
+
 def test_batched_cached_maps_with_mixed_view_sizes():
     """gslm_jvp_batch / gslm_backward_batch through LinearSolverFunctions.matvec / matvec_T on views of two different
     sizes in one padded batch == the per-view entry points (gslm_jvp_cached, gslm_backward) view by view."""
