@@ -245,6 +245,7 @@ class LinearSolverFunctions:
         self._act = a = self._activated()
         self._views = []
         self._plan = None
+        self._eval_cache = {}          # loss_value()'s stacked targets are re-gathered after every linearisation
         self._loss_batches = []
         losses = []
         for start, end in self._batches():
@@ -314,7 +315,9 @@ class LinearSolverFunctions:
     def loss_value(self):
         """||r(theta)||^2 at the current parameters as a 0-dim device tensor, WITHOUT building a linearisation:
         render-only forward passes (gslm_render) and the residual reduced on the fly.  What the back-tracking line
-        search needs (train_jvp.py:262-279 calls evaluate_loss + loss_scalar seven times per LM step)."""
+        search needs (train_jvp.py:262-279 calls evaluate_loss + loss_scalar seven times per LM step).  The stacked
+        targets / alpha masks of the views are gathered on the first call and reused until the next linearize():
+        they are constants of a line search."""
         if not self.cached:
             self.evaluate_loss()
             return self.loss_scalar
