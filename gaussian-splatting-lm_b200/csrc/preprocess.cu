@@ -165,8 +165,11 @@ struct PreTanView {
 };
 struct PreTanBatch { PreTanView v[MAX_BATCH_VIEWS]; };
 
+#ifndef GSLM_TAN_MINB
+#define GSLM_TAN_MINB 3
+#endif
 template <bool CAMT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, GSLM_TAN_MINB)
 k_preprocess_tangent(PreTanArgs a, const __grid_constant__ PreTanBatch vb) {
     const PreTanView& vw = vb.v[blockIdx.y];
     const uint32_t n_active = *vw.n_active;
