@@ -31,6 +31,7 @@ struct TileArgs {          // one linearised view
     const uint32_t* cid;
     const uint32_t* g_inv;
     const float* final_T;
+    const uint32_t* order;     // launch slot -> tile id (longest lists first)
     int W, H, tiles;
     const float* bg;
 };
@@ -38,8 +39,9 @@ struct TileArgs {          // one linearised view
 __device__ __forceinline__ bool make_tile(const TileArgs& a, int warp, WTile& c) {
     c.lane = threadIdx.x & 31;
     c.lbit = 1u << c.lane;
-    const int tile = blockIdx.x * DWARPS + warp;
-    if (tile >= a.tiles) return false;
+    const int slot = blockIdx.x * DWARPS + warp;
+    if (slot >= a.tiles) return false;
+    const int tile = (int)__ldg(a.order + slot);
     const int gx = (a.W + TILE_X - 1) / TILE_X;
     c.W = a.W; c.H = a.H;
     c.px = (tile % gx) * TILE_X + (c.lane & 15);
@@ -230,7 +232,7 @@ k_blend_jtjv(const __grid_constant__ JtjvBatch vb, float* __restrict__ out_vJJv)
 static int tiles_of(int W, int H) { return ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y); }
 static TileArgs tile_args(const BinningView& bv, const ImageView& iv, int W, int H, const float* bg) {
     TileArgs a;
-    a.cstart = iv.cstart; a.records = bv.records; a.masks = bv.masks; a.cid = bv.cid; a.g_inv = bv.g_inv; a.final_T = iv.final_T;
+    a.cstart = iv.cstart; a.records = bv.records; a.masks = bv.masks; a.cid = bv.cid; a.g_inv = bv.g_inv; a.final_T = iv.final_T; a.order = iv.order;
     a.W = W; a.H = H; a.tiles = tiles_of(W, H); a.bg = bg;
     return a;
 }

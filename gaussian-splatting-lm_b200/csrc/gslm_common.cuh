@@ -72,6 +72,7 @@ struct ImageView {  // per-pixel / per-tile state
     uint2* ranges;            // [T] full-list ranges (ImageState::ranges)
     uint32_t* ccount;         // [T] compact instances per tile
     uint32_t* cstart;         // [T+1] exclusive scan of ccount; cstart[T] = Rc
+    uint32_t* order;          // [T] tile ids, longest compact lists first: the launch order of the derivative tile kernels
     size_t total;
 };
 struct BinningView {  // compact per-instance state that outlives the forward pass (92 B / compact instance)
