@@ -625,7 +625,21 @@ __global__ void __launch_bounds__(1024) k_tile_order(int T, const uint32_t* __re
         for (int c = 127; c >= 0; --c) { s_at[c] = at; at += s_n[c]; }
     }
     __syncthreads();
-    for (int t = tid; t < T; t += blockDim.x) order[atomicAdd(&s_at[length_class(ccount[t])], 1u)] = (uint32_t)t;
+    // stable placement by ONE warp, 32 tiles per step: inside a class the tiles keep their id order, so neighbours
+    // of one class (which share Gaussians, i.e. tangent rows in L2) still run together
+    if (tid < 32) {
+        for (int t0 = 0; t0 < T; t0 += 32) {
+            const int t = t0 + tid;
+            const int c = t < T ? length_class(ccount[t]) : 127 + 1 + tid;    // out-of-range lanes: unique fake class
+            const uint32_t peers = __match_any_sync(0xffffffffu, c);
+            const int leader = __ffs(peers) - 1;
+            uint32_t base = 0;
+            if (tid == leader && t < T) { base = s_at[c]; s_at[c] = base + __popc(peers); }
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (t < T) order[base + __popc(peers & ((1u << tid) - 1u))] = (uint32_t)t;
+            __syncwarp();
+        }
+    }
 }
 
 int run_compaction(const GeomView& gv, const BinningView& bv, const BinningTemp& bt, const ImageView& iv, int P,
