@@ -503,6 +503,17 @@ int32_t gslm_backward_batch(const GslmGaussians* g, int32_t n_views, const GslmC
     return 0;
 }
 
+int32_t gslm_tangent_records(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam,
+                             const GslmCameraTangent* camt, const void* geom_buffer, float* out_records, void* stream) {
+    if (check_inputs(g, cam)) return 1;
+    if (!geom_buffer || !out_records) { set_error("null argument"); return 1; }
+    if (g->P == 0) return 0;
+    GeomView gv = carve_geom(const_cast<void*>(geom_buffer), g->P);
+    TangentPtrs t = make_tangents(gt, camt);
+    if (launch_preprocess_tangent(*g, t, *cam, gv, reinterpret_cast<float4*>(out_records), (cudaStream_t)stream)) return 1;
+    return debug_sync(cam, (cudaStream_t)stream, "tangent_records");
+}
+
 int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_rendered, int64_t num_cached,
                          const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
                          const void* binning_temp_buffer, GslmBufferView* out) {

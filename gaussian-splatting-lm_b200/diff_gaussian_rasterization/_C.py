@@ -99,7 +99,7 @@ EXPORTS = ("gslm_last_error", "gslm_abi_version", "gslm_sizeof", "gslm_camera_of
            "gslm_jtjv_batch_scratch_bytes", "gslm_jtjv_batch", "gslm_jvp_batch_scratch_bytes", "gslm_jvp_batch",
            "gslm_backward_batch_scratch_bytes", "gslm_backward_batch", "gslm_loss_lin_bytes", "gslm_loss_blocks",
            "gslm_loss_blocks_jvp", "gslm_loss_blocks_vjp", "gslm_activation_jvp", "gslm_activation_vjp",
-           "gslm_buffer_view", "gslm_timing_num_stages",
+           "gslm_buffer_view", "gslm_tangent_records", "gslm_timing_num_stages",
            "gslm_timing_stage_name", "gslm_timing_enable", "gslm_timing_collect")
 
 
@@ -146,6 +146,7 @@ def lib():
         L.gslm_activation_jvp.argtypes = [vp, vp, vp, vp]
         L.gslm_activation_vjp.argtypes = [vp, vp, vp, vp, vp, vp]
         L.gslm_buffer_view.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int64, vp, vp, vp, vp, vp]
+        L.gslm_tangent_records.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.gslm_timing_stage_name.restype = C.c_char_p
         L.gslm_timing_collect.argtypes = [vp, vp]
         _lib = L
@@ -478,6 +479,30 @@ def jvp_cached(gauss_args, tangent_args, cam_args, radii, geomBuffer, R, binning
                              out_t.data_ptr(),
                              _ptr(out_d), _stream()))
     return out_t, out_d
+
+
+def tangent_records(gauss_args, tangent_args, cam_args, geomBuffer, cam_tangent=None):
+    """Introspection for tests (gslm_tangent_records): [P,12] per-Gaussian tangent records of a linearised view; rows of
+    Gaussians without a cached instance stay NaN.  cam_tangent: dict with any of bg, viewmatrix, projmatrix, campos
+    (tensors), tan_fovx, tan_fovy, scale_modifier (floats)."""
+    L = lib()
+    g, k1 = _gaussians(*gauss_args)
+    gt, k3 = _tangent_gaussians(*tangent_args)
+    bg, vm, pm, tfx, tfy, H, W, campos, aa, dbg = cam_args
+    cam, k2 = _camera(bg, vm, pm, tfx, tfy, H, W, campos, False, aa, dbg)
+    ct, k4 = None, []
+    if cam_tangent:
+        ct = GslmCameraTangent()
+        k4 = [_f32(cam_tangent.get(k)) if cam_tangent.get(k) is not None else None
+              for k in ("bg", "viewmatrix", "projmatrix", "campos")]
+        ct.bg, ct.viewmatrix, ct.projmatrix, ct.campos = [_ptr(k) if k is not None else None for k in k4]
+        ct.tan_fovx, ct.tan_fovy = float(cam_tangent.get("tan_fovx", 0.0)), float(cam_tangent.get("tan_fovy", 0.0))
+        ct.scale_modifier = float(cam_tangent.get("scale_modifier", 0.0))
+    out = torch.full((g.P, 12), float("nan"), dtype=torch.float32, device=k1[0].device)
+    _check(L.gslm_tangent_records(C.addressof(g), C.addressof(gt), C.addressof(cam),
+                                  C.addressof(ct) if ct is not None else None, _ptr(geomBuffer), out.data_ptr(),
+                                  _stream()))
+    return out
 
 
 def jtjv(gauss_args, tangent_args, cam_args, radii, geomBuffer, R, binningBuffer, imageBuffer, weight, outs,

@@ -335,6 +335,18 @@ int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_r
                          const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
                          const void* binning_temp_buffer, GslmBufferView* out);
 
+/* Introspection for tests: the per-Gaussian TANGENT records of one linearised view, i.e. the output of the tangent
+ * preprocess (the restatement of preprocessCUDAJvp, DGR/cuda_rasterizer/forward_impl.h:208-367) exactly as the tile
+ * sweeps consume it.  out_records: [P,12] floats, row of Gaussian i =
+ *   (a1, a2, a3, a4 | a5, o_t / o, r_t, g_t | b_t, (1/depth)_t, 0, 0)   with, for the reference's per-Gaussian
+ * tangents (means2D_t = (x_t, y_t), conic_t = (A_t, B_t, C_t), opacity o_t, rgb_t, depth_t) of
+ * DGR/tests/render_data/{means2D,conic_opacity,rgb,depth}_grad.csv:
+ *   a1 = -(A x_t + B y_t), a2 = -(C y_t + B x_t), a3 = -A_t / 2, a4 = -C_t / 2, a5 = -B_t, (1/depth)_t = -depth_t / depth^2.
+ * Only rows of Gaussians that own a cached instance in this view are written (the others are never read).
+ * camt may be NULL.  tests/test_gpu_parity.py compares the rows with the reference's golden tangents. */
+int32_t gslm_tangent_records(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam,
+                             const GslmCameraTangent* camt, const void* geom_buffer, float* out_records, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

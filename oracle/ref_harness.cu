@@ -121,6 +121,72 @@ int gsref_state(uint32_t* point_list, uint32_t* ranges, uint32_t* n_contrib, flo
     return 0;
 }
 
+#ifdef GSREF_WITH_JVP
+// ---- forward mode: the reference's own JVP kernels (preprocessCUDAJvp, renderCUDAJvpSplit) driven through
+// CudaRasterizer::Rasterizer::forwardJvp exactly as RasterizeGaussiansJvpCUDA does (rasterize_points.cu:244-297):
+// every differentiable input travels as a FloatGradArray<float> / FloatGrad<float> (value, tangent).  Only built when
+// the functional float_grad.h stand-in (oracle/ref_shim) is in use.  All tangent pointers must be valid device
+// arrays of the primal's size (zeros for "no tangent"); colors_precomp / cov3D_precomp may be NULL (both halves).
+int gsref_forward_jvp(int P, int D, int M, const float* background, const float* background_t, int W, int H,
+                      const float* means3D, const float* means3D_t, const float* shs, const float* shs_t,
+                      const float* colors_precomp, const float* colors_precomp_t, const float* opacities,
+                      const float* opacities_t, const float* scales, const float* scales_t, float scale_modifier,
+                      float scale_modifier_t, const float* rotations, const float* rotations_t,
+                      const float* cov3D_precomp, const float* cov3D_precomp_t, const float* viewmatrix,
+                      const float* viewmatrix_t, const float* projmatrix, const float* projmatrix_t,
+                      const float* campos, const float* campos_t, float tan_fovx, float tan_fovx_t, float tan_fovy,
+                      float tan_fovy_t, int prefiltered, int antialiasing, float* out_color, float* out_color_t,
+                      float* out_invdepth, float* out_invdepth_t, int* radii, int debug) {
+    try {
+        std::function<char*(size_t)> ga = [](size_t n) { return g_geom.get(n); };
+        std::function<char*(size_t)> ba = [](size_t n) { return g_bin.get(n); };
+        std::function<char*(size_t)> ia = [](size_t n) { return g_img.get(n); };
+        g_P = P; g_W = W; g_H = H;
+        auto A = [](const float* d, const float* t) { return FloatGradArray<float>(const_cast<float*>(d), const_cast<float*>(t)); };
+        FloatGradArray<float> bg = A(background, background_t), m3 = A(means3D, means3D_t), sh = A(shs, shs_t),
+                              col = A(colors_precomp, colors_precomp_t), op = A(opacities, opacities_t),
+                              sc = A(scales, scales_t), rot = A(rotations, rotations_t),
+                              cov = A(cov3D_precomp, cov3D_precomp_t), vm = A(viewmatrix, viewmatrix_t),
+                              pm = A(projmatrix, projmatrix_t), cp = A(campos, campos_t),
+                              oc = A(out_color, out_color_t), od = A(out_invdepth, out_invdepth_t);
+        FloatGrad<float> smod(scale_modifier, scale_modifier_t), tfx(tan_fovx, tan_fovx_t), tfy(tan_fovy, tan_fovy_t);
+        const bool pre = prefiltered != 0, aa = antialiasing != 0, dbg = debug != 0;
+        g_R = CudaRasterizer::Rasterizer::forwardJvp(ga, ba, ia, P, D, M, bg, W, H, m3, sh, col, op, sc, smod, rot, cov, vm,
+                                                     pm, cp, tfx, tfy, pre, oc, od, aa, radii, dbg);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e == cudaSuccess) e = cudaGetLastError();
+        if (e != cudaSuccess) { g_err = cudaGetErrorString(e); return -1; }
+        return g_R;
+    } catch (const std::exception& ex) {
+        g_err = ex.what();
+        return -1;
+    }
+}
+
+// Per-Gaussian tangent records of the last gsref_forward_jvp call (the tail of GeometryStateJvp,
+// rasterizer_impl.cu:172-194): depths_t [P], means2D_t [P,2], cov3D_t [P,6], conic_opacity_t [P,4], rgb_t [P,3];
+// plus the primal conic_opacity [P,4] and rgb [P,3].  Any pointer may be NULL.
+int gsref_jvp_state(float* depths_t, float* means2D_t, float* cov3D_t, float* conic_opacity_t, float* rgb_t,
+                    float* conic_opacity, float* rgb) {
+    using namespace CudaRasterizer;
+    char* gp = g_geom.p;
+    GeometryStateJvp geom = GeometryStateJvp::fromChunk(gp, g_P);
+    const size_t P = (size_t)g_P;
+    auto cp = [](void* dst, const void* src, size_t n) {
+        return !dst || n == 0 || cudaMemcpy(dst, src, n, cudaMemcpyDeviceToDevice) == cudaSuccess;
+    };
+    bool ok = cp(depths_t, geom.depths.grad_ptr(), 4 * P) && cp(means2D_t, geom.means2D.grad_ptr(), 8 * P) &&
+              cp(cov3D_t, geom.cov3D.grad_ptr(), 24 * P) && cp(conic_opacity_t, geom.conic_opacity.grad_ptr(), 16 * P) &&
+              cp(rgb_t, geom.rgb.grad_ptr(), 12 * P) && cp(conic_opacity, geom.conic_opacity.data_ptr(), 16 * P) &&
+              cp(rgb, geom.rgb.data_ptr(), 12 * P);
+    if (!ok) { g_err = "jvp state copy failed"; return -1; }
+    return 0;
+}
+int gsref_has_jvp() { return 1; }
+#else
+int gsref_has_jvp() { return 0; }
+#endif
+
 void gsref_mark_visible(int P, float* means3D, float* viewmatrix, float* projmatrix, bool* present) {
     CudaRasterizer::Rasterizer::markVisible(P, means3D, viewmatrix, projmatrix, present);
 }
