@@ -72,6 +72,8 @@ def cpu_jtjv_views(g, cams, tangent, views):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import gs_oracle as o
     import scene_synth as ss
+    if hasattr(o, "set_num_threads"):
+        o.set_num_threads(os.cpu_count() or 1)
     t0 = time.perf_counter()
     for i in views:
         c = ss.camera_dict(cams[i])
@@ -95,6 +97,8 @@ def run_reference(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1 to its workers: the CPU arm is entitled to every host core
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     import scene_synth as ss
     g, cams = ss.make_config(a.config, sh_degree=a.sh_degree, views=a.views or None, P=a.points or None)
     P, V = g["means3D"].shape[0], len(cams)
@@ -111,12 +115,14 @@ def run_reference(a):
             break
     per_view = sum(times) / (len(times) * n)
     value = 1.0 / (per_view * V)
-    sample = f"{n} of {V} views per step, {len(times)} timed steps; per-view time x {V} views = one matvec"
+    sample = (f"{n} of {V} views per step, {len(times)} timed steps; value and ms_per_step are EXTRAPOLATED: "
+              f"measured per-view time x {V} views = one matvec (timed CPU work: {sum(times):.1f} s)")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": len(times),
         "warmup": a.warmup, "ms_per_step": per_view * V * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(a, P, V, W, H)},
+        "ms_per_step_extrapolated": True, "measured_s": sum(times),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
@@ -182,7 +188,10 @@ def main():
     P, V = g["means3D"].shape[0], len(cams_np)
     W, H = cams_np[0].image_width, cams_np[0].image_height
     model = GaussianModel.from_activated(g, device=dev, num_cameras=V, requires_grad=False)
-    cams = [ss.torch_camera(c, dev, uid=i) for i, c in enumerate(cams_np)]
+    # gt = 0: ONE shared zero target (config D has 256 views per rank list; the solver copies targets
+    # into its own per-batch stacks)
+    zero_gt = torch.zeros(3, H, W, device=dev)
+    cams = [ss.torch_camera(c, dev, original_image=zero_gt, uid=i) for i, c in enumerate(cams_np)]
     pipe = SimpleNamespace(debug=False, antialiasing=False, compute_cov3D_python=False, convert_SHs_python=False)
     loss_func = functools.partial(batch_training_loss, iteration=1, opt=SimpleNamespace(lambda_dssim=0.2), pipe=pipe,
                                   bg=torch.zeros(3, device=dev), train_test_exp=False,
@@ -197,11 +206,22 @@ def main():
             torch.cuda.synchronize()
 
     # ---- linearisation (once per LM step; untimed for the headline, reported) ----
+    # cold = the first pass of the process (every buffer is a fresh cudaMalloc); warm = what every later LM step pays
+    # (the caching allocator hands the same blocks back)
     sync_all()
     t0 = time.perf_counter()
     F.evaluate_loss()
     sync_all()
-    linearize_ms = (time.perf_counter() - t0) * 1e3
+    linearize_cold_ms = (time.perf_counter() - t0) * 1e3
+    lin_passes = []
+    for _ in range(2):
+        n_malloc = torch.cuda.memory_stats(dev).get("num_device_alloc", 0)
+        t0 = time.perf_counter()
+        F.linearize()
+        sync_all()
+        lin_passes.append((round((time.perf_counter() - t0) * 1e3, 2),
+                           torch.cuda.memory_stats(dev).get("num_device_alloc", 0) - n_malloc))
+    linearize_ms = min(t for t, _ in lin_passes)
     R_total = sum(int(vc.R) for vc in F._views)
     R_cached = sum(vc.R.cached for vc in F._views)     # instances some pixel blended: what every CG iteration sweeps
     pix = sum(vc.W * vc.H for vc in F._views)
@@ -251,6 +271,14 @@ def main():
     if sampler:
         sampler.start()
     ms_step = timed(step, a.steps)
+
+    # fixed-seed check values, printed so that the lines at N = 1 / 2 / 4 / 8 can be compared by eye
+    with torch.no_grad():
+        chk = F.normal_matvec(v)
+        check = {"norm_JtJv": float(torch.linalg.vector_norm(chk.packed().double())),
+                 "v_JtJv": float(torch.dot(v.packed().double(), chk.packed().double())),
+                 "loss": float(F.loss_scalar)}
+        del chk
 
     # ---- end to end: v from pinned host memory, result back to the host, every step ----
     n_flat = v.length
@@ -312,13 +340,26 @@ def main():
     alg_flops = (24.0 * 256 * R_cached + 154.0 * hits) / launches
     if a.ssim:
         alg_flops = pix * 3 * (3 * 44.0 + 8) * 2 / launches       # 3 separable 11-tap blurs (22 FMA) + epilogue
-    fp32_peak = 71.6   # TFLOP/s, scalar FFMA measured on this pool's B200 with tools/ffma2_bench.cu (profiles/r1_ffma2_bench.txt)
+    # FP32 peak measured IN THIS RUN on this device (gslm_fp32_peak_probe: scalar FFMA on independent chains = the
+    # FLOP peak; packed FFMA2 with three distinct register operands = what the sweeps issue; + MUFU = their mix)
+    probe = {name: round(_C.fp32_peak_probe(mode, dev)[0], 2) for mode, name in
+             ((0, "scalar_ffma"), (1, "ffma2_3reg"), (2, "ffma2_3reg_mufu"))}
+    fp32_peak = probe["scalar_ffma"]
     traffic = None
-    tj = os.path.join(ROOT, "profiles", "traffic.json")   # dram bytes of the same kernel from the ncu --set full capture
+    executed = None
+    tj = os.path.join(ROOT, "profiles", "traffic.json")   # counters of the same kernel from the ncu --set full capture
     if os.path.exists(tj):
         t = json.load(open(tj))
         if t.get("kernel") == "k_blend_jtjv" and t.get("views_per_launch") and not a.ssim:
-            traffic = t["dram_bytes_per_launch"] / t["views_per_launch"] * (n_local / launches)
+            scale = (n_local / launches) / t["views_per_launch"]
+            traffic = t["dram_bytes_per_launch"] * scale
+            if t.get("executed_flops_per_launch"):
+                ex = t["executed_flops_per_launch"] * scale
+                executed = {"flops_per_launch": ex, "achieved": ex / dur_s / 1e12 if dur_s > 0 else 0.0,
+                            "frac": (ex / dur_s / 1e12) / fp32_peak if dur_s > 0 else 0.0,
+                            "issue_active_pct": t.get("issue_active_pct"), "fma_pipe_pct": t.get("fma_pipe_pct"),
+                            "alu_pipe_pct": t.get("alu_pipe_pct"), "xu_pipe_pct": t.get("xu_pipe_pct"),
+                            "source": t.get("executed_source")}
     result = {
         "metric": METRIC, "value": 1e3 / ms_step, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
@@ -328,21 +369,37 @@ def main():
                    "visible_gaussians_per_view_mean_rank0": (sum(p_vis) / len(p_vis)) if p_vis else 0,
                    "tile_list_length_rank0": tile_q,
                    "l2_policy": "inputs larger than L2 (per-view records + gradients >> 126 MB)",
-                   "linearize_ms": round(linearize_ms, 2), "mask_xyz": bool(a.mask_xyz)},
+                   "linearize_ms": round(linearize_ms, 2), "linearize_cold_ms": round(linearize_cold_ms, 2),
+                   "linearize_warm_passes_ms_and_cudaMallocs": lin_passes,
+                   "view_ids_rank0": F.view_ids if len(F.view_ids) <= 64 else F.view_ids[:64],
+                   "mask_xyz": bool(a.mask_xyz)},
+        "check": check,
         "e2e": {"value": 1e3 / ms_e2e, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": 4 * n_flat,
                 "d2h_bytes_per_step": 4 * n_flat, "per_rank_bytes": moved,
                 "staging": "each rank copies 1/N of the replicated vector from pinned host memory + all_gather; result slices back"},
         "gpu_launches": int(launches_per_step) * a.steps,
-        "roofline": {"kernel": "k_loss_stream<3> (loss-block JVP, VJP)" if a.ssim else "k_blend_jtjv", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved / hbm_peak, "traffic": traffic,
-                     "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s",
-                     "launch_ms": dur_s * 1e3, "launches_per_step": launches, "alg_bytes_per_launch": alg_bytes,
-                     "binding_roof": {"bound": "fp32 (FMA pipe / issue slots; no tensor-core work on this path)",
-                                      "achieved": alg_flops / dur_s / 1e12 if dur_s > 0 else 0.0, "peak": fp32_peak,
-                                      "unit": "TFLOP/s", "frac": (alg_flops / dur_s / 1e12) / fp32_peak if dur_s > 0 else 0.0,
-                                      "alg_flops_per_launch": alg_flops, "pairs_hit_rank0": hits}},
         "stage_ms_per_step": stage_share,
     }
+    hbm_roof = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                "alg_bytes_per_launch": alg_bytes,
+                "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s"}
+    if a.ssim:
+        # the loss-block kernels stream image planes: HBM is their roof
+        result["roofline"] = dict(hbm_roof, kernel="k_loss_stream<3> (loss-block JVP, VJP)", traffic=None,
+                                  launch_ms=dur_s * 1e3, launches_per_step=launches)
+    else:
+        # k_blend_jtjv is FP32-pipe / issue bound (no tensor-core work on this path): `frac` is the
+        # ALGORITHMIC flop count (the reference algorithm's: 24 per tested pair + 154 per hit) over the FP32 peak
+        # measured in this run; `executed` = the flops the kernel really issues (SASS opcode counts of the ncu
+        # capture, profiles/) -- the kernel takes hit / skip from masks and uses the moment form of the adjoint, so it
+        # executes fewer flops than the algorithm it replaces.  The HBM view of the same launch rides along.
+        alg_tf = alg_flops / dur_s / 1e12 if dur_s > 0 else 0.0
+        result["roofline"] = {"kernel": "k_blend_jtjv", "bound": "fp32", "achieved": alg_tf, "peak": fp32_peak,
+                              "unit": "TFLOP/s", "frac": alg_tf / fp32_peak if fp32_peak else 0.0, "traffic": traffic,
+                              "peak_source": "measured in this run (gslm_fp32_peak_probe, scalar FFMA)",
+                              "fp32_probe_tflops": probe, "launch_ms": dur_s * 1e3, "launches_per_step": launches,
+                              "alg_flops_per_launch": alg_flops, "pairs_hit_rank0": hits, "executed": executed,
+                              "hbm": hbm_roof}
     if sampler:
         sampler.join(timeout=2)
         result["clocks"] = sampler.summary()

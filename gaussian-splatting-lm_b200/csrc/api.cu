@@ -59,16 +59,60 @@ static __global__ void k_gather_totals(const char* geom_base, size_t view_stride
     if (v < n_views) totals[v] = *reinterpret_cast<const uint32_t*>(geom_base + v * view_stride + offset_of_last);
 }
 
+// What the solver derives from each rendered image, in one pass (the reference does it with ~8 torch elementwise
+// kernels per view: clamp, compares, mask products, the residual subtraction; gaussian_renderer/batch_render.py:118,
+// solver/batch_training_loss.py:10-17).
+static __global__ void k_residual_epilogue(const float* __restrict__ color, int W, int H, GslmResidualEpilogue e) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, c = blockIdx.z;
+    if (x >= W) return;
+    const float v = color[((size_t)c * H + y) * W + x];
+    const float am = e.alpha_mask ? e.alpha_mask[(size_t)y * e.alpha_row + x] : 1.f;
+    // d clamp(x, 0, 1) / dx as torch defines it: 1 on the closed interval
+    float m = (v >= 0.f && v <= 1.f) ? 1.f : 0.f;
+    float img = fminf(fmaxf(v, 0.f), 1.f);
+    if (v != v) img = v;      // torch.clamp propagates NaN
+    // individually rounded like the torch composition it replaces (a contracted fma would differ in the last bit)
+    if (e.apply_alpha_mask) { img = __fmul_rn(img, am); m = __fmul_rn(m, am); }
+    if (e.gt && e.subtract_gt) img = __fsub_rn(img, e.gt[(size_t)c * e.gt_plane + (size_t)y * e.gt_row + x]);
+    if (e.out_image) e.out_image[(size_t)c * e.image_plane + (size_t)y * e.image_row + x] = img;
+    if (e.out_mask) e.out_mask[(size_t)c * e.mask_plane + (size_t)y * e.mask_row + x] = m;
+    if (e.out_weight) e.out_weight[((size_t)c * H + y) * W + x] = __fmul_rn(__fmul_rn(e.weight_scale, m), m);
+}
+
+static int launch_residual_epilogue(const float* color, int W, int H, const GslmResidualEpilogue& e, cudaStream_t s) {
+    if (!e.out_image && !e.out_mask && !e.out_weight) return 0;
+    k_residual_epilogue<<<dim3((W + 255) / 256, H, 3), 256, 0, s>>>(color, W, H, e);
+    GSLM_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+// small grow-only pinned host buffer for the instance counts of a forward batch (so that the read-backs are truly
+// asynchronous and the host can run ahead of the device)
+static uint32_t* pinned_counts(size_t n) {
+    static thread_local uint32_t* buf = nullptr;
+    static thread_local size_t cap = 0;
+    if (n > cap) {
+        if (buf) cudaFreeHost(buf);
+        buf = nullptr;
+        cap = 0;
+        const size_t want = n < 256 ? 256 : n;
+        if (cudaMallocHost(reinterpret_cast<void**>(&buf), want * sizeof(uint32_t)) != cudaSuccess) return nullptr;
+        cap = want;
+    }
+    return buf;
+}
+
 extern "C" {
 
 const char* gslm_last_error(void) { return last_error(); }
-int32_t gslm_abi_version(void) { return 2; }    // 2: GslmCamera::tile_culling, gslm_render_batch, gslm_sizeof
+int32_t gslm_abi_version(void) { return 3; }    // 2: GslmCamera::tile_culling, gslm_render_batch, gslm_sizeof; 3: gslm_forward_batch, gslm_count_instances
 
 size_t gslm_sizeof(const char* n) {
     if (!n) return 0;
 #define GSLM_SZ(T) if (!strcmp(n, #T)) return sizeof(T);
     GSLM_SZ(GslmGaussians) GSLM_SZ(GslmCamera) GSLM_SZ(GslmCameraTangent) GSLM_SZ(GslmGrads) GSLM_SZ(GslmLossBatch)
     GSLM_SZ(GslmActivations) GSLM_SZ(GslmRawVector) GSLM_SZ(GslmActVector) GSLM_SZ(GslmBufferView)
+    GSLM_SZ(GslmResidualEpilogue)
 #undef GSLM_SZ
     return 0;
 }
@@ -222,6 +266,125 @@ int32_t gslm_render_batch(const GslmGaussians* g, int32_t n_views, const GslmCam
         if (debug_sync(&cam, s, "render_batch")) return 1;
     }
     return 0;
+}
+
+int32_t gslm_count_instances(const GslmGaussians* g, int32_t n_views, const GslmCamera* cams, GslmAllocFn alloc,
+                             void* alloc_ctx, int32_t* num_rendered, void* stream) {
+    if (n_views < 0 || (n_views > 0 && (!cams || !num_rendered)) || !alloc || !g) { set_error("null argument"); return 1; }
+    for (int v = 0; v < n_views; v++) {
+        if (check_inputs(g, &cams[v])) return 1;
+        num_rendered[v] = 0;
+    }
+    const int P = g->P;
+    if (n_views == 0 || P == 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    // one geometry state + radii, reused view after view (stream order); the counts collect in a device array
+    const size_t gbytes = align_up(gslm_geom_bytes(P)), rbytes = align_up((size_t)P * sizeof(int32_t));
+    char* base = (char*)alloc(alloc_ctx, -1, 128 + gbytes + rbytes + align_up((size_t)n_views * sizeof(uint32_t)));
+    if (!base) { set_error("allocator returned null"); return 1; }
+    base = (char*)align_up((size_t)base);
+    int32_t* radii = reinterpret_cast<int32_t*>(base + gbytes);
+    uint32_t* totals = reinterpret_cast<uint32_t*>(base + gbytes + rbytes);
+    GeomView gv = carve_geom(base, P);
+    for (int v = 0; v < n_views; v++) {
+        if (launch_preprocess(*g, cams[v], gv, radii, s)) return 1;
+        if (cams[v].tile_culling && run_tile_cull(gv, radii, P, cams[v].width, cams[v].height, s)) return 1;
+        if (run_scan(gv, P, s)) return 1;
+        GSLM_CUDA_OK(cudaMemcpyAsync(totals + v, gv.point_offsets + (P - 1), sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+    }
+    std::vector<uint32_t> R(n_views, 0u);
+    GSLM_CUDA_OK(cudaMemcpyAsync(R.data(), totals, n_views * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    GSLM_CUDA_OK(cudaStreamSynchronize(s));
+    for (int v = 0; v < n_views; v++) num_rendered[v] = (int32_t)R[v];
+    return 0;
+}
+
+int32_t gslm_forward_batch(const GslmGaussians* g, int32_t n_views, const GslmCamera* cams, GslmAllocFn alloc,
+                           void* alloc_ctx, float* const* out_color, float* const* out_invdepth,
+                           int32_t* const* radii, const GslmResidualEpilogue* epilogues, int32_t* num_rendered,
+                           int32_t* num_cached, void* stream) {
+    if (n_views < 0 || (n_views > 0 && (!cams || !out_color || !radii || !num_rendered || !num_cached)) || !alloc || !g) {
+        set_error("null argument");
+        return 1;
+    }
+    if (n_views == 0) return 0;
+    for (int v = 0; v < n_views; v++) {
+        if (check_inputs(g, &cams[v])) return 1;
+        if (!out_color[v] || (g->P > 0 && !radii[v])) { set_error("null argument"); return 1; }
+        num_rendered[v] = num_cached[v] = 0;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    const int P = g->P;
+    std::vector<GeomView> gv(n_views);
+    std::vector<ImageView> iv(n_views);
+    for (int v = 0; v < n_views; v++) {
+        void* gb = alloc(alloc_ctx, GSLM_BUF_GEOM | (v << 8), gslm_geom_bytes(P));
+        void* ib = alloc(alloc_ctx, GSLM_BUF_IMAGE | (v << 8), gslm_image_bytes(cams[v].width, cams[v].height));
+        if (!gb || !ib) { set_error("allocator returned null"); return 1; }
+        gv[v] = carve_geom(gb, P);
+        iv[v] = carve_image(ib, cams[v].width, cams[v].height);
+    }
+    uint32_t* host = pinned_counts(2 * (size_t)n_views);
+    if (!host) { set_error("pinned host allocation failed"); return 1; }
+    uint32_t* R = host;
+    uint32_t* Rc = host + n_views;
+    for (int v = 0; v < 2 * n_views; v++) host[v] = 0u;
+    // phase 1: every view preprocessed, culled and scanned; ONE synchronisation for all instance counts
+    if (P > 0) {
+        for (int v = 0; v < n_views; v++) {
+            if (launch_preprocess(*g, cams[v], gv[v], radii[v], s)) return 1;
+            if (cams[v].tile_culling && run_tile_cull(gv[v], radii[v], P, cams[v].width, cams[v].height, s)) return 1;
+            if (run_scan(gv[v], P, s)) return 1;
+            GSLM_CUDA_OK(cudaMemcpyAsync(R + v, gv[v].point_offsets + (P - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        }
+        GSLM_CUDA_OK(cudaStreamSynchronize(s));
+    }
+    uint32_t Rmax = 0;
+    for (int v = 0; v < n_views; v++) { num_rendered[v] = (int32_t)R[v]; Rmax = R[v] > Rmax ? R[v] : Rmax; }
+    // phase 2: bin + blend view v while the host waits for the compact count of view v - 1 (two sort scratches):
+    // the device never idles on a read-back
+    const int n_slots = n_views > 1 ? 2 : 1;
+    void* tbuf[2] = {nullptr, nullptr};
+    for (int k = 0; k < n_slots; k++) {
+        tbuf[k] = alloc(alloc_ctx, GSLM_BUF_BINNING_TEMP | (k << 8), gslm_binning_temp_bytes(P, Rmax));
+        if (!tbuf[k]) { set_error("allocator returned null"); return 1; }
+    }
+    cudaEvent_t ev[2];
+    for (int k = 0; k < 2; k++) GSLM_CUDA_OK(cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming));
+    int rc = 0;
+    auto finish = [&](int u) -> int {
+        const GslmCamera& cam = cams[u];
+        const int T = ((cam.width + TILE_X - 1) / TILE_X) * ((cam.height + TILE_Y - 1) / TILE_Y);
+        (void)T;
+        GSLM_CUDA_OK(cudaEventSynchronize(ev[u & 1]));
+        num_cached[u] = (int32_t)Rc[u];
+        void* bbuf = alloc(alloc_ctx, GSLM_BUF_BINNING | (u << 8), gslm_binning_bytes(Rc[u]));
+        if (!bbuf) { set_error("allocator returned null"); return 1; }
+        BinningView bv = carve_binning(bbuf, Rc[u]);
+        BinningTemp bt = carve_binning_temp(tbuf[u % n_slots], R[u], P);
+        if (P > 0 && run_compaction(gv[u], bv, bt, iv[u], P, cam.width, cam.height, Rc[u], s)) return 1;
+        return 0;
+    };
+    for (int v = 0; v < n_views && !rc; v++) {
+        const GslmCamera& cam = cams[v];
+        const int W = cam.width, H = cam.height;
+        const int T = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+        BinningTemp bt = carve_binning_temp(tbuf[v % n_slots], R[v], P);
+        const float* features = g->colors_precomp ? g->colors_precomp : gv[v].rgb;
+        rc = run_binning(gv[v], radii[v], bt, iv[v], P, W, H, R[v], cam.tile_culling != 0, s)
+             || launch_blend_fwd(gv[v], bt, iv[v], W, H, features, cam.bg, out_color[v],
+                                 out_invdepth ? out_invdepth[v] : nullptr, true, s)
+             || run_tile_scan(iv[v], W, H, s);
+        if (rc) break;
+        if (cudaMemcpyAsync(Rc + v, iv[v].cstart + T, sizeof(uint32_t), cudaMemcpyDeviceToHost, s) != cudaSuccess ||
+            cudaEventRecord(ev[v & 1], s) != cudaSuccess) { set_error("forward_batch: read-back failed"); rc = 1; break; }
+        if (epilogues && launch_residual_epilogue(out_color[v], W, H, epilogues[v], s)) { rc = 1; break; }
+        if (v >= 1) rc = finish(v - 1);
+        if (!rc && cam.debug) rc = debug_sync(&cam, s, "forward_batch");
+    }
+    if (!rc) rc = finish(n_views - 1);
+    for (int k = 0; k < 2; k++) cudaEventDestroy(ev[k]);
+    return rc;
 }
 
 int32_t gslm_jvp_cached(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam, const int32_t* radii,

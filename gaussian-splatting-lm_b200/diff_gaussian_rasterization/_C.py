@@ -59,6 +59,13 @@ class GslmActVector(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("means3D", "shs", "scales", "rotations", "opacities")]
 
 
+class GslmResidualEpilogue(C.Structure):
+    _fields_ = [("gt", C.c_void_p), ("alpha_mask", C.c_void_p), ("out_image", C.c_void_p), ("out_mask", C.c_void_p),
+                ("out_weight", C.c_void_p), ("gt_plane", C.c_int64), ("gt_row", C.c_int64), ("alpha_row", C.c_int64),
+                ("image_plane", C.c_int64), ("image_row", C.c_int64), ("mask_plane", C.c_int64), ("mask_row", C.c_int64),
+                ("weight_scale", C.c_float), ("apply_alpha_mask", C.c_int32), ("subtract_gt", C.c_int32)]
+
+
 class GslmBufferView(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("point_list", "tile_keys_sorted", "ranges", "n_contrib", "final_T",
                                           "tiles_touched", "point_offsets", "depths", "means2D", "conic_opacity",
@@ -94,7 +101,8 @@ def _cached(R, imageBuffer=None, W=None, H=None):
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_int32, C.c_size_t)
 
 EXPORTS = ("gslm_last_error", "gslm_abi_version", "gslm_sizeof", "gslm_camera_offsetof", "gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_binning_temp_bytes",
-           "gslm_mark_visible", "gslm_forward", "gslm_render", "gslm_render_batch", "gslm_forward_jvp", "gslm_backward_scratch_bytes", "gslm_backward",
+           "gslm_mark_visible", "gslm_forward", "gslm_render", "gslm_render_batch", "gslm_forward_batch",
+           "gslm_count_instances", "gslm_fp32_probe_scratch_bytes", "gslm_fp32_peak_probe", "gslm_forward_jvp", "gslm_backward_scratch_bytes", "gslm_backward",
            "gslm_jvp_scratch_bytes", "gslm_jvp_cached", "gslm_jtjv_scratch_bytes", "gslm_jtjv",
            "gslm_jtjv_batch_scratch_bytes", "gslm_jtjv_batch", "gslm_jvp_batch_scratch_bytes", "gslm_jvp_batch",
            "gslm_backward_batch_scratch_bytes", "gslm_backward_batch", "gslm_loss_lin_bytes", "gslm_loss_blocks",
@@ -128,6 +136,10 @@ def lib():
         L.gslm_forward.argtypes = [vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp, vp]
         L.gslm_render.argtypes = [vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp]
         L.gslm_render_batch.argtypes = [vp, C.c_int32, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp]
+        L.gslm_forward_batch.argtypes = [vp, C.c_int32, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp, vp, vp]
+        L.gslm_count_instances.argtypes = [vp, C.c_int32, vp, ALLOC_FN, vp, vp, vp]
+        L.gslm_fp32_probe_scratch_bytes.restype = C.c_size_t
+        L.gslm_fp32_peak_probe.argtypes = [C.c_int32, vp, vp, vp, vp]
         L.gslm_forward_jvp.argtypes = [vp, vp, vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         L.gslm_backward.argtypes = [vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
         L.gslm_jvp_cached.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp]
@@ -194,11 +206,13 @@ class _Alloc:
 
     def _alloc(self, _ctx, which, nbytes):
         which, nbytes = int(which), max(int(nbytes), 1)
-        if which == 3:
-            # sort scratch: dead when the call returns, so ONE grow-only buffer per (device, stream) serves every
+        # batch calls (gslm_forward_batch) ask with kind | (index << 8): per-view buffers / the two sort scratch slots
+        kind, index = (which & 0xff, which >> 8) if which >= 0 else (which, 0)
+        if kind == 3:
+            # sort scratch: dead when the call returns, so ONE grow-only buffer per (device, stream, slot) serves every
             # forward call (stream order makes the reuse safe); a fresh multi-GB torch.empty per view costs
             # milliseconds of allocator work and fragments the cache
-            key = (self.device, _stream())
+            key = (self.device, _stream(), index)
             t = _SORT_SCRATCH.get(key)
             if t is None or t.numel() < nbytes:
                 _SORT_SCRATCH.pop(key, None)
@@ -216,6 +230,22 @@ class _Alloc:
 
 
 _SORT_SCRATCH = {}            # (device, stream) -> grow-only uint8 tensor
+
+
+def _view_tuple(v):
+    return v[0], v[1], float(v[2]), float(v[3]), int(v[4]), int(v[5]), v[6]
+
+
+def _camera_array(background, views, antialiasing, debug, tile_culling):
+    n = len(views)
+    cams = (GslmCamera * max(n, 1))()
+    keep = []
+    for i, v in enumerate(views):
+        vm, pm, tfx, tfy, H, W, campos = _view_tuple(v)
+        c, k = _camera(background, vm, pm, tfx, tfy, H, W, campos, False, antialiasing, debug, tile_culling)
+        C.memmove(C.addressof(cams[i]), C.addressof(c), C.sizeof(GslmCamera))
+        keep.append(k)
+    return cams, keep
 
 
 def release_scratch():
@@ -368,6 +398,114 @@ def render_batch(background, means3D, colors, opacity, scales, rotations, scale_
                                C.addressof(counts), _stream()))
     _after_forward(al)
     return list(counts), out
+
+
+def count_instances(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, views, sh,
+                    degree, antialiasing=False, tile_culling=None):
+    """gslm_count_instances: num_rendered of every view (list of ints) without rendering; one host synchronisation."""
+    L = lib()
+    g, k1 = _gaussians(means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, sh, degree)
+    n = len(views)
+    if n == 0 or g.P == 0:
+        return [0] * n
+    cams, keep = _camera_array(background, views, antialiasing, False, tile_culling)
+    counts = (C.c_int32 * n)()
+    al = _Alloc(k1[0].device)
+    _check(L.gslm_count_instances(C.addressof(g), n, C.addressof(cams), al.cb, None, C.addressof(counts), _stream()))
+    al.cb = None
+    return list(counts)
+
+
+class ResidualSpec:
+    """Per-view outputs of the fused residual epilogue of forward_batch (GslmResidualEpilogue): strided views into the
+    solver's padded batch tensors.  image / mask: [3,H,W] views (any strides with unit column stride), weight:
+    contiguous [3,H,W]; gt: [3,H,W] view or None; alpha_mask: [1,H,W] / [H,W] view or None."""
+    __slots__ = ("gt", "alpha_mask", "image", "mask", "weight", "weight_scale", "apply_alpha_mask", "subtract_gt")
+
+    def __init__(self, image=None, mask=None, weight=None, gt=None, alpha_mask=None, weight_scale=1.0,
+                 apply_alpha_mask=True, subtract_gt=True):
+        self.gt, self.alpha_mask, self.image, self.mask, self.weight = gt, alpha_mask, image, mask, weight
+        self.weight_scale, self.apply_alpha_mask, self.subtract_gt = weight_scale, apply_alpha_mask, subtract_gt
+
+    def c_struct(self, H, W):
+        def chk3(t, name):
+            if t is None:
+                return None, 0, 0
+            if not (t.is_cuda and t.dtype == torch.float32 and tuple(t.shape) == (3, H, W) and (W == 1 or t.stride(2) == 1)):
+                raise RuntimeError(f"gslm_b200: epilogue {name} must be a float32 CUDA [3,{H},{W}] view with unit column stride")
+            return t.data_ptr(), t.stride(0), t.stride(1)
+        e = GslmResidualEpilogue()
+        e.gt, e.gt_plane, e.gt_row = chk3(self.gt, "gt")
+        e.out_image, e.image_plane, e.image_row = chk3(self.image, "image")
+        e.out_mask, e.mask_plane, e.mask_row = chk3(self.mask, "mask")
+        if self.weight is not None:
+            if not (self.weight.is_contiguous() and tuple(self.weight.shape) == (3, H, W) and self.weight.is_cuda
+                    and self.weight.dtype == torch.float32):
+                raise RuntimeError("gslm_b200: epilogue weight must be a contiguous float32 CUDA [3,H,W] tensor")
+            e.out_weight = self.weight.data_ptr()
+        am = self.alpha_mask
+        if am is not None:
+            am = am.reshape(am.shape[-2], am.shape[-1]) if am.dim() == 3 else am
+            if not (am.is_cuda and am.dtype == torch.float32 and tuple(am.shape) == (H, W) and (W == 1 or am.stride(1) == 1)):
+                raise RuntimeError("gslm_b200: epilogue alpha_mask must be a float32 CUDA [H,W] view")
+            e.alpha_mask, e.alpha_row = am.data_ptr(), am.stride(0)
+        e.weight_scale = float(self.weight_scale)
+        e.apply_alpha_mask, e.subtract_gt = int(bool(self.apply_alpha_mask)), int(bool(self.subtract_gt))
+        return e
+
+
+def forward_batch(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, views, sh,
+                  degree, antialiasing, debug, residual=None, tile_culling=None, want_invdepth=False):
+    """gslm_forward_batch: the LINEARISING forward pass (rasterize_gaussians) of several cameras in one library call.
+    views: sequence of (viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, campos); residual: optional list of
+    ResidualSpec (one per view).  Returns a list of per-view tuples with the layout of rasterize_gaussians:
+    (num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepth-or-None)."""
+    L = lib()
+    dev = means3D.device
+    g, k1 = _gaussians(means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, sh, degree)
+    n = len(views)
+    if n == 0:
+        return []
+    if g.P == 0:
+        return [rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                                    cov3D_precomp, v[0], v[1], v[2], v[3], v[4], v[5], sh, degree, v[6], False,
+                                    antialiasing, debug, tile_culling) for v in views]
+    cams, keep = _camera_array(background, views, antialiasing, debug, tile_culling)
+    sizes = [(int(v[4]), int(v[5])) for v in views]
+    colors_out = [torch.empty((3, H, W), dtype=torch.float32, device=dev) for H, W in sizes]
+    invd = [torch.empty((1, H, W), dtype=torch.float32, device=dev) for H, W in sizes] if want_invdepth else None
+    radii = torch.zeros((n, g.P), dtype=torch.int32, device=dev)
+    VP = C.c_void_p * n
+    p_color = VP(*[t.data_ptr() for t in colors_out])
+    p_invd = VP(*[t.data_ptr() for t in invd]) if invd else None
+    p_radii = VP(*[radii[i].data_ptr() for i in range(n)])
+    epi = None
+    if residual is not None:
+        epi = (GslmResidualEpilogue * n)()
+        for i, (spec, (H, W)) in enumerate(zip(residual, sizes)):
+            epi[i] = spec.c_struct(H, W) if spec is not None else GslmResidualEpilogue()
+    nr, nc = (C.c_int32 * n)(), (C.c_int32 * n)()
+    al = _Alloc(dev)
+    _check(L.gslm_forward_batch(C.addressof(g), n, C.addressof(cams), al.cb, None, C.addressof(p_color),
+                                C.addressof(p_invd) if p_invd is not None else None, C.addressof(p_radii),
+                                C.addressof(epi) if epi is not None else None, C.addressof(nr), C.addressof(nc),
+                                _stream()))
+    _after_forward(al)
+    out = []
+    for i in range(n):
+        out.append((NumRendered(nr[i], nc[i]), colors_out[i], radii[i], al.get(0 | (i << 8)), al.get(1 | (i << 8)),
+                    al.get(2 | (i << 8)), invd[i] if invd else None))
+    return out
+
+
+def fp32_peak_probe(mode=0, device=None):
+    """gslm_fp32_peak_probe -> (TFLOP/s, ms): FP32 throughput measured on the current device and stream."""
+    L = lib()
+    dev = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+    scratch = torch.empty(L.gslm_fp32_probe_scratch_bytes(), dtype=torch.uint8, device=dev)
+    tf, ms = C.c_float(0), C.c_float(0)
+    _check(L.gslm_fp32_peak_probe(int(mode), scratch.data_ptr(), C.addressof(tf), C.addressof(ms), _stream()))
+    return float(tf.value), float(ms.value)
 
 
 def rasterize_gaussians_jvp(background, background_grad, means3D, means3D_grad, colors, colors_grad, opacity,

@@ -37,6 +37,9 @@ class GaussianModel:
             setattr(self, n, torch.empty(0))
         self.pretrained_exposures = None
         self.exposure_mapping = {}
+        # bumped by every method that changes parameter VALUES (update_step, load_ply): `.data +=` leaves the
+        # tensors' own version counters untouched, and LinearSolverFunctions' cached linearisation must notice
+        self._param_version = 0
         self.setup_functions()
 
     @classmethod
@@ -54,6 +57,7 @@ class GaussianModel:
                "_exposure": torch.eye(3, 4, device=device)[None].repeat(num_cameras, 1, 1)}
         for n, v in raw.items():
             setattr(m, n, nn.Parameter(v.requires_grad_(requires_grad)) if requires_grad else v)
+        m._param_version += 1
         return m
 
     # ---- checkpoint format (reference :315-404) ----
@@ -143,6 +147,7 @@ class GaussianModel:
         if self._exposure.numel() == 0:
             self._exposure = torch.eye(3, 4, device=device)[None].clone()
         self.active_sh_degree = self.max_sh_degree
+        self._param_version += 1
 
     # ---- forward-AD plumbing (reference :71-139) ----
     @contextmanager
@@ -163,6 +168,13 @@ class GaussianModel:
     def update_step(self, s):
         for n, f in zip(_PARAMS, _STATE_FIELDS):
             getattr(self, n).data += getattr(s, f)
+        self._param_version += 1
+
+    def param_signature(self):
+        """Changes whenever a parameter tensor is replaced, resized, modified in place through autograd-visible ops,
+        or stepped by update_step / load_ply: what a cached linearisation is valid for."""
+        return (self._param_version, int(self.active_sh_degree)) + tuple(
+            (getattr(self, n).data_ptr(), getattr(self, n)._version, tuple(getattr(self, n).shape)) for n in _PARAMS[:6])
 
     # ---- activations (reference :192-224) ----
     @property

@@ -46,10 +46,24 @@ class _ViewCache:
     __slots__ = ("cam", "H", "W", "R", "radii", "geom", "binning", "img", "weight", "mask", "residual", "cam_args")
 
 
+def balanced_view_assignment(costs, world):
+    """Greedy (longest-processing-time-first) assignment of views to ranks on a per-view cost (the
+    instance count R), with at most ceil(V / world) views per rank so that memory and launch counts stay even.
+    Deterministic: ties go to the lower view index / lower rank.  Returns world ascending index lists."""
+    V = len(costs)
+    cap = (V + world - 1) // world
+    load, owned = [0] * world, [[] for _ in range(world)]
+    for i in sorted(range(V), key=lambda i: (-int(costs[i]), i)):
+        r = min((r for r in range(world) if len(owned[r]) < cap), key=lambda r: (load[r], r))
+        owned[r].append(i)
+        load[r] += int(costs[i])
+    return [sorted(o) for o in owned]
+
+
 class LinearSolverFunctions:
 
     def __init__(self, loss_func, gaussians, viewpoint_cams, batch_size=-1, param_mask=None, splat_mask=None,
-                 cached=None, shard_views=True, tile_culling=True):
+                 cached=None, shard_views=True, tile_culling=True, balance_views=True):
         self.loss_func = loss_func
         # exact tile culling in the cached mode's own forward passes (include/gslm_b200.h, GslmCamera::tile_culling):
         # residuals, linearisation cache and every product are bit-identical with and without it
@@ -58,9 +72,11 @@ class LinearSolverFunctions:
         self.all_cams = list(viewpoint_cams)
         d = _dist() if shard_views else None
         self.dist = d
-        # data-parallel axis: views.  rank r owns views r, r + world, ... (round robin keeps per-rank R balanced
-        # for rigs whose neighbouring cameras see similar content)
-        self.viewpoint_cams = self.all_cams[d.get_rank()::d.get_world_size()] if d else self.all_cams
+        # data-parallel axis: views.  Default: rank r owns views r, r + world, ... (round robin); in cached mode the
+        # assignment is re-balanced on the per-view instance counts below (_balance_views)
+        self.view_ids = list(range(d.get_rank(), len(self.all_cams), d.get_world_size())) if d else \
+            list(range(len(self.all_cams)))
+        self.viewpoint_cams = [self.all_cams[i] for i in self.view_ids]
         self.B = len(self.viewpoint_cams)
         self.batch_size = max(self.B, 1) if batch_size < 0 else batch_size
         self.batch_stats = {}
@@ -78,6 +94,38 @@ class LinearSolverFunctions:
         self._views = None
         self._scratch = None
         self._plan = None
+        if d and self.cached and balance_views and len(self.all_cams) > d.get_world_size():
+            self._balance_views(batch_size)
+
+    def _balance_views(self, batch_size):
+        """Views -> ranks by greedy balancing on the per-view instance count R.  Every rank counts its
+        round-robin share (gslm_count_instances: preprocess + culling + scan, no rendering), ONE all_gather makes the
+        full list known everywhere, and the deterministic LPT assignment is computed identically on every rank."""
+        d = self.dist
+        world, rank = d.get_world_size(), d.get_rank()
+        V = len(self.all_cams)
+        pipe, bg = self._kw("pipe"), self._kw("bg")
+        a = self._activated(with_layer=False)
+        e = torch.empty(0, device=a["means3D"].device)
+        views = [(c.world_view_transform, c.full_proj_transform, math.tan(c.FoVx * 0.5), math.tan(c.FoVy * 0.5),
+                  int(c.image_height), int(c.image_width), c.camera_center) for c in self.viewpoint_cams]
+        mine = _C.count_instances(bg, a["means3D"], e, a["opacities"], a["scales"], a["rotations"], 1.0, e, views,
+                                  a["shs"], a["sh_degree"], pipe.antialiasing, tile_culling=self.tile_culling)
+        per = (V + world - 1) // world
+        t = torch.zeros(per, dtype=torch.int64, device=a["means3D"].device)
+        t[:len(mine)] = torch.tensor(mine, dtype=torch.int64)
+        allc = torch.empty(per * world, dtype=torch.int64, device=t.device)
+        d.all_gather_into_tensor(allc, t)
+        allc = allc.view(world, per).cpu()
+        costs = [0] * V
+        for r in range(world):
+            for k, i in enumerate(range(r, V, world)):
+                costs[i] = int(allc[r, k])
+        self.view_costs = costs
+        self.view_ids = balanced_view_assignment(costs, world)[rank]
+        self.viewpoint_cams = [self.all_cams[i] for i in self.view_ids]
+        self.B = len(self.viewpoint_cams)
+        self.batch_size = max(self.B, 1) if batch_size < 0 else batch_size
 
     # ------------------------------------------------------------------ reference API
     def get_initial_solution(self):
@@ -110,8 +158,9 @@ class LinearSolverFunctions:
         return self.loss
 
     def _scalar(self, t):
-        if self.dist and isinstance(t, torch.Tensor):
-            t = t.clone()
+        if self.dist:
+            # a rank that owns no view holds the Python int 0 here: it must still enter the collective
+            t = torch.as_tensor(t, dtype=torch.float32, device=self.gaussians._xyz.device).clone()
             self.dist.all_reduce(t)
         return t
 
@@ -232,60 +281,102 @@ class LinearSolverFunctions:
             act["tangent"] = tuple(torch.empty_like(act[k]) for k in ("shs", "scales", "rotations", "opacities"))
         return act
 
+    def _check_depth_branch(self):
+        """The depth residual block is not implemented by the reference (solver/batch_training_loss.py:88-93 raises);
+        the cached path must not silently drop it."""
+        w = self._kw("depth_l1_weight")
+        it = self._kw("iteration", 0)
+        if w is not None and w(it) > 0 and any(getattr(c, "depth_reliable", False) for c in self.viewpoint_cams):
+            raise NotImplementedError("Ll1depth_pure_per_pixel is not implemented in this version.")
+
+    def _param_signature(self):
+        g = self.gaussians
+        if hasattr(g, "param_signature"):
+            return g.param_signature()
+        return tuple((getattr(g, n).data_ptr(), getattr(g, n)._version) for n in
+                     ("_xyz", "_features_dc", "_features_rest", "_scaling", "_rotation", "_opacity"))
+
     def _gauss_args(self):
         a = self._act
         e = self._empty
         return (a["means3D"], e, a["opacities"], a["scales"], a["rotations"], 1.0, e, a["shs"], a["sh_degree"])
 
+    LINEARIZE_CHUNK = 16   # views per gslm_forward_batch call
+
+    def _targets(self, start, end, like):
+        """gather_targets of the batch [start, end), cached: targets and alpha masks are constants of the object."""
+        if not hasattr(self, "_target_cache"):
+            self._target_cache = {}
+        key = (start, end, tuple(like.shape))
+        if key not in self._target_cache:
+            self._target_cache[key] = gather_targets(self.viewpoint_cams[start:end], like)
+        return self._target_cache[key]
+
     def linearize(self):
-        """Forward-render every local view once; keep per-view caches, residuals and pixel weights."""
+        """Forward-render every local view once; keep per-view caches, residuals and pixel weights.
+        The views go through gslm_forward_batch in chunks of LINEARIZE_CHUNK (one host synchronisation per chunk plus
+        one overlapped read-back per view) and the clamp mask / alpha mask / residual / pixel weight of every view
+        come out of the library's fused epilogue: no per-view torch kernels."""
+        self._check_depth_branch()
         pipe, bg = self._kw("pipe"), self._kw("bg")
         dev = self.gaussians._xyz.device
         self._empty = torch.empty(0, device=dev)
         self._act = a = self._activated()
+        self._lin_signature = self._param_signature()
         self._views = []
         self._plan = None
         self._eval_cache = {}          # loss_value()'s stacked targets are re-gathered after every linearisation
         self._loss_batches = []
-        losses = []
+        batches, specs, view_args = [], [], []
         for start, end in self._batches():
             cams = self.viewpoint_cams[start:end]
             Hm, Wm = max(c.image_height for c in cams), max(c.image_width for c in cams)
-            resid = torch.zeros((len(cams), 3, Hm, Wm), dtype=torch.float32, device=dev)
-            gt, masks = gather_targets(cams, resid)
-            images = resid if self.ssim else None      # ssim mode: `resid` first collects the clamped renders
-            cmask = torch.zeros_like(resid) if self.ssim else None   # d clamp / d colour, fused into the loss kernels
+            uniform = all((c.image_height, c.image_width) == (Hm, Wm) for c in cams)
+            new = torch.empty if uniform else torch.zeros       # padding must read as zero
+            resid = new((len(cams), 3, Hm, Wm), dtype=torch.float32, device=dev)
+            gt, masks = self._targets(start, end, resid)
+            # ssim mode: `resid` collects the clamped renders, cmask = d clamp / d colour (fused into the loss kernels)
+            cmask = new(resid.shape, dtype=torch.float32, device=dev) if self.ssim else None
+            batches.append((cams, resid, gt, masks, cmask))
             for i, cam in enumerate(cams):
                 H, W = int(cam.image_height), int(cam.image_width)
                 vc = _ViewCache()
                 vc.cam, vc.H, vc.W = cam, H, W
                 tfx, tfy = math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5)
-                (vc.R, color, vc.radii, vc.geom, vc.binning, vc.img, _) = _C.rasterize_gaussians(
-                    bg, a["means3D"], self._empty, a["opacities"], a["scales"], a["rotations"], 1.0, self._empty,
-                    cam.world_view_transform, cam.full_proj_transform, tfx, tfy, H, W, a["shs"], a["sh_degree"],
-                    cam.camera_center, False, pipe.antialiasing, pipe.debug, tile_culling=self.tile_culling)
                 vc.cam_args = (bg, cam.world_view_transform, cam.full_proj_transform, tfx, tfy, H, W,
                                cam.camera_center, pipe.antialiasing, pipe.debug)
-                # d clamp(x,0,1)/dx as torch defines it (inclusive bounds) times the alpha mask
-                m = ((color >= 0) & (color <= 1)).to(torch.float32)
+                view_args.append((cam.world_view_transform, cam.full_proj_transform, tfx, tfy, H, W, cam.camera_center))
                 if self.ssim:
-                    images[i, :, :H, :W] = color.clamp(0, 1)     # the alpha mask is applied inside the loss kernels
-                    cmask[i, :, :H, :W] = m
-                elif masks is not None:
-                    m = m * masks[i, :, :H, :W]
-                    resid[i, :, :H, :W] = color.clamp(0, 1) * masks[i, :, :H, :W] - gt[i, :, :H, :W]
+                    # the alpha mask is applied inside the loss kernels
+                    vc.mask, vc.weight = None, None
+                    specs.append(_C.ResidualSpec(image=resid[i, :, :H, :W], mask=cmask[i, :, :H, :W],
+                                                 apply_alpha_mask=False, subtract_gt=False))
                 else:
-                    resid[i, :, :H, :W] = color.clamp(0, 1) - gt[i, :, :H, :W]
-                vc.mask = m
-                vc.weight = 2.0 * m * m      # two aliased residual blocks => multiplicity 2 (batch_training_loss.py:15-17)
+                    # d clamp(x,0,1)/dx as torch defines it (inclusive bounds) times the alpha mask; two aliased
+                    # residual blocks => multiplicity 2 in J^T J (batch_training_loss.py:15-17)
+                    vc.mask = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+                    vc.weight = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+                    specs.append(_C.ResidualSpec(image=resid[i, :, :H, :W], mask=vc.mask, weight=vc.weight,
+                                                 gt=gt[i, :, :H, :W],
+                                                 alpha_mask=masks[i, 0, :H, :W] if masks is not None else None,
+                                                 weight_scale=2.0, apply_alpha_mask=True, subtract_gt=True))
                 self._views.append(vc)
+        for c0 in range(0, len(self._views), self.LINEARIZE_CHUNK):
+            c1 = min(c0 + self.LINEARIZE_CHUNK, len(self._views))
+            outs = _C.forward_batch(bg, a["means3D"], self._empty, a["opacities"], a["scales"], a["rotations"], 1.0,
+                                    self._empty, view_args[c0:c1], a["shs"], a["sh_degree"], pipe.antialiasing,
+                                    pipe.debug, residual=specs[c0:c1], tile_culling=self.tile_culling)
+            for vc, (R, _color, radii, geom, binning, img, _) in zip(self._views[c0:c1], outs):
+                vc.R, vc.radii, vc.geom, vc.binning, vc.img = R, radii, geom, binning, img
+        losses = []
+        for cams, resid, gt, masks, cmask in batches:
             depth_block = torch.zeros((0,), dtype=torch.float32, device=dev)
             sizes = [(c.image_height, c.image_width) for c in cams]
             if self.ssim:
                 lam = self._kw("opt").lambda_dssim
                 al = torch.tensor([math.sqrt((1.0 - lam) / (3 * h * w)) for h, w in sizes], device=dev)
                 be = torch.tensor([math.sqrt(lam / (3 * h * w)) for h, w in sizes], device=dev)
-                lb = _C.LossBatch(images, masks, gt, al, be, tangent_masks=cmask)
+                lb = _C.LossBatch(resid, masks, gt, al, be, tangent_masks=cmask)
                 r1, r2 = lb.blocks(want_lin=True)
                 self._loss_batches.append(lb)
                 losses.append(BatchLossImageState(r1, r2, depth_block, sizes, False))
@@ -321,6 +412,7 @@ class LinearSolverFunctions:
         if not self.cached:
             self.evaluate_loss()
             return self.loss_scalar
+        self._check_depth_branch()
         pipe, bg = self._kw("pipe"), self._kw("bg")
         dev = self.gaussians._xyz.device
         empty = torch.empty(0, device=dev)
@@ -412,7 +504,10 @@ class LinearSolverFunctions:
                                   _flat=out.flat)
 
     def _require_linearized(self):
-        if self._views is None:
+        """The reference's matvec / matvec_T render at the CURRENT parameters on every call
+        (solver/solver_functions.py:75-113); a cached linearisation is therefore only reused while the parameters
+        are the ones it was taken at -- after update_step / load_ply / any in-place change it is rebuilt."""
+        if self._views is None or self._lin_signature != self._param_signature():
             self.linearize()
 
     def _get_plan(self):

@@ -149,6 +149,45 @@ int32_t gslm_render_batch(const GslmGaussians* g, int32_t n_views, const GslmCam
                           void* alloc_ctx, float* const* out_color, float* const* out_invdepth, int32_t* const* radii,
                           int32_t* num_rendered, void* stream);
 
+/* The instance counts (num_rendered) of n_views cameras without rendering them: preprocess + (culling) + scan per view
+ * and ONE host synchronisation for all counts.  What the multi-GPU view assignment balances on ("greedy
+ * balancing on per-view R").  The allocator is asked once for anonymous scratch (which = -1). */
+int32_t gslm_count_instances(const GslmGaussians* g, int32_t n_views, const GslmCamera* cams, GslmAllocFn alloc,
+                             void* alloc_ctx, int32_t* num_rendered, void* stream);
+
+/* What the LM solver derives from each rendered image (gaussian_renderer/batch_render.py:118 clamp(0,1);
+ * solver/batch_training_loss.py:10-17 alpha mask and residual), produced by the forward batch in one pass per view
+ * instead of ~8 torch elementwise kernels.  With m = 1[0 <= colour <= 1] (torch's clamp derivative), am = alpha mask:
+ *   out_image  = clamp(colour, 0, 1) [* am if apply_alpha_mask] [- gt if subtract_gt]   (plane / row strides in floats)
+ *   out_mask   = m [* am if apply_alpha_mask]                                          (plane / row strides in floats)
+ *   out_weight = weight_scale * out_mask^2                                             (contiguous [3,H,W])
+ * Any output pointer may be NULL. */
+typedef struct GslmResidualEpilogue {
+    const float* gt;          /* [3,H,W] with strides gt_plane / gt_row, or NULL                              */
+    const float* alpha_mask;  /* [H,W] with row stride alpha_row, or NULL                                     */
+    float* out_image;
+    float* out_mask;
+    float* out_weight;
+    int64_t gt_plane, gt_row, alpha_row, image_plane, image_row, mask_plane, mask_row;
+    float weight_scale;
+    int32_t apply_alpha_mask, subtract_gt;
+} GslmResidualEpilogue;
+
+/* n_views LINEARISING forward passes (gslm_forward) of the same Gaussians in one call: the twin of gslm_render_batch
+ * for the passes that are differentiated afterwards (LinearSolverFunctions.linearize; the reference renders its views
+ * one by one with a host synchronisation each, rasterizer_impl.cu:325, DGR/diff_gaussian_rasterization/batch_render.py:
+ * 171-213).  Every view is preprocessed and scanned first and all instance counts come back with ONE synchronisation;
+ * then view v is binned and blended while the host waits for the compact count of view v - 1 (two alternating sort
+ * scratches), so the device never idles on a read-back.  The allocator is called with
+ *   which = kind | (view << 8)   for GSLM_BUF_GEOM, GSLM_BUF_IMAGE, GSLM_BUF_BINNING (one each per view), and
+ *   which = GSLM_BUF_BINNING_TEMP | (slot << 8), slot = 0, 1   for the sort scratches (dead when the call returns).
+ * out_color / radii / num_rendered / num_cached: HOST arrays of n_views entries (radii entries must be non-NULL);
+ * out_invdepth and epilogues may be NULL.  Buffers and results are bit-identical to n_views gslm_forward calls. */
+int32_t gslm_forward_batch(const GslmGaussians* g, int32_t n_views, const GslmCamera* cams, GslmAllocFn alloc,
+                           void* alloc_ctx, float* const* out_color, float* const* out_invdepth,
+                           int32_t* const* radii, const GslmResidualEpilogue* epilogues, int32_t* num_rendered,
+                           int32_t* num_cached, void* stream);
+
 /* Replaces _C.rasterize_gaussians_jvp (DGR/rasterize_points.cu:143-298; forwardJvp,
  * DGR/cuda_rasterizer/rasterizer_jvp_impl.h:125-325).  `gt` holds the tangent pointers in
  * the same fields as `g` (NULL => zero tangent; P/sh_degree/M/scale_modifier ignored,
@@ -306,6 +345,14 @@ int32_t gslm_timing_num_stages(void);
 const char* gslm_timing_stage_name(int32_t stage);
 void gslm_timing_enable(int32_t on);
 int32_t gslm_timing_collect(float* ms, int32_t* counts);
+
+/* FP32 peak probe (no reference counterpart): the denominator of the tile kernels' roofline, measured in the run that
+ * quotes it.  mode 0: scalar FFMA on independent chains (the FP32 FLOP peak); 1: packed FFMA2 with three distinct 64-bit
+ * register operands (what the tile sweeps issue); 2: mode 1 + one MUFU.EX2 per 12 FFMA2 (the sweeps' mix).
+ * scratch: gslm_fp32_probe_scratch_bytes() device bytes.  *out_tflops: FMA = 2 flops; best of 3 launches of ~10 ms each,
+ * timed with CUDA events on `stream`; synchronises the stream. */
+size_t gslm_fp32_probe_scratch_bytes(void);
+int32_t gslm_fp32_peak_probe(int32_t mode, void* scratch, float* out_tflops, float* out_ms, void* stream);
 
 /* Introspection for tests (bit-exact binning checks): device pointers INTO the buffers. */
 typedef struct GslmBufferView {

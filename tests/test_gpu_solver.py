@@ -377,3 +377,45 @@ def test_batched_cached_maps_with_mixed_view_sizes():
                                             accumulate_into=sinks)
     ref = F._to_state(views)
     assert h.rel_l2(T.packed().cpu().numpy(), ref.packed().cpu().numpy()) < 1e-5
+
+
+def test_cached_linearisation_follows_the_parameters():
+    """the reference's matvec re-renders at the CURRENT parameters on every call
+    (solver/solver_functions.py:75-113).  After update_step the cached mode must not answer with J at the old
+    parameters: it re-linearises, and the result equals a fresh object's."""
+    from solver.solver_functions import LinearSolverFunctions
+    model, cams, loss_func, pipe, bg = _setup(P=2500)
+    F = LinearSolverFunctions(loss_func, model, cams, batch_size=2)
+    F.evaluate_loss()
+    v = _rand_state(model, 5)
+    before = F.normal_matvec(v).packed().clone()
+    with torch.no_grad():
+        model.update_step(_rand_state(model, 6) * 0.05)
+        stale_views = F._views
+        after = F.normal_matvec(v).packed().clone()
+        assert F._views is not stale_views, "the linearisation was not rebuilt after update_step"
+        fresh = LinearSolverFunctions(loss_func, model, cams, batch_size=2).normal_matvec(v).packed()
+    assert torch.equal(after, fresh)
+    assert h.rel_l2(after.cpu().numpy(), before.cpu().numpy()) > 1e-3      # the parameters really moved
+    # same for J v and J^T u, and for a replaced parameter tensor (load_ply-style)
+    with torch.no_grad():
+        model._opacity = torch.nn.Parameter(model._opacity.detach() * 0.9)
+        jv = F.matvec(v)
+        jv_fresh = LinearSolverFunctions(loss_func, model, cams, batch_size=2).matvec(v)
+    for a, b in zip(jv.batch_losses, jv_fresh.batch_losses):
+        assert torch.equal(a.Ll1_per_pixel, b.Ll1_per_pixel)
+
+
+def test_cached_mode_raises_on_the_depth_branch_like_the_reference():
+    """depth_l1_weight > 0 with a depth_reliable camera raises NotImplementedError in the reference
+    (solver/batch_training_loss.py:88-93) and in the generic mode; the cached mode must not drop the term silently."""
+    from solver.solver_functions import LinearSolverFunctions
+    model, cams, loss_func, pipe, bg = _setup(P=500, V=2)
+    cams[1].depth_reliable = True
+    lf = functools.partial(loss_func.func, **{**loss_func.keywords, "depth_l1_weight": lambda it: 1.0})
+    F = LinearSolverFunctions(lf, model, cams)
+    assert F.cached
+    with pytest.raises(NotImplementedError):
+        F.evaluate_loss()
+    with pytest.raises(NotImplementedError):
+        F.loss_value()
