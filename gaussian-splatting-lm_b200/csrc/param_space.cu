@@ -214,3 +214,45 @@ extern "C" int32_t gslm_activation_vjp(const GslmActivations* a, const GslmActVe
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
 }
+
+// ---- densification bookkeeping (train_jvp.py:311-316, scene/gaussian_model.py:561-563) in one pass ----
+//   max_radii2D[i]        = max(max_radii2D[i], radii[i])                    for visible i (radii[i] > 0)
+//   xyz_gradient_accum[i] += || dL_dmeans2D[i, :2] ||                         (the viewspace gradient of the batch)
+//   denom[i]              += 1
+// replacing three boolean-mask gathers / scatters and a norm over [P,3] in torch.
+namespace gslm {
+namespace {
+__global__ void __launch_bounds__(256) k_densification_stats(int P, const int32_t* __restrict__ radii,
+                                                             const float* __restrict__ viewspace_grad,
+                                                             float* __restrict__ max_radii2D,
+                                                             float* __restrict__ xyz_gradient_accum,
+                                                             float* __restrict__ denom)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P; i += gridDim.x * blockDim.x) {
+        const int r = radii[i];
+        if (r <= 0) continue;
+        if (max_radii2D) max_radii2D[i] = fmaxf(max_radii2D[i], (float)r);
+        if (viewspace_grad) {
+            const float gx = viewspace_grad[3 * (size_t)i], gy = viewspace_grad[3 * (size_t)i + 1];
+            xyz_gradient_accum[i] += sqrtf(__fadd_rn(__fmul_rn(gx, gx), __fmul_rn(gy, gy)));
+            denom[i] += 1.f;
+        }
+    }
+}
+}  // namespace
+}  // namespace gslm
+
+extern "C" int32_t gslm_densification_stats(int32_t P, const int32_t* radii, const float* viewspace_grad,
+                                            float* max_radii2D, float* xyz_gradient_accum, float* denom, void* stream)
+{
+    if (P < 0 || (P > 0 && (!radii || (viewspace_grad && (!xyz_gradient_accum || !denom))))) {
+        set_error("gslm_densification_stats: bad argument");
+        return 1;
+    }
+    if (P == 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int grid = (int)min((size_t)(P + 255) / 256, (size_t)148 * 16);
+    k_densification_stats<<<grid, 256, 0, s>>>(P, radii, viewspace_grad, max_radii2D, xyz_gradient_accum, denom);
+    GSLM_CUDA_OK(cudaGetLastError());
+    return 0;
+}

@@ -107,6 +107,7 @@ EXPORTS = ("gslm_last_error", "gslm_abi_version", "gslm_sizeof", "gslm_camera_of
            "gslm_jtjv_batch_scratch_bytes", "gslm_jtjv_batch", "gslm_jvp_batch_scratch_bytes", "gslm_jvp_batch",
            "gslm_backward_batch_scratch_bytes", "gslm_backward_batch", "gslm_loss_lin_bytes", "gslm_loss_blocks",
            "gslm_loss_blocks_jvp", "gslm_loss_blocks_vjp", "gslm_activation_jvp", "gslm_activation_vjp",
+           "gslm_densification_stats",
            "gslm_buffer_view", "gslm_tangent_records", "gslm_timing_num_stages",
            "gslm_timing_stage_name", "gslm_timing_enable", "gslm_timing_collect")
 
@@ -157,6 +158,7 @@ def lib():
         L.gslm_loss_blocks_vjp.argtypes = [vp, vp, vp, vp, vp, C.c_int32, vp]
         L.gslm_activation_jvp.argtypes = [vp, vp, vp, vp]
         L.gslm_activation_vjp.argtypes = [vp, vp, vp, vp, vp, vp]
+        L.gslm_densification_stats.argtypes = [C.c_int32, vp, vp, vp, vp, vp, vp]
         L.gslm_buffer_view.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int64, vp, vp, vp, vp, vp]
         L.gslm_tangent_records.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.gslm_timing_stage_name.restype = C.c_char_p
@@ -892,6 +894,20 @@ class Activations:
             d = (C.c_float * 6)(*[float(x) for x in damp6])
             _check(lib().gslm_activation_vjp(C.addressof(self.c), C.addressof(av), C.addressof(vv), d,
                                              C.addressof(ov), _stream()))
+
+
+def densification_stats(radii, viewspace_grad, max_radii2D, xyz_gradient_accum, denom):
+    """gslm_densification_stats: the bookkeeping of train_jvp.py:311-316 in one pass (in place on the three
+    accumulators).  radii: int32 [P]; viewspace_grad: [P,3] float32 or None."""
+    P = int(radii.shape[0])
+    if radii.dtype != torch.int32:
+        radii = radii.to(torch.int32)
+    vg = _f32(viewspace_grad)
+    for t in (max_radii2D, xyz_gradient_accum, denom):
+        if t is not None and not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.numel() == P):
+            raise RuntimeError("gslm_b200: densification accumulators must be contiguous float32 CUDA tensors of P elements")
+    _check(lib().gslm_densification_stats(P, _ptr(radii.contiguous()), _ptr(vg), _ptr(max_radii2D),
+                                          _ptr(xyz_gradient_accum), _ptr(denom), _stream()))
 
 
 def timing_enable(on=True):

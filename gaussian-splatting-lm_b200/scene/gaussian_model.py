@@ -176,6 +176,37 @@ class GaussianModel:
         return (self._param_version, int(self.active_sh_degree)) + tuple(
             (getattr(self, n).data_ptr(), getattr(self, n)._version, tuple(getattr(self, n).shape)) for n in _PARAMS[:6])
 
+    # ---- densification bookkeeping (reference scene/gaussian_model.py:561-563, train_jvp.py:311-316) ----
+    def init_densification_stats(self):
+        """max_radii2D [P], xyz_gradient_accum [P,1], denom [P,1] as training_setup creates them (reference :168-170)."""
+        P, dev = self._xyz.shape[0], self._xyz.device
+        self.max_radii2D = torch.zeros(P, device=dev)
+        self.xyz_gradient_accum = torch.zeros((P, 1), device=dev)
+        self.denom = torch.zeros((P, 1), device=dev)
+
+    def add_densification_stats(self, viewspace_point_tensor, update_filter):
+        """The reference's method: accumulates ||viewspace grad[:, :2]|| and the visit count on `update_filter`."""
+        grad = viewspace_point_tensor.grad if getattr(viewspace_point_tensor, "grad", None) is not None \
+            else viewspace_point_tensor
+        self.xyz_gradient_accum[update_filter] += torch.norm(grad[update_filter, :2], dim=-1, keepdim=True)
+        self.denom[update_filter] += 1
+
+    def update_densification_stats(self, radii, viewspace_grad):
+        """train_jvp.py:313-316 in ONE kernel on CUDA (gslm_densification_stats): max_radii2D, xyz_gradient_accum and
+        denom updated on the visible set radii > 0.  radii: [P] (max over the batch's views); viewspace_grad: [P,3]
+        (the batch's dL_dmeans2D, e.g. LinearSolverFunctions.viewspace_grad) or a tensor carrying it in .grad."""
+        if not hasattr(self, "max_radii2D") or self.max_radii2D.shape[0] != self._xyz.shape[0]:
+            self.init_densification_stats()
+        g = viewspace_grad.grad if getattr(viewspace_grad, "grad", None) is not None else viewspace_grad
+        if radii.is_cuda:
+            from diff_gaussian_rasterization import _C
+            _C.densification_stats(radii, g.detach(), self.max_radii2D, self.xyz_gradient_accum.view(-1),
+                                   self.denom.view(-1))
+            return
+        vis = radii > 0
+        self.max_radii2D[vis] = torch.max(self.max_radii2D[vis], radii[vis].to(self.max_radii2D.dtype))
+        self.add_densification_stats(g, vis)
+
     # ---- activations (reference :192-224) ----
     @property
     def get_scaling(self):

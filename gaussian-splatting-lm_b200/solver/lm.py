@@ -9,10 +9,10 @@ Gauss-Newton product: linearise, solve the damped normal equations with CG, back
 CGLS and CG on the normal equations generate the same iterates in exact arithmetic (Bjorck 1996, 7.4); the
 reference's CGLS remains available unchanged in solver.conjugate_gradient.cgls_damped.
 
-Device-resident: every scalar of the CG recurrence (alpha, beta, <r, r>, p^T A p) is a 0-dim CUDA tensor, p^T J^T J p
-comes out of the fused tile kernel for free (gslm_jtjv's out_vJJv), convergence is handled by masking the step
-instead of branching -- so a CG solve issues NO host synchronisation (the reference's dot() does one .item() per
-inner product, solver/solver_functions.py:125-130) and could be captured in a CUDA graph.
+Device-resident: every scalar of the CG recurrence (alpha, beta, <r, r>, p^T A p) is a 0-dim CUDA tensor,
+convergence is handled by masking the step instead of branching -- so a CG solve issues NO host synchronisation
+(the reference's dot() does one .item() per inner product, solver/solver_functions.py:125-130) and the iteration is
+captured in a CUDA graph (cg_normal_equations(graph=True)).
 """
 import torch
 
@@ -26,12 +26,22 @@ def _damp_mul(v, damp):
     return (v * damp).packed()
 
 
-def cg_normal_equations(F, damp=None, max_iter=2, tol=1e-10, rhs=None, x0=None, callback=None):
+def cg_normal_equations(F, damp=None, max_iter=2, tol=1e-10, rhs=None, x0=None, callback=None, graph=False):
     """Solve (J^T J + D) s = J^T(-r) at F's current linearisation with `max_iter` CG iterations.
 
     F: LinearSolverFunctions in cached mode with evaluate_loss() already called (the linearisation).
     Returns (s, info) with info = {"residual_norms": 1-D device tensor [max_iter + 1]} -- nothing is read back.
-    A converged solve (||r|| < tol ||r0||) keeps iterating with zero steps, so the launch sequence is static."""
+    A converged solve (||r|| < tol ||r0||) keeps iterating with zero steps, so the launch sequence is static.
+
+    p^T A p is taken as dot(p, A p) on the (masked, damped) product: a fixed-order reduction, so the CG step sizes
+    are bit-reproducible run to run.  (The fused tile kernel can also return v^T J^T W J v through out_vJJv, but it
+    accumulates that scalar with one atomicAdd per tile -- order-dependent in the last bits; it stays available as a
+    diagnostic, F.normal_matvec(return_quad=True).)
+
+    graph=True: iteration 1 runs eagerly (it doubles as the warm-up), iteration 2 is captured into a CUDA graph
+    (every launch of the iteration: activation JVP, tangent preprocess / fused tile kernel / adjoint per chunk of
+    views, the NCCL allreduce, activation VJP, the CG vector updates) and iterations 2..max_iter are replays: one
+    cudaGraphLaunch each instead of ~30 launches through Python and ctypes.  Same arithmetic, same bits."""
     if rhs is None:
         rhs = F.matvec_T(-1 * F.loss)
     b = rhs.packed()
@@ -41,37 +51,47 @@ def cg_normal_equations(F, damp=None, max_iter=2, tol=1e-10, rhs=None, x0=None, 
     if x0 is None:
         r = b.clone()
     else:
-        Ax, _ = F.normal_matvec(wrap(x), damp=damp, return_quad=True)
-        r = b - Ax.packed()
+        r = b - F.normal_matvec(wrap(x), damp=damp).packed()
     p = r.clone()
     rs = torch.dot(r, r)
     rs0 = rs.clone()
-    norms = [rs.sqrt()]
+    norms = torch.zeros(max_iter + 1, dtype=torch.float32, device=b.device)
+    norms[0] = rs.sqrt()
     tiny = torch.finfo(torch.float32).tiny
-    for k in range(max_iter):
-        pv = wrap(p)
-        Ap, quad = F.normal_matvec(pv, damp=damp, return_quad=True)      # one fused sweep over all views
-        Apf = Ap.packed()
-        # p^T A p = p^T J^T W J p (from the tile kernel) + p^T D p; the masked groups of Ap are zeroed by the state
-        # constructor, so use the dot product with the masked Ap when a mask is active
-        if F.param_mask is not None or F.splat_mask is not None or quad is None:
-            pAp = torch.dot(p, Apf)
-        else:
-            pAp = quad.reshape(())
-            if damp is not None:
-                pAp = pAp + pv.dot_tensor(pv, damp)
+    pv = wrap(p)            # views of the static buffer p
+
+    def iteration():
+        """One CG iteration, in place on the static buffers x, r, p, rs."""
+        Apf = F.normal_matvec(pv, damp=damp).packed()                    # one fused sweep over all views
+        pAp = torch.dot(p, Apf)
         live = (rs > (tol * tol) * rs0) & (pAp > tiny)
         alpha = torch.where(live, rs / pAp.clamp_min(tiny), torch.zeros_like(rs))
         x.add_(alpha * p)
         r.sub_(alpha * Apf)
         rs_new = torch.dot(r, r)
         beta = torch.where(live, rs_new / rs.clamp_min(tiny), torch.zeros_like(rs))
-        p = r + beta * p
-        rs = rs_new
-        norms.append(rs.sqrt())
+        p.mul_(beta).add_(r)
+        rs.copy_(rs_new)
+
+    g = None
+    for k in range(max_iter):
+        if graph and k == 1 and max_iter > 2 and callback is None:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                iteration()
+        if g is not None:
+            g.replay()
+        else:
+            iteration()
+        norms[k + 1] = rs.sqrt()
         if callback is not None:
             callback(wrap(x), wrap(r), k + 1)
-    return wrap(x), {"residual_norms": torch.stack(norms)}
+    info = {"residual_norms": norms, "graphed": g is not None}
+    if g is not None:
+        # the graph's private pool owns the buffers of the captured iteration; results live in x / r / p (ours)
+        torch.cuda.current_stream().synchronize()
+        del g
+    return wrap(x), info
 
 
 def line_search(gaussians, s, val_loss, alpha0=2.0, halvings=6):

@@ -571,9 +571,29 @@ class LinearSolverFunctions:
             out.append(BatchLossImageState(t1, t2, depth_block, [(c.image_height, c.image_width) for c in cams], False))
         return MultiBatchLossImageState(out)
 
+    # densification bookkeeping (train_jvp.py:311-316): set track_viewspace = True and every cached matvec_T also
+    # leaves the batch's viewspace gradient dL_dmeans2D [P,3] in self.viewspace_grad (summed over all views and
+    # ranks); max_radii() gives the per-Gaussian maximum screen radius over all views.  Feed both to
+    # GaussianModel.update_densification_stats.
+    track_viewspace = False
+    viewspace_grad = None
+
+    def max_radii(self):
+        self._require_linearized()
+        P = self._act["means3D"].shape[0]
+        r = torch.zeros(P, dtype=torch.int32, device=self._act["means3D"].device)
+        for vc in self._views:
+            torch.maximum(r, vc.radii, out=r)
+        if self.dist:
+            self.dist.all_reduce(r, op=self.dist.ReduceOp.MAX)
+        return r
+
     def _matvec_T_cached(self, vs):
         self._require_linearized()
         flat, views, sinks = self._act_accumulators()
+        if self.track_viewspace:
+            self.viewspace_grad = torch.zeros((self._act["means3D"].shape[0], 3), dtype=torch.float32, device=flat.device)
+            sinks = (self.viewspace_grad,) + sinks[1:]
         cots = []
         for idx, _ in enumerate(self._batches()):
             u = vs.batch_losses[idx]
@@ -584,6 +604,8 @@ class LinearSolverFunctions:
         self._pull_back(cots, sinks)
         if self.dist:
             self.dist.all_reduce(flat)
+            if self.track_viewspace:
+                self.dist.all_reduce(self.viewspace_grad)
         return self._to_state(views)
 
     def _normal_matvec_ssim(self, gargs, targs, sinks, quad):

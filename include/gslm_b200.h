@@ -337,6 +337,14 @@ int32_t gslm_activation_jvp(const GslmActivations* act, const GslmRawVector* v, 
 int32_t gslm_activation_vjp(const GslmActivations* act, const GslmActVector* g, const GslmRawVector* v,
                             const float* damp6, const GslmRawVector* out, void* stream);
 
+/* Densification bookkeeping of the training driver (train_jvp.py:311-316: max_radii2D[vis] = max(max_radii2D[vis],
+ * radii[vis]); GaussianModel.add_densification_stats, scene/gaussian_model.py:561-563: xyz_gradient_accum[vis] +=
+ * ||viewspace_grad[vis, :2]||, denom[vis] += 1) with vis = radii > 0, in one pass.  radii: int32 [P] (max over the
+ * views of the batch), viewspace_grad: [P,3] = dL_dmeans2D summed over the batch (NULL: only the radii are tracked),
+ * max_radii2D / xyz_gradient_accum / denom: float [P] accumulators (max_radii2D may be NULL). */
+int32_t gslm_densification_stats(int32_t P, const int32_t* radii, const float* viewspace_grad, float* max_radii2D,
+                                 float* xyz_gradient_accum, float* denom, void* stream);
+
 /* ---- optional per-stage device timing (no reference counterpart; bench.py's live roofline numbers) ----
  * When enabled, each stage brackets its kernels with a cudaEvent pair on the launching stream.
  * gslm_timing_collect synchronises the device and returns, per stage, the summed elapsed milliseconds and the

@@ -68,5 +68,50 @@ def full(src, dst, cmd):
                     f.write(f"  {m:86s}{r[ix[m]]:>16s} {units[ix[m]]}\n")
 
 
+# flops per lane of one executed FP32 SASS instruction (FMA = 2; packed ".F32x2" forms do two lanes' worth per thread)
+FLOPS = {"FFMA2": 4, "FMUL2": 2, "FADD2": 2, "FFMA": 2, "FMUL": 1, "FADD": 1, "MUFU": 1, "FMNMX": 1}
+
+
+def sass(src, dst, cmd):
+    """Per-opcode EXECUTED instruction counts of the (first) kernel in an ncu report that was captured with
+    --import-source on: the source page's per-SASS-line "# Instructions Executed" (warp level) and "# Thread
+    Instructions Executed" columns, summed by opcode; the executed FP32 flop count follows from FLOPS above."""
+    raw = subprocess.run(["ncu", "-i", src, "--page", "source", "--csv", "--print-source", "sass"],
+                         capture_output=True, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    h = next(i for i, r in enumerate(rows) if "Source" in r and any("Instructions Executed" in c for c in r))
+    hdr = rows[h]
+    i_src = hdr.index("Source")
+    i_warp = next(j for j, c in enumerate(hdr) if c.strip() == "# Instructions Executed" or c.strip() == "Instructions Executed")
+    i_thr = next((j for j, c in enumerate(hdr) if "Thread Instructions Executed" in c), None)
+    agg = collections.defaultdict(lambda: [0, 0])
+    for r in rows[h + 1:]:
+        if len(r) <= max(i_src, i_warp):
+            continue
+        toks = r[i_src].replace("@", " @").split()
+        toks = [t for t in toks if not t.startswith("@") and not t.startswith("!")]
+        if not toks:
+            continue
+        op = toks[0].split(".")[0].rstrip(";")
+        try:
+            w = int(float(r[i_warp].replace(",", "") or 0))
+            t = int(float(r[i_thr].replace(",", "") or 0)) if i_thr is not None else 32 * w
+        except ValueError:
+            continue
+        agg[op][0] += w
+        agg[op][1] += t
+    tot_w = sum(v[0] for v in agg.values())
+    flops = sum(FLOPS.get(op, 0) * v[1] for op, v in agg.items())
+    with open(dst, "w") as f:
+        f.write(f"# command (under gpurun, 1x B200): {cmd}\n")
+        f.write("# executed SASS instructions of one captured launch by opcode (ncu source page); flops = thread-level "
+                "count x flops per lane (FFMA2 4, FMUL2/FADD2 2, FFMA 2, FMUL/FADD/MUFU/FMNMX 1)\n")
+        f.write(f"{'opcode':12s}{'warp_instr':>16s}{'share%':>8s}{'thread_instr':>18s}{'flops':>18s}\n")
+        for op, v in sorted(agg.items(), key=lambda kv: -kv[1][0]):
+            f.write(f"{op:12s}{v[0]:16d}{100.0 * v[0] / max(tot_w, 1):8.2f}{v[1]:18d}{FLOPS.get(op, 0) * v[1]:18d}\n")
+        f.write(f"{'TOTAL':12s}{tot_w:16d}{100.0:8.2f}{sum(v[1] for v in agg.values()):18d}{flops:18d}\n")
+    print(f"executed_flops_per_launch = {flops}")
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](*sys.argv[2:5])
+    {"launches": launches, "full": full, "sass": sass}[sys.argv[1]](*sys.argv[2:5])

@@ -156,7 +156,7 @@ def test_cg_on_fused_normal_matvec_and_cgls_agree(capsys):
 
 @pytest.mark.parametrize("masked", [True, False])
 def test_device_resident_cg_matches_host_cg(masked):
-    """solver.lm.cg_normal_equations (all scalars on the device, p^T A p from the tile kernel) == the reference-style
+    """solver.lm.cg_normal_equations (all scalars on the device, p^T A p by a fixed-order dot) == the reference-style
     conjugate_gradient driven through Python floats, after the same number of iterations (rel 1e-4), and it never
     synchronises: the residual norms come back as one device tensor."""
     from solver.conjugate_gradient import conjugate_gradient
@@ -181,6 +181,26 @@ def test_device_resident_cg_matches_host_cg(masked):
     # a converged solve keeps a static launch sequence: with a huge tolerance every step is masked to zero
     s0, _ = cg_normal_equations(F, damp=D, max_iter=2, tol=10.0)
     assert float(s0.packed().abs().sum()) == 0.0
+
+
+def test_cuda_graphed_cg_iteration_is_bit_identical():
+    """cg_normal_equations(graph=True): iteration 1 eager, iteration 2 captured, 2..n replayed -- the same bits as the
+    eager loop (the CG iteration captured in a CUDA graph), in both residual modes."""
+    from solver.gaussian_model_state import GaussianModelDampMatrix
+    from solver.lm import cg_normal_equations
+    from solver.solver_functions import LinearSolverFunctions
+    model, cams, loss_func, pipe, bg = _setup(P=2000)
+    D = GaussianModelDampMatrix(5e2, 5e-2, 5e-2, 5e-2, 5e-2, 5e-2, 1e1)
+    F = LinearSolverFunctions(loss_func, model, cams, batch_size=2)
+    F.evaluate_loss()
+    s_e, info_e = cg_normal_equations(F, damp=D, max_iter=5, tol=0.0)
+    s_g, info_g = cg_normal_equations(F, damp=D, max_iter=5, tol=0.0, graph=True)
+    assert info_g["graphed"] and not info_e["graphed"]
+    assert torch.equal(s_e.packed(), s_g.packed())
+    assert torch.equal(info_e["residual_norms"], info_g["residual_norms"])
+    # and the solver object is still usable eagerly afterwards
+    s_2, _ = cg_normal_equations(F, damp=D, max_iter=5, tol=0.0)
+    assert torch.equal(s_e.packed(), s_2.packed())
 
 
 def test_lm_step_reduces_validation_loss():
@@ -419,3 +439,43 @@ def test_cached_mode_raises_on_the_depth_branch_like_the_reference():
         F.evaluate_loss()
     with pytest.raises(NotImplementedError):
         F.loss_value()
+
+
+def test_densification_bookkeeping_matches_the_reference_lines():
+    """SURVEY 8 f4 / train_jvp.py:311-316 + scene/gaussian_model.py:561-563: max_radii2D, xyz_gradient_accum and denom
+    from ONE kernel (gslm_densification_stats) fed by the cached adjoint's dL_dmeans2D == the reference's torch lines
+    applied to what autograd leaves in viewspace_points.grad on the generic path."""
+    from gaussian_renderer.batch_render import batch_render
+    from solver.solver_functions import LinearSolverFunctions
+    model, cams, loss_func, pipe, bg = _setup(P=3000)
+    F = LinearSolverFunctions(loss_func, model, cams, batch_size=4)
+    F.track_viewspace = True
+    F.evaluate_loss()
+    F.matvec_T(F.loss)                                   # gradient of 0.5 ||r||^2: what a first-order step would use
+    radii = F.max_radii()
+    model.init_densification_stats()
+    model.max_radii2D[::3] = 7.0                          # pre-existing state must be max-ed / added, not overwritten
+    model.xyz_gradient_accum[::5] = 0.25
+    ref_max, ref_acc, ref_den = model.max_radii2D.clone(), model.xyz_gradient_accum.clone(), model.denom.clone()
+    model.update_densification_stats(radii, F.viewspace_grad)
+    # the reference's lines on the autograd path (batch_render's viewspace_points.grad)
+    model.zero_grad()
+    pkg = batch_render(cams, model, pipe, bg)
+    gt = torch.stack([c.original_image for c in cams])
+    img = pkg["render"]
+    masks = torch.zeros_like(img[:, :1])
+    for i, c in enumerate(cams):
+        masks[i] = c.alpha_mask if c.alpha_mask is not None else 0.0     # batch quirk: mask-less views of a masked batch are zeroed
+    r = img * masks - gt
+    (2.0 * 0.5 * (r * r).sum()).backward()               # two aliased residual blocks
+    vs_grad = pkg["viewspace_points"].grad
+    vis = pkg["visibility_filter"].view(-1)
+    assert torch.equal((radii > 0).nonzero().view(-1), vis)
+    assert h.rel_l2(F.viewspace_grad.cpu().numpy(), vs_grad.cpu().numpy()) < 1e-3
+    rr = pkg["max_radii"].to(ref_max.dtype)
+    ref_max[vis] = torch.max(ref_max[vis], rr[vis])
+    ref_acc[vis] += torch.norm(vs_grad[vis, :2], dim=-1, keepdim=True)
+    ref_den[vis] += 1
+    assert torch.equal(model.max_radii2D, ref_max.view(-1))
+    assert torch.equal(model.denom, ref_den)
+    assert h.rel_l2(model.xyz_gradient_accum.cpu().numpy(), ref_acc.cpu().numpy()) < 1e-3

@@ -33,6 +33,10 @@ def C():
 CASES = [  # (config, view, sh degree, antialiasing, P override)
     ("A", 0, 3, False, None), ("A", 2, 1, True, None), ("B", 5, 3, False, None), ("B", 11, 0, True, None),
     ("C", 17, 3, False, None),      # full headline size: 1M Gaussians, 1920x1080, R ~ 20M
+    # config D-like: ring camera 7 of 8 sits INSIDE the cloud (eye = (2.8, -2.8, 0.9), cube
+    # [-3, 3]^3 + far shell): near-plane culling at z <= 0.2 (auxiliary.h:194-219), Gaussians behind and around the
+    # camera, screen-filling splats next to it, 1600x1060
+    ("D", 7, 3, False, 300_000), ("D", 7, 1, True, 120_000),
 ]
 
 
