@@ -259,6 +259,11 @@ class LinearSolverFunctions:
             host_flat[lo:hi].copy_(flat[lo:hi], non_blocking=True)
         return 4 * max(hi - lo, 0)
 
+    def host_pipeline(self, depth=2):
+        """Double-buffered host staging for a stream of INDEPENDENT products (block of probe vectors / right-hand
+        sides): see HostPipeline."""
+        return HostPipeline(self, depth)
+
     # ------------------------------------------------------------------ cached mode
     def _kw(self, name, default=None):
         return self.loss_func.keywords.get(name, default)
@@ -644,3 +649,90 @@ class LinearSolverFunctions:
                 self.dist.all_reduce(quad)
         out = self._to_state(views, v, damp)
         return (out, quad) if return_quad else out
+
+
+class HostPipeline:
+    """Streams host-resident parameter-space vectors through F.normal_matvec with the PCIe copies off the critical
+    path: the host->device copy of vector k + 1 (copy-in stream) and the device->host copy of result k - 1 (copy-out
+    stream) overlap the kernels of product k (the caller's stream).  Every product still pays its own H2D and D2H --
+    they are just not serialised with the compute, as bench.py's strictly sequential leg is (`e2e.serial`).
+    Valid for INDEPENDENT products (a block of probe vectors or right-hand sides); a CG whose vectors live on the host
+    cannot overlap (v_{k+1} depends on result k) -- keep those vectors on the device (solver/lm.py).
+
+    Multi-GPU: parameter-space vectors are replicated, so every rank moves only 1/N of each vector over its own PCIe
+    link; one all_gather over NVLink (on a dedicated process group, so it does not queue behind the products'
+    allreduce) completes the input, and each rank returns its 1/N slice of the result.
+
+        pipe = F.host_pipeline()
+        for v_host, out_host in work:        # pinned float32 [n] tensors
+            pipe.submit(v_host, out_host)
+        pipe.flush()                          # all results have landed in their out_host buffers
+    """
+
+    def __init__(self, F, depth=2):
+        self.F = F
+        self.depth = max(int(depth), 1)
+        dev = F.gaussians._xyz.device
+        self.dev = dev
+        self.s_in, self.s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        self.states = [GaussianModelState.from_gaussians(F.gaussians) for _ in range(self.depth)]
+        self.n = self.states[0].packed().numel()
+        d = F.dist
+        self.world, self.rank = (d.get_world_size(), d.get_rank()) if d else (1, 0)
+        self.per = (self.n + self.world - 1) // self.world
+        self.group = d.new_group(backend="nccl") if (d and dev.type == "cuda") else None
+        self.stage = [torch.empty(self.per * self.world, dtype=torch.float32, device=dev) for _ in range(self.depth)] \
+            if self.world > 1 else None
+        self.ev_in = [torch.cuda.Event() for _ in range(self.depth)]
+        self.ev_free = [None] * self.depth          # compute of the product that last read slot i has finished
+        self.ev_out = []                             # pending result copies
+        self.k = 0
+        self.bytes_in = self.bytes_out = 0
+
+    def submit(self, host_in, host_out):
+        F, slot = self.F, self.k % self.depth
+        self.k += 1
+        cur = torch.cuda.current_stream(self.dev)
+        flat = self.states[slot].packed()
+        lo, hi = self.rank * self.per, min((self.rank + 1) * self.per, self.n)
+        with torch.cuda.stream(self.s_in):
+            if self.ev_free[slot] is not None:
+                self.s_in.wait_event(self.ev_free[slot])
+            if self.world == 1:
+                flat.copy_(host_in, non_blocking=True)
+            else:
+                st = self.stage[slot]
+                mine = st[self.rank * self.per:(self.rank + 1) * self.per]
+                if hi > lo:
+                    mine[:hi - lo].copy_(host_in[lo:hi], non_blocking=True)
+                F.dist.all_gather_into_tensor(st, mine, group=self.group)
+                flat.copy_(st[:self.n])
+            self.ev_in[slot].record(self.s_in)
+        self.bytes_in = 4 * max(hi - lo, 0)
+        cur.wait_event(self.ev_in[slot])
+        out = F.normal_matvec(self.states[slot])
+        done = torch.cuda.Event()
+        done.record(cur)
+        self.ev_free[slot] = done
+        res = out.packed()
+        with torch.cuda.stream(self.s_out):
+            self.s_out.wait_event(done)
+            if hi > lo:
+                host_out[lo:hi].copy_(res[lo:hi], non_blocking=True)
+            res.record_stream(self.s_out)
+            e = torch.cuda.Event()
+            e.record(self.s_out)
+        self.ev_out.append(e)
+        self.ev_out = self.ev_out[-2 * self.depth:]
+        self.bytes_out = 4 * max(hi - lo, 0)
+
+    def flush(self):
+        """Make the caller's stream wait for every pending copy (so CUDA events on it bracket the whole pipeline) and
+        block the host until the results are in host memory."""
+        cur = torch.cuda.current_stream(self.dev)
+        for e in self.ev_out:
+            cur.wait_event(e)
+        cur.wait_stream(self.s_in)
+        for e in self.ev_out:
+            e.synchronize()
+        self.ev_out = []
