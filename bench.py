@@ -181,7 +181,9 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        # a mismatched collective must fail in two minutes, not hold the box for NCCL's default ten
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
     _C.lib()
 
     g, cams_np = ss.make_config(a.config, sh_degree=a.sh_degree, views=a.views or None, P=a.points or None)
@@ -330,8 +332,10 @@ def main():
     ms_e2e = timed_pipeline(a.steps)
     moved = [pipe_.bytes_in, pipe_.bytes_out]
     # the pipelined results are the device-resident ones, bit for bit
-    e2e_equal = bool(torch.equal(out_hosts[(counter[0] - 1) & 1][:16].cuda(), F.normal_matvec(v).packed()[:16])) \
-        if rank == 0 else None
+    ref_out = F.normal_matvec(v).packed()            # every rank (the product ends in a collective)
+    lo_ = rank * ((n_flat + world - 1) // world)
+    e2e_equal = bool(torch.equal(out_hosts[(counter[0] - 1) & 1][lo_:lo_ + 16].to(dev), ref_out[lo_:lo_ + 16]))
+    del ref_out
     if sampler:
         sampler.stop_flag = True
 
