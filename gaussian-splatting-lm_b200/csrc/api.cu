@@ -86,6 +86,54 @@ static int launch_residual_epilogue(const float* color, int W, int H, const Gslm
     return 0;
 }
 
+static int clear_sinks(const GslmGrads& acc, int P, int M, cudaStream_t s) {
+    const size_t n = (size_t)P;
+    struct { float* p; size_t count; } sinks[8] = {
+        {acc.dL_dmeans2D, 3 * n}, {acc.dL_dcolors, 3 * n}, {acc.dL_dopacity, n}, {acc.dL_dmeans3D, 3 * n},
+        {acc.dL_dcov3D, 6 * n}, {acc.dL_dsh, 3 * n * (size_t)M}, {acc.dL_dscales, 3 * n}, {acc.dL_drotations, 4 * n}};
+    for (auto& k : sinks)
+        if (k.p && k.count) GSLM_CUDA_OK(cudaMemsetAsync(k.p, 0, k.count * sizeof(float), s));
+    return 0;
+}
+
+// The per-Gaussian adjoint of one chunk of views.  overwrite: the first chunk of an overwrite-mode product zero-fills
+// inside the kernel.  On the LAST chunk the launch may be cut into n_slices Gaussian ranges with a host callback after
+// each (the caller starts the collective / the activation VJP of that slice while the next one is produced).
+// the callbacks a product with NO local views owes its caller (same slice boundaries as adjoint_chunk: a rank without
+// views must still enter the same sequence of collectives as the others)
+static void empty_product_callbacks(int P, int n_slices, GslmSliceFn on_slice, void* slice_ctx) {
+    if (!on_slice) return;
+    const int nranges = (P + ACT_RANGE - 1) / ACT_RANGE;
+    if (n_slices <= 1) { on_slice(slice_ctx, 0, 0, P); return; }
+    if (n_slices > nranges) n_slices = nranges;
+    for (int k = 0; k < n_slices; k++) {
+        const int lo = (int)((int64_t)nranges * k / n_slices), hi = (int)((int64_t)nranges * (k + 1) / n_slices);
+        const int64_t g_hi = (int64_t)hi * ACT_RANGE;
+        on_slice(slice_ctx, k, lo * ACT_RANGE, (int32_t)(g_hi < P ? g_hi : P));
+    }
+}
+
+static int adjoint_chunk(const GslmGaussians& g, int n, const GslmCamera* cams, const int32_t* const* radii,
+                         const GeomView* gv, const float4* const* inst, const GslmGrads& acc, bool overwrite, bool last,
+                         int n_slices, GslmSliceFn on_slice, void* slice_ctx, cudaStream_t s) {
+    const int nranges = (g.P + ACT_RANGE - 1) / ACT_RANGE;
+    if (!last || n_slices <= 1) {
+        if (launch_preprocess_bwd_views(g, n, cams, radii, gv, inst, acc, s, 0, nranges, overwrite)) return 1;
+        if (last && on_slice) on_slice(slice_ctx, 0, 0, g.P);
+        return 0;
+    }
+    if (n_slices > nranges) n_slices = nranges;
+    for (int k = 0; k < n_slices; k++) {
+        const int lo = (int)((int64_t)nranges * k / n_slices), hi = (int)((int64_t)nranges * (k + 1) / n_slices);
+        if (launch_preprocess_bwd_views(g, n, cams, radii, gv, inst, acc, s, lo, hi, overwrite)) return 1;
+        if (on_slice) {
+            const int64_t g_hi = (int64_t)hi * ACT_RANGE;
+            on_slice(slice_ctx, k, lo * ACT_RANGE, (int32_t)(g_hi < g.P ? g_hi : g.P));
+        }
+    }
+    return 0;
+}
+
 // small grow-only pinned host buffer for the instance counts of a forward batch (so that the read-backs are truly
 // asynchronous and the host can run ahead of the device)
 static uint32_t* pinned_counts(size_t n) {
@@ -509,6 +557,16 @@ int32_t gslm_jtjv_batch(const GslmGaussians* g, const GslmGaussians* gt, int32_t
                         const void* const* binning_buffers, const void* const* image_buffers,
                         const int32_t* num_cached, const float* const* weights, void* scratch, size_t scratch_bytes,
                         GslmGrads* grads, float* out_vJJv, void* stream) {
+    return gslm_jtjv_batch_sliced(g, gt, n_views, cams, radii, geom_buffers, binning_buffers, image_buffers, num_cached,
+                                  weights, scratch, scratch_bytes, grads, out_vJJv, 1, nullptr, nullptr, stream);
+}
+
+int32_t gslm_jtjv_batch_sliced(const GslmGaussians* g, const GslmGaussians* gt, int32_t n_views, const GslmCamera* cams,
+                               const int32_t* const* radii, const void* const* geom_buffers,
+                               const void* const* binning_buffers, const void* const* image_buffers,
+                               const int32_t* num_cached, const float* const* weights, void* scratch,
+                               size_t scratch_bytes, GslmGrads* grads, float* out_vJJv, int32_t n_slices,
+                               GslmSliceFn on_slice, void* slice_ctx, void* stream) {
     if (n_views < 0 || (n_views > 0 && (!cams || !radii || !geom_buffers || !binning_buffers || !image_buffers ||
                                         !num_cached || !scratch)) || !grads || !g) {
         set_error("null argument");
@@ -525,14 +583,15 @@ int32_t gslm_jtjv_batch(const GslmGaussians* g, const GslmGaussians* gt, int32_t
     if (P == 0) return 0;
     TangentPtrs t = make_tangents(gt, nullptr);
     GslmGrads acc = *grads;
-    if (!acc.accumulate) {   // overwrite semantics = clear, then accumulate every view
-        const size_t n = (size_t)P;
-        struct { float* p; size_t count; } sinks[8] = {
-            {acc.dL_dmeans2D, 3 * n}, {acc.dL_dcolors, 3 * n}, {acc.dL_dopacity, n}, {acc.dL_dmeans3D, 3 * n},
-            {acc.dL_dcov3D, 6 * n}, {acc.dL_dsh, 3 * n * (size_t)g->M}, {acc.dL_dscales, 3 * n}, {acc.dL_drotations, 4 * n}};
-        for (auto& k : sinks)
-            if (k.p && k.count) GSLM_CUDA_OK(cudaMemsetAsync(k.p, 0, k.count * sizeof(float), s));
-        acc.accumulate = 1;
+    // overwrite semantics = clear, then accumulate every view.  (cudaMemsetAsync beats zero-filling inside the first
+    // adjoint launch -- kept as launch_preprocess_bwd_views(zero_first) -- by 0.06 ms per product at P = 1M: the
+    // stores delay the start of every warp's dependent chain.)
+    if (!acc.accumulate && clear_sinks(acc, P, g->M, s)) return 1;
+    const bool overwrite = false;
+    acc.accumulate = 1;
+    if (n_views == 0) {
+        empty_product_callbacks(P, n_slices, on_slice, slice_ctx);
+        return 0;
     }
     for (int v0 = 0; v0 < n_views; v0 += MAX_BATCH_VIEWS) {
         const int n = (n_views - v0) < MAX_BATCH_VIEWS ? (n_views - v0) : MAX_BATCH_VIEWS;
@@ -555,7 +614,8 @@ int32_t gslm_jtjv_batch(const GslmGaussians* g, const GslmGaussians* gt, int32_t
         if (launch_preprocess_tangent_batch(*g, t, n, cams + v0, gv, tgeom, s)) return 1;
         if (launch_blend_jtjv_batch(n, bv, iv, cams + v0, tgeom, weights ? weights + v0 : nullptr, inst, out_vJJv, s))
             return 1;
-        if (launch_preprocess_bwd_views(*g, n, cams + v0, radii + v0, gv, inst, acc, s)) return 1;
+        if (adjoint_chunk(*g, n, cams + v0, radii + v0, gv, inst, acc, overwrite && v0 == 0,
+                          v0 + MAX_BATCH_VIEWS >= n_views, n_slices, on_slice, slice_ctx, s)) return 1;
     }
     return 0;
 }
@@ -621,6 +681,16 @@ int32_t gslm_backward_batch(const GslmGaussians* g, int32_t n_views, const GslmC
                             const void* const* binning_buffers, const void* const* image_buffers,
                             const int32_t* num_cached, const float* const* dL_dcolor, void* scratch,
                             size_t scratch_bytes, GslmGrads* grads, void* stream) {
+    return gslm_backward_batch_sliced(g, n_views, cams, radii, geom_buffers, binning_buffers, image_buffers, num_cached,
+                                      dL_dcolor, scratch, scratch_bytes, grads, 1, nullptr, nullptr, stream);
+}
+
+int32_t gslm_backward_batch_sliced(const GslmGaussians* g, int32_t n_views, const GslmCamera* cams,
+                                   const int32_t* const* radii, const void* const* geom_buffers,
+                                   const void* const* binning_buffers, const void* const* image_buffers,
+                                   const int32_t* num_cached, const float* const* dL_dcolor, void* scratch,
+                                   size_t scratch_bytes, GslmGrads* grads, int32_t n_slices, GslmSliceFn on_slice,
+                                   void* slice_ctx, void* stream) {
     if (n_views < 0 || (n_views > 0 && (!cams || !radii || !geom_buffers || !binning_buffers || !image_buffers ||
                                         !num_cached || !scratch || !dL_dcolor)) || !grads || !g) {
         set_error("null argument");
@@ -636,14 +706,12 @@ int32_t gslm_backward_batch(const GslmGaussians* g, int32_t n_views, const GslmC
     const int P = g->P;
     if (P == 0) return 0;
     GslmGrads acc = *grads;
-    if (!acc.accumulate) {   // overwrite semantics = clear, then accumulate every view
-        const size_t n = (size_t)P;
-        struct { float* p; size_t count; } sinks[8] = {
-            {acc.dL_dmeans2D, 3 * n}, {acc.dL_dcolors, 3 * n}, {acc.dL_dopacity, n}, {acc.dL_dmeans3D, 3 * n},
-            {acc.dL_dcov3D, 6 * n}, {acc.dL_dsh, 3 * n * (size_t)g->M}, {acc.dL_dscales, 3 * n}, {acc.dL_drotations, 4 * n}};
-        for (auto& k : sinks)
-            if (k.p && k.count) GSLM_CUDA_OK(cudaMemsetAsync(k.p, 0, k.count * sizeof(float), s));
-        acc.accumulate = 1;
+    if (!acc.accumulate && clear_sinks(acc, P, g->M, s)) return 1;
+    const bool overwrite = false;
+    acc.accumulate = 1;
+    if (n_views == 0) {
+        empty_product_callbacks(P, n_slices, on_slice, slice_ctx);
+        return 0;
     }
     for (int v0 = 0; v0 < n_views; v0 += MAX_BATCH_VIEWS) {
         const int n = (n_views - v0) < MAX_BATCH_VIEWS ? (n_views - v0) : MAX_BATCH_VIEWS;
@@ -661,7 +729,8 @@ int32_t gslm_backward_batch(const GslmGaussians* g, int32_t n_views, const GslmC
             p += align_up((size_t)num_cached[v] * REC_F4 * sizeof(float4));
         }
         if (launch_blend_bwd_batch(n, bv, iv, cams + v0, dL_dcolor + v0, inst, s)) return 1;
-        if (launch_preprocess_bwd_views(*g, n, cams + v0, radii + v0, gv, inst, acc, s)) return 1;
+        if (adjoint_chunk(*g, n, cams + v0, radii + v0, gv, inst, acc, overwrite && v0 == 0,
+                          v0 + MAX_BATCH_VIEWS >= n_views, n_slices, on_slice, slice_ctx, s)) return 1;
     }
     return 0;
 }

@@ -81,16 +81,17 @@ __global__ void __launch_bounds__(256) k_activation_jvp(Act a, GslmRawVector v, 
 struct Damp { float xyz, dc, rest, scaling, rotation, opacity; };
 
 __global__ void __launch_bounds__(256) k_activation_vjp(Act a, GslmActVector g, GslmRawVector v, Damp d,
-                                                        GslmRawVector out)
+                                                        GslmRawVector out, int g_lo, int g_hi)
 {
-    const size_t n_sh = (size_t)a.P * 3 * a.M, stride = (size_t)gridDim.x * blockDim.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
     const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int row = 3 * a.M;
+    const size_t sh_lo = (size_t)g_lo * row, n_sh = (size_t)g_hi * row;   // SH elements of the Gaussians [g_lo, g_hi)
     const bool dv = v.xyz != nullptr;
     if ((row & 3) == 0 && (reinterpret_cast<size_t>(g.shs) & 15u) == 0) {
         const int qrow = row >> 2;
         const size_t n4 = n_sh >> 2;
-        for (size_t c = tid; c < n4; c += stride) {
+        for (size_t c = (sh_lo >> 2) + tid; c < n4; c += stride) {
             const size_t i = c / qrow;
             const int r = (int)(c - i * qrow) << 2;
             const float4 gq = __ldg(reinterpret_cast<const float4*>(g.shs) + c);
@@ -107,7 +108,7 @@ __global__ void __launch_bounds__(256) k_activation_vjp(Act a, GslmActVector g, 
             }
         }
     } else {
-        for (size_t e = tid; e < n_sh; e += stride) {
+        for (size_t e = sh_lo + tid; e < n_sh; e += stride) {
             const size_t i = e / row;
             const int r = (int)(e - i * row);
             const float gv = __ldg(g.shs + e);
@@ -120,7 +121,7 @@ __global__ void __launch_bounds__(256) k_activation_vjp(Act a, GslmActVector g, 
             }
         }
     }
-    for (size_t i = tid; i < (size_t)a.P; i += stride) {
+    for (size_t i = (size_t)g_lo + tid; i < (size_t)g_hi; i += stride) {
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
             const size_t k = 3 * i + c;
@@ -190,8 +191,17 @@ extern "C" int32_t gslm_activation_jvp(const GslmActivations* a, const GslmRawVe
 extern "C" int32_t gslm_activation_vjp(const GslmActivations* a, const GslmActVector* g, const GslmRawVector* v,
                                        const float* damp6, const GslmRawVector* out, void* stream)
 {
+    return gslm_activation_vjp_range(a, g, v, damp6, out, 0, a ? a->P : 0, stream);
+}
+
+extern "C" int32_t gslm_activation_vjp_range(const GslmActivations* a, const GslmActVector* g, const GslmRawVector* v,
+                                             const float* damp6, const GslmRawVector* out, int32_t g_lo, int32_t g_hi,
+                                             void* stream)
+{
     if (check(a, "gslm_activation_vjp")) return 1;
     if (a->P == 0) return 0;
+    if (g_lo < 0 || g_hi > a->P || g_lo > g_hi) { set_error("gslm_activation_vjp: bad Gaussian range"); return 1; }
+    if (g_lo == g_hi) return 0;
     if (!g || !g->means3D || !g->shs || !g->scales || !g->rotations || !g->opacities) {
         set_error("gslm_activation_vjp: bad activated-space gradient");
         return 1;
@@ -209,8 +219,8 @@ extern "C" int32_t gslm_activation_vjp(const GslmActivations* a, const GslmActVe
     }
     cudaStream_t s = (cudaStream_t)stream;
     StageScope sc(ST_ACTIVATION, s);
-    k_activation_vjp<<<grid_for(a->P, a->M), 256, 0, s>>>(
-        Act{a->P, a->M, a->scales, a->rotations, a->rot_norm, a->opacities}, *g, vin, d, *out);
+    k_activation_vjp<<<grid_for(g_hi - g_lo, a->M), 256, 0, s>>>(
+        Act{a->P, a->M, a->scales, a->rotations, a->rot_norm, a->opacities}, *g, vin, d, *out, g_lo, g_hi);
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
 }

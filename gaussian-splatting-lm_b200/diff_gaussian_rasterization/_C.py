@@ -99,13 +99,15 @@ def _cached(R, imageBuffer=None, W=None, H=None):
 
 
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_int32, C.c_size_t)
+SLICE_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int32, C.c_int32, C.c_int32)
 
 EXPORTS = ("gslm_last_error", "gslm_abi_version", "gslm_sizeof", "gslm_camera_offsetof", "gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_binning_temp_bytes",
            "gslm_mark_visible", "gslm_forward", "gslm_render", "gslm_render_batch", "gslm_forward_batch",
            "gslm_count_instances", "gslm_fp32_probe_scratch_bytes", "gslm_fp32_peak_probe", "gslm_forward_jvp", "gslm_backward_scratch_bytes", "gslm_backward",
            "gslm_jvp_scratch_bytes", "gslm_jvp_cached", "gslm_jtjv_scratch_bytes", "gslm_jtjv",
-           "gslm_jtjv_batch_scratch_bytes", "gslm_jtjv_batch", "gslm_jvp_batch_scratch_bytes", "gslm_jvp_batch",
-           "gslm_backward_batch_scratch_bytes", "gslm_backward_batch", "gslm_loss_lin_bytes", "gslm_loss_blocks",
+           "gslm_jtjv_batch_scratch_bytes", "gslm_jtjv_batch", "gslm_jtjv_batch_sliced", "gslm_jvp_batch_scratch_bytes",
+           "gslm_jvp_batch", "gslm_backward_batch_scratch_bytes", "gslm_backward_batch", "gslm_backward_batch_sliced",
+           "gslm_activation_vjp_range", "gslm_loss_lin_bytes", "gslm_loss_blocks",
            "gslm_loss_blocks_jvp", "gslm_loss_blocks_vjp", "gslm_activation_jvp", "gslm_activation_vjp",
            "gslm_densification_stats",
            "gslm_buffer_view", "gslm_tangent_records", "gslm_timing_num_stages",
@@ -147,6 +149,11 @@ def lib():
         L.gslm_jtjv.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
         L.gslm_jtjv_batch_scratch_bytes.argtypes = [C.c_int32, C.c_int32, vp]
         L.gslm_jtjv_batch.argtypes = [vp, vp, C.c_int32, vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, vp, vp, vp]
+        L.gslm_jtjv_batch_sliced.argtypes = [vp, vp, C.c_int32, vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, vp, vp,
+                                             C.c_int32, SLICE_FN, vp, vp]
+        L.gslm_backward_batch_sliced.argtypes = [vp, C.c_int32, vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, vp,
+                                                 C.c_int32, SLICE_FN, vp, vp]
+        L.gslm_activation_vjp_range.argtypes = [vp, vp, vp, vp, vp, C.c_int32, C.c_int32, vp]
         L.gslm_jvp_batch_scratch_bytes.argtypes = [C.c_int32, C.c_int32]
         L.gslm_jvp_batch.argtypes = [vp, vp, C.c_int32, vp, vp, vp, vp, vp, vp, C.c_size_t, vp, vp]
         L.gslm_backward_batch_scratch_bytes.argtypes = [C.c_int32, vp]
@@ -709,9 +716,34 @@ class JtjvBatchPlan:
         return self.scratch
 
 
-def jtjv_batch(gauss_args, tangent_args, plan, outs, out_vJJv=None, accumulate=True):
+class _SliceCallback:
+    """Wraps a Python callable(slice, g_lo, g_hi) as a GslmSliceFn; exceptions raised inside the C call are kept and
+    re-raised by check() afterwards (ctypes would only print them)."""
+
+    def __init__(self, fn):
+        self.err = None
+
+        def tramp(_ctx, k, g_lo, g_hi):
+            if self.err is None:
+                try:
+                    fn(int(k), int(g_lo), int(g_hi))
+                except BaseException as e:      # noqa: BLE001 -- re-raised by check()
+                    self.err = e
+        self.c = SLICE_FN(tramp)
+
+    def check(self):
+        # cb -> c -> tramp -> cb is a reference cycle that would keep the callable (and the 2 x 59 P floats it owns)
+        # alive until the cycle collector runs: every product would then cudaMalloc fresh buffers
+        self.c = None
+        err, self.err = self.err, None
+        if err is not None:
+            raise err
+
+
+def jtjv_batch(gauss_args, tangent_args, plan, outs, out_vJJv=None, accumulate=True, n_slices=1, on_slice=None):
     """outs (8-tuple like rasterize_gaussians_backward, entries may be None) (+)= sum over the plan's views of
-    J_v^T diag(weight_v) J_v v -- ONE call into the library per CG iteration."""
+    J_v^T diag(weight_v) J_v v -- ONE call into the library per CG iteration.  on_slice(k, g_lo, g_hi): host callback
+    after the launch that completes the Gaussian rows [g_lo, g_hi) (gslm_jtjv_batch_sliced)."""
     L = lib()
     g, k1 = _gaussians(*gauss_args)
     gt, k3 = _tangent_gaussians(*tangent_args)
@@ -721,10 +753,14 @@ def jtjv_batch(gauss_args, tangent_args, plan, outs, out_vJJv=None, accumulate=T
      gr.dL_drotations) = [_ptr(o) for o in outs]
     gr.accumulate = 1 if accumulate else 0
     vp = lambda a: C.cast(a, C.c_void_p)
-    _check(L.gslm_jtjv_batch(C.addressof(g), C.addressof(gt), plan.n, vp(plan.cams), vp(plan.radii), vp(plan.geom),
-                             vp(plan.binning), vp(plan.image), vp(plan.num_cached),
-                             vp(plan.weights) if plan.any_weight else None, scratch.data_ptr(), scratch.numel(),
-                             C.addressof(gr), _ptr(out_vJJv), _stream()))
+    cb = _SliceCallback(on_slice) if on_slice is not None else None
+    _check(L.gslm_jtjv_batch_sliced(C.addressof(g), C.addressof(gt), plan.n, vp(plan.cams), vp(plan.radii),
+                                    vp(plan.geom), vp(plan.binning), vp(plan.image), vp(plan.num_cached),
+                                    vp(plan.weights) if plan.any_weight else None, scratch.data_ptr(),
+                                    scratch.numel(), C.addressof(gr), _ptr(out_vJJv), int(n_slices),
+                                    cb.c if cb else SLICE_FN(), None, _stream()))
+    if cb:
+        cb.check()
 
 
 def jvp_batch(gauss_args, tangent_args, plan, out_images):
@@ -740,8 +776,9 @@ def jvp_batch(gauss_args, tangent_args, plan, out_images):
                             _stream()))
 
 
-def backward_batch(gauss_args, plan, cot_images, outs, accumulate=True):
-    """outs (8-tuple like rasterize_gaussians_backward) (+)= sum over the plan's views of J_v^T cot_images[v]."""
+def backward_batch(gauss_args, plan, cot_images, outs, accumulate=True, n_slices=1, on_slice=None):
+    """outs (8-tuple like rasterize_gaussians_backward) (+)= sum over the plan's views of J_v^T cot_images[v];
+    on_slice as in jtjv_batch."""
     L = lib()
     g, k1 = _gaussians(*gauss_args)
     scratch = plan.scratch_for(g.P)
@@ -751,9 +788,13 @@ def backward_batch(gauss_args, plan, cot_images, outs, accumulate=True):
      gr.dL_drotations) = [_ptr(o) for o in outs]
     gr.accumulate = 1 if accumulate else 0
     vp = lambda a: C.cast(a, C.c_void_p)
-    _check(L.gslm_backward_batch(C.addressof(g), plan.n, vp(plan.cams), vp(plan.radii), vp(plan.geom),
-                                 vp(plan.binning), vp(plan.image), vp(plan.num_cached), vp(cots), scratch.data_ptr(),
-                                 scratch.numel(), C.addressof(gr), _stream()))
+    cb = _SliceCallback(on_slice) if on_slice is not None else None
+    _check(L.gslm_backward_batch_sliced(C.addressof(g), plan.n, vp(plan.cams), vp(plan.radii), vp(plan.geom),
+                                        vp(plan.binning), vp(plan.image), vp(plan.num_cached), vp(cots),
+                                        scratch.data_ptr(), scratch.numel(), C.addressof(gr), int(n_slices),
+                                        cb.c if cb else SLICE_FN(), None, _stream()))
+    if cb:
+        cb.check()
 
 
 def buffer_view(P, W, H, R, geomBuffer, binningBuffer, imageBuffer, sortScratch=None):
@@ -882,18 +923,21 @@ class Activations:
         av = GslmActVector(None, _ptr(shs_t), _ptr(scales_t), _ptr(rotations_t), _ptr(opacities_t))
         _check(lib().gslm_activation_jvp(C.addressof(self.c), C.addressof(rv), C.addressof(av), _stream()))
 
-    def vjp(self, means3D_g, shs_g, scales_g, rotations_g, opacities_g, out_state, v_state=None, damp6=None):
-        """out_state <- activation VJP of the activated-space gradient (+ damp6[k] * v_state per group)."""
+    def vjp(self, means3D_g, shs_g, scales_g, rotations_g, opacities_g, out_state, v_state=None, damp6=None,
+            g_lo=0, g_hi=None):
+        """out_state <- activation VJP of the activated-space gradient (+ damp6[k] * v_state per group), for the
+        Gaussians [g_lo, g_hi) (default: all)."""
         av = GslmActVector(*[_ptr(t) for t in (means3D_g, shs_g, scales_g, rotations_g, opacities_g)])
         ov = _raw_vector(out_state)
+        g_hi = self.P if g_hi is None else int(g_hi)
         if v_state is None:
-            _check(lib().gslm_activation_vjp(C.addressof(self.c), C.addressof(av), None, None, C.addressof(ov),
-                                             _stream()))
+            _check(lib().gslm_activation_vjp_range(C.addressof(self.c), C.addressof(av), None, None, C.addressof(ov),
+                                                   int(g_lo), g_hi, _stream()))
         else:
             vv = _raw_vector(v_state)
             d = (C.c_float * 6)(*[float(x) for x in damp6])
-            _check(lib().gslm_activation_vjp(C.addressof(self.c), C.addressof(av), C.addressof(vv), d,
-                                             C.addressof(ov), _stream()))
+            _check(lib().gslm_activation_vjp_range(C.addressof(self.c), C.addressof(av), C.addressof(vv), d,
+                                                   C.addressof(ov), int(g_lo), g_hi, _stream()))
 
 
 def densification_stats(radii, viewspace_grad, max_radii2D, xyz_gradient_accum, denom):

@@ -478,7 +478,8 @@ class LinearSolverFunctions:
         the allreduce payload) and the 8-tuple of sinks the kernels write into."""
         a = self._act
         P, M = a["means3D"].shape[0], a["shs"].shape[1]
-        flat = torch.zeros(P * (3 + 3 * M + 3 + 4 + 1), dtype=torch.float32, device=a["means3D"].device)
+        # torch.empty: the adjoint launches run in overwrite mode (the first chunk zero-fills its own rows in-kernel)
+        flat = torch.empty(P * (3 + 3 * M + 3 + 4 + 1), dtype=torch.float32, device=a["means3D"].device)
         off = 0
         views = {}
         for name, shape in (("means3D", (P, 3)), ("shs", (P, M, 3)), ("scales", (P, 3)), ("rotations", (P, 4)),
@@ -492,21 +493,22 @@ class LinearSolverFunctions:
                  views["rotations"])
         return flat, views, sinks
 
+    # Gaussian-range slices of the last adjoint launch when a collective follows (multi-GPU).  1 = the collective
+    # starts when the whole adjoint stage is done.  Measured on 2 and 8 x B200 (profiles/r2g_*): cutting the launch
+    # into 4 ranges so that NCCL reduces slice k while slice k + 1 is produced LOSES (adjoint stage 1.47 -> 2.34 ms
+    # per step at 32 views/rank): the stage is latency-bound and a quarter-size launch fills 41 % of the SMs.
+    N_SLICES = 1
+
+    def _tail(self, views, v=None, damp=None):
+        """The end of every parameter-space product: (allreduce over ranks) -> activation VJP (+ damping), run per
+        Gaussian-range slice as the library's adjoint stage completes it (`_ProductTail`)."""
+        return _ProductTail(self, views, v, damp)
+
     def _to_state(self, views, v=None, damp=None):
-        """Activation VJP: activated-space gradients -> raw-parameter GaussianModelState (masked), with the damping
-        term `+ damp * v` (float lambda or GaussianModelDampMatrix) fused into the same pass."""
-        a = self._act
-        out = GaussianModelState.from_gaussians(self.gaussians)
-        grads = (views["means3D"], views["shs"], views["scales"], views["rotations"], views["opacities"])
-        if damp is None:
-            a["layer"].vjp(*grads, out)
-        else:
-            d7 = damp.values() if isinstance(damp, GaussianModelDampMatrix) else (float(damp),) * 7
-            a["layer"].vjp(*grads, out, v, d7[:6])
-            if out.exposure_grad.numel():
-                out.exposure_grad.add_(v.exposure_grad, alpha=float(d7[6]))
-        return GaussianModelState(*out.tensors(), param_mask=self.param_mask, splat_mask=self.splat_mask,
-                                  _flat=out.flat)
+        """Activation VJP (+ damping) of a complete activated-space gradient (this rank's: no collective)."""
+        t = _ProductTail(self, views, v, damp, local=True)
+        t(0, 0, self._act["means3D"].shape[0])
+        return t.finish()
 
     def _require_linearized(self):
         """The reference's matvec / matvec_T render at the CURRENT parameters on every call
@@ -554,8 +556,8 @@ class LinearSolverFunctions:
             k += t.shape[0]
         return tens
 
-    def _pull_back(self, cots, sinks):
-        """sinks += sum over local views of J_r^T (mask * cot): ONE library call; cots = per-batch padded tensors."""
+    def _pull_back(self, cots, sinks, tail):
+        """sinks = sum over local views of J_r^T (mask * cot): ONE library call; cots = per-batch padded tensors."""
         per_view, k = [], 0
         for cot in cots:
             for i in range(cot.shape[0]):
@@ -563,7 +565,8 @@ class LinearSolverFunctions:
                 c = cot[i, :, :vc.H, :vc.W]
                 per_view.append(c.contiguous() if self.ssim else c * vc.mask)     # ssim: already masked by the VJP kernel
             k += cot.shape[0]
-        _C.backward_batch(self._gauss_args(), self._get_plan(), per_view, sinks)
+        _C.backward_batch(self._gauss_args(), self._get_plan(), per_view, sinks, accumulate=False,
+                          n_slices=tail.n_slices, on_slice=tail)
 
     def _matvec_cached(self, v):
         self._require_linearized()
@@ -597,7 +600,7 @@ class LinearSolverFunctions:
         self._require_linearized()
         flat, views, sinks = self._act_accumulators()
         if self.track_viewspace:
-            self.viewspace_grad = torch.zeros((self._act["means3D"].shape[0], 3), dtype=torch.float32, device=flat.device)
+            self.viewspace_grad = torch.empty((self._act["means3D"].shape[0], 3), dtype=torch.float32, device=flat.device)
             sinks = (self.viewspace_grad,) + sinks[1:]
         cots = []
         for idx, _ in enumerate(self._batches()):
@@ -606,14 +609,13 @@ class LinearSolverFunctions:
                 cots.append(self._loss_batches[idx].vjp(u.Ll1_per_pixel, u.ssim_loss_per_pixel))
             else:
                 cots.append(u.Ll1_per_pixel + u.ssim_loss_per_pixel)     # J^T of the two aliased blocks
-        self._pull_back(cots, sinks)
-        if self.dist:
-            self.dist.all_reduce(flat)
-            if self.track_viewspace:
-                self.dist.all_reduce(self.viewspace_grad)
-        return self._to_state(views)
+        tail = self._tail(views)
+        self._pull_back(cots, sinks, tail)
+        if self.dist and self.track_viewspace:
+            self.dist.all_reduce(self.viewspace_grad)
+        return tail.finish()
 
-    def _normal_matvec_ssim(self, gargs, targs, sinks, quad):
+    def _normal_matvec_ssim(self, gargs, targs, sinks, quad, tail):
         """J_r^T (L^T L) J_r v: image tangents from the batched tangent tile kernel, the loss-block JVP and VJP
         kernels in image space, then the batched adjoint tile kernel."""
         cots = []
@@ -622,7 +624,7 @@ class LinearSolverFunctions:
             if quad is not None:
                 quad += (t1 * t1).sum() + (t2 * t2).sum()
             cots.append(lb.vjp(t1, t2))
-        self._pull_back(cots, sinks)
+        self._pull_back(cots, sinks, tail)
 
     def normal_matvec(self, v, damp=None, return_quad=False):
         """J^T J v (+ damp * v): the Gauss-Newton product CG needs, one fused tile kernel per view.
@@ -639,16 +641,82 @@ class LinearSolverFunctions:
         gargs = self._gauss_args()
         flat, views, sinks = self._act_accumulators()
         quad = torch.zeros(1, dtype=torch.float32, device=flat.device) if return_quad else None
+        tail = self._tail(views, v, damp)
         if self.ssim:
-            self._normal_matvec_ssim(gargs, targs, sinks, quad)
+            self._normal_matvec_ssim(gargs, targs, sinks, quad, tail)
         else:
-            _C.jtjv_batch(gargs, targs, self._get_plan(), sinks, out_vJJv=quad)
-        if self.dist:
-            self.dist.all_reduce(flat)
-            if quad is not None:
-                self.dist.all_reduce(quad)
-        out = self._to_state(views, v, damp)
+            _C.jtjv_batch(gargs, targs, self._get_plan(), sinks, out_vJJv=quad, accumulate=False,
+                          n_slices=tail.n_slices, on_slice=tail)
+        if self.dist and quad is not None:
+            self.dist.all_reduce(quad)
+        out = tail.finish()
         return (out, quad) if return_quad else out
+
+
+class _ProductTail:
+    """Callable handed to the library as the per-slice callback of gslm_jtjv_batch_sliced / gslm_backward_batch_sliced.
+
+    Single GPU: one call for [0, P): the activation VJP (+ damping) on the caller's stream.
+    Multi-GPU: the library cuts the last adjoint launch into N_SLICES Gaussian ranges; after each launch this object
+    records an event on the compute stream and, on a communication stream, (1) all-reduces the five row blocks of the
+    slice (means3D, shs, scales, rotations, opacities rows [g_lo, g_hi)) as ONE grouped NCCL call and (2) runs the
+    activation VJP of the slice -- so the reduction of slice k and its VJP overlap the production of slice k + 1, and
+    only the last slice's collective is exposed.  finish() joins the streams and returns the masked raw-space state."""
+
+    _GROUPS = ("means3D", "shs", "scales", "rotations", "opacities")
+
+    def __init__(self, F, views, v, damp, local=False):
+        self.F, self.views, self.v, self.damp = F, views, v, damp
+        self.out = GaussianModelState.from_gaussians(F.gaussians, zero=False)
+        self.dist = None if local else F.dist
+        self.n_slices = F.N_SLICES if self.dist else 1
+        self.d7 = None
+        if damp is not None:
+            self.d7 = damp.values() if isinstance(damp, GaussianModelDampMatrix) else (float(damp),) * 7
+        if self.dist:
+            dev = self.out.flat.device
+            if getattr(F, "_comm_stream", None) is None:
+                F._comm_stream = torch.cuda.Stream(dev)
+            self.comm = F._comm_stream
+            self.cur = torch.cuda.current_stream(dev)
+            P = F._act["means3D"].shape[0]
+            self.rows = [views[n].view(P, -1) for n in self._GROUPS]
+
+    def _vjp(self, g_lo, g_hi):
+        vw = self.views
+        grads = (vw["means3D"], vw["shs"], vw["scales"], vw["rotations"], vw["opacities"])
+        layer = self.F._act["layer"]
+        if self.d7 is None:
+            layer.vjp(*grads, self.out, g_lo=g_lo, g_hi=g_hi)
+        else:
+            layer.vjp(*grads, self.out, self.v, self.d7[:6], g_lo=g_lo, g_hi=g_hi)
+
+    def __call__(self, k, g_lo, g_hi):
+        if not self.dist:
+            self._vjp(g_lo, g_hi)
+            return
+        import torch.distributed as dist
+        ev = torch.cuda.Event()
+        ev.record(self.cur)
+        with torch.cuda.stream(self.comm):
+            self.comm.wait_event(ev)
+            if g_hi > g_lo:
+                with dist._coalescing_manager():          # one grouped NCCL launch for the five row blocks
+                    for r in self.rows:
+                        dist.all_reduce(r[g_lo:g_hi])
+            self._vjp(g_lo, g_hi)
+
+    def finish(self):
+        F = self.F
+        if self.dist:
+            self.cur.wait_stream(self.comm)
+            for t in self.views.values():       # produced on `cur`, consumed on `comm`
+                t.record_stream(self.comm)
+            self.out.flat.record_stream(self.comm)
+        out = self.out
+        if self.d7 is not None and out.exposure_grad.numel():
+            out.exposure_grad.add_(self.v.exposure_grad, alpha=float(self.d7[6]))
+        return GaussianModelState(*out.tensors(), param_mask=F.param_mask, splat_mask=F.splat_mask, _flat=out.flat)
 
 
 class HostPipeline:

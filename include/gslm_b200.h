@@ -249,6 +249,21 @@ int32_t gslm_jtjv_batch(const GslmGaussians* g, const GslmGaussians* gt, int32_t
                         const int32_t* num_cached, const float* const* weights, void* scratch, size_t scratch_bytes,
                         GslmGrads* grads, float* out_vJJv, void* stream);
 
+/* The same call with the per-Gaussian adjoint of the LAST chunk of views cut into n_slices ranges of Gaussian ids
+ * (multiples of 256).  After the launch that completes slice k -- rows [g_lo, g_hi) of every sink are final from then
+ * on, in stream order -- the HOST callback on_slice(ctx, k, g_lo, g_hi) runs: the multi-GPU caller records an event and
+ * starts the allreduce and the activation VJP of that slice on a communication stream while the next slice is still
+ * being produced (SURVEY 8e "Overlap": the reference has no counterpart, its sum over views is the Python `+=` of
+ * DGR/diff_gaussian_rasterization/batch_render.py:330-346).  n_slices <= 1: one callback for [0, P) at the end
+ * (on_slice may be NULL).  Results are bit-identical to the unsliced call. */
+typedef void (*GslmSliceFn)(void* ctx, int32_t slice, int32_t g_lo, int32_t g_hi);
+int32_t gslm_jtjv_batch_sliced(const GslmGaussians* g, const GslmGaussians* gt, int32_t n_views, const GslmCamera* cams,
+                               const int32_t* const* radii, const void* const* geom_buffers,
+                               const void* const* binning_buffers, const void* const* image_buffers,
+                               const int32_t* num_cached, const float* const* weights, void* scratch,
+                               size_t scratch_bytes, GslmGrads* grads, float* out_vJJv, int32_t n_slices,
+                               GslmSliceFn on_slice, void* slice_ctx, void* stream);
+
 /* J v and J^T u for n_views linearised views per call (colour only), <= 16 views per kernel launch: what
  * LinearSolverFunctions.matvec / matvec_T issue (solver/solver_functions.py:75-113; the reference's CGLS,
  * solver/conjugate_gradient.py:51-127, calls both every iteration, and the L1 + SSIM normal product needs the
@@ -265,6 +280,14 @@ int32_t gslm_backward_batch(const GslmGaussians* g, int32_t n_views, const GslmC
                             const void* const* binning_buffers, const void* const* image_buffers,
                             const int32_t* num_cached, const float* const* dL_dcolor, void* scratch,
                             size_t scratch_bytes, GslmGrads* grads, void* stream);
+
+/* gslm_backward_batch with the sliced adjoint of gslm_jtjv_batch_sliced (same callback contract). */
+int32_t gslm_backward_batch_sliced(const GslmGaussians* g, int32_t n_views, const GslmCamera* cams,
+                                   const int32_t* const* radii, const void* const* geom_buffers,
+                                   const void* const* binning_buffers, const void* const* image_buffers,
+                                   const int32_t* num_cached, const float* const* dL_dcolor, void* scratch,
+                                   size_t scratch_bytes, GslmGrads* grads, int32_t n_slices, GslmSliceFn on_slice,
+                                   void* slice_ctx, void* stream);
 
 /* ---- residual side: the two per-pixel loss blocks and their derivatives --------------------------------------
  * Replaces compute_batch_loss_block (solver/batch_training_loss.py:10-31) with the SSIM map of ssim_per_pixel /
@@ -336,6 +359,10 @@ int32_t gslm_activation_jvp(const GslmActivations* act, const GslmRawVector* v, 
  * damping of train_jvp.py:237-260) */
 int32_t gslm_activation_vjp(const GslmActivations* act, const GslmActVector* g, const GslmRawVector* v,
                             const float* damp6, const GslmRawVector* out, void* stream);
+/* the same restricted to the Gaussians [g_lo, g_hi): the per-slice tail of the sliced products above */
+int32_t gslm_activation_vjp_range(const GslmActivations* act, const GslmActVector* g, const GslmRawVector* v,
+                                  const float* damp6, const GslmRawVector* out, int32_t g_lo, int32_t g_hi,
+                                  void* stream);
 
 /* Densification bookkeeping of the training driver (train_jvp.py:311-316: max_radii2D[vis] = max(max_radii2D[vis],
  * radii[vis]); GaussianModel.add_densification_stats, scene/gaussian_model.py:561-563: xyz_gradient_accum[vis] +=

@@ -99,3 +99,49 @@ def test_adjoint_identity_at_full_size(full):
         u = F.loss * 1.0 + Jv * 0.1
         lhs, rhs = F.dot(u, Jv), F.dot(F.matvec_T(u), v)
         assert abs(lhs - rhs) <= 1e-2 * max(abs(lhs), abs(rhs))
+
+
+def _quirk_gaussians(model, F):
+    """Gaussians whose parameters enter one of the reference's two NON-adjoint code paths in some view of the fixture:
+    (1) opacity > 0.99: alpha = min(0.99, o G) can clamp -- zero tangent in renderCUDAJvpSplit, live gradient in
+        backward.cu:569 (SURVEY A.4);
+    (2) |x/z| > 1.3 tan(fovx) or |y/z| > 1.3 tan(fovy) in camera space: computeCov2D clamps t.x / t.y
+        (forward.cu:84-90), the backward pass treats the clamped coordinate as independent of t.z
+        (backward.cu:300-312)."""
+    import math
+    xyz = model._xyz.detach()
+    flag = torch.sigmoid(model._opacity.detach()).view(-1) > 0.99
+    ones = torch.ones_like(xyz[:, :1])
+    for vc in F._views:
+        t = torch.cat((xyz, ones), dim=1) @ vc.cam.world_view_transform          # row-vector convention
+        tx, ty = math.tan(vc.cam.FoVx * 0.5), math.tan(vc.cam.FoVy * 0.5)
+        z = t[:, 2]
+        flag |= (z > 0.2) & (((t[:, 0] / z).abs() > 1.3 * tx) | ((t[:, 1] / z).abs() > 1.3 * ty))
+    return flag
+
+
+def test_adjoint_identity_at_full_size_without_the_reference_quirks(full):
+    """how much of the 1e-2 above is the documented quirks?  With the tangent restricted to the
+    Gaussians that touch neither quirk, <u, J v> == <J^T u, v> holds to 1e-4 at the full per-view size -- the
+    tolerance of the reference's own tests/test_matvec.py -- so the whole gap of the unrestricted identity is the two
+    quirks the kernels reproduce on purpose."""
+    model, F = full
+    with torch.no_grad():
+        quirk = _quirk_gaussians(model, F)
+        frac = float(quirk.float().mean())
+        assert 0.0 < frac < 0.2                      # the restriction keeps most of the scene
+        v = _state(model, 5)
+        for t in v.tensors()[:6]:
+            t[quirk] = 0
+        Jv = F.matvec(v)
+        u = F.loss * 1.0 + Jv * 0.1
+        JTu = F.matvec_T(u)
+        lhs, rhs = F.dot(u, Jv), F.dot(JTu, v)
+        assert abs(lhs - rhs) <= 1e-4 * max(abs(lhs), abs(rhs)), (lhs, rhs, frac)
+        # and the gap of the unrestricted identity sits on the quirk Gaussians' rows
+        w = _state(model, 5)
+        for t in w.tensors()[:6]:
+            t[~quirk] = 0
+        Jw = F.matvec(w)
+        gap = abs(F.dot(u, Jw) - F.dot(JTu, w))
+        print(f"quirk Gaussians: {100 * frac:.2f} %; identity gap on their rows {gap:.4e}, on the others {abs(lhs - rhs):.4e}")

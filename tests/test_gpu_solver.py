@@ -383,6 +383,7 @@ def test_batched_cached_maps_with_mixed_view_sizes():
     u = Jv * 0.5 + F.loss * 1.0
     T = F.matvec_T(u)
     flat, views, sinks = F._act_accumulators()
+    flat.zero_()                       # the accumulators come uninitialised (the batched calls overwrite)
     a, e = F._act, torch.empty(0, device="cuda")
     k = 0
     for b in u.batch_losses:
