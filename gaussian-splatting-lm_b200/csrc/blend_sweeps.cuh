@@ -36,6 +36,7 @@
 // =============================================================================
 #pragma once
 #include "blend_common.cuh"
+#include <type_traits>
 
 namespace gslm {
 
@@ -44,6 +45,12 @@ namespace gslm {
 #endif
 #ifndef GSLM_BAND_SKIP
 #define GSLM_BAND_SKIP 1
+#endif
+#ifndef GSLM_FASTPATH
+#define GSLM_FASTPATH 1
+#endif
+#ifndef GSLM_DYCHAIN
+#define GSLM_DYCHAIN 1
 #endif
 #ifndef GSLM_DEFER_REDUCE
 #define GSLM_DEFER_REDUCE 0
@@ -96,9 +103,13 @@ __device__ __forceinline__ uint32_t mask_word(const uint4& m0, const uint4& m1, 
         case 4: return m1.x; case 5: return m1.y; case 6: return m1.z; default: return m1.w;
     }
 }
-// alpha_raw of pixel pair p (rows 4p + h, 4p + 2 + h) and its dy; 0 where the primal pass did not blend
+// alpha_raw of pixel pair p (rows 4p + h, 4p + 2 + h) and its dy; 0 where the primal pass did not blend.
+// CHAIN: dy arrives holding the previous pair's offsets and is stepped by -4 (one broadcast constant for all pairs
+// instead of a 64-bit constant pair per pair; only valid when every pair is visited in order).
+template <bool CHAIN = false>
 __device__ __forceinline__ f2 pair_alpha(const WTile& c, const InstCol& i, const uint4& m0, const uint4& m1, int p, f2& dy) {
-    dy = add2(splat(i.dyb), make_float2(-4.f * p, -4.f * p - 2.f));
+    if (CHAIN && p > 0) dy = add2(dy, splat(-4.f));
+    else dy = add2(splat(i.dyb), make_float2(-4.f * p, -4.f * p - 2.f));
     const f2 pl = fma2(dy, fma2(splat(i.cc), dy, splat(i.fx)), splat(i.ex));
     f2 a;
     a.x = (mask_word(m0, m1, 2 * p) & c.lbit) ? ex2_approx(pl.x) : 0.f;
@@ -155,13 +166,12 @@ __device__ __forceinline__ void tangent_sweep(const WTile& c, WarpRing& ring, fl
 #if GSLM_BAND_SKIP
             // a pair of rows-of-pixels (4-row band of the tile) that no pixel blended is skipped: the test is on
             // the broadcast mask words, hence warp-uniform (23 % of the bands at 1M Gaussians / 1080p)
-#pragma unroll
-            for (int p = 0; p < 4; p++) {
-                if ((mask_word(m0, m1, 2 * p) | mask_word(m0, m1, 2 * p + 1)) == 0u) continue;
-                f2 dy;
-                f2 a = pair_alpha(c, i, m0, m1, p, dy);
+            f2 dyc = splat(0.f);
+            auto pair = [&](int p, bool clampable, auto chain) {
+                f2& dy = dyc;
+                f2 a = pair_alpha<decltype(chain)::value && GSLM_DYCHAIN>(c, i, m0, m1, p, dy);
                 f2 pw = fma2(dy, fma2(splat(t0.w), dy, splat(kx)), splat(hx));
-                if (q2.w > 0.99f) {
+                if (clampable) {
                     pw.x = a.x < 0.99f ? pw.x : 0.f;
                     pw.y = a.y < 0.99f ? pw.y : 0.f;
                     a.x = fminf(0.99f, a.x);
@@ -176,6 +186,24 @@ __device__ __forceinline__ void tangent_sweep(const WTile& c, WarpRing& ring, fl
                 if (WITH_D) s.D = fma2(splat(t2.y), aT, fma2(splat(q2.y), aTt, s.D));
                 s.Tt = add2(s.Tt, neg2(aTt));
                 s.T = add2(s.T, neg2(aT));
+            };
+            const uint32_t b0 = m0.x | m0.y, b1 = m0.z | m0.w, b2 = m1.x | m1.y, b3 = m1.z | m1.w;
+#if GSLM_FASTPATH
+            // all four bands live (the common case): ONE basic block, so the scheduler interleaves the four
+            // independent pairs (MUFU latency of one hides behind the FMAs of the others) and no per-pair branch issues
+            // ... and alpha_raw <= o <= 0.99 cannot reach the clamp (all but a few instances): no clamp arithmetic
+            const bool cl = q2.w > 0.99f;
+            if (b0 && b1 && b2 && b3 && !cl) {
+                pair(0, false, std::true_type{}); pair(1, false, std::true_type{}); pair(2, false, std::true_type{});
+                pair(3, false, std::true_type{});
+            } else
+#endif
+            {
+                const bool cl2 = q2.w > 0.99f;
+                if (b0) pair(0, cl2, std::false_type{});
+                if (b1) pair(1, cl2, std::false_type{});
+                if (b2) pair(2, cl2, std::false_type{});
+                if (b3) pair(3, cl2, std::false_type{});
             }
 #else
             f2 a[4], pw[4];
@@ -267,13 +295,12 @@ __device__ __forceinline__ void adjoint_sweep(const WTile& c, WarpRing& ring, fl
             // follow from Q0 = sum q, Q1 = sum q dy, Q2 = sum q dy^2 after the loop
             f2 Q0 = splat(0.f), Q1 = Q0, Q2 = Q0, G0 = Q0, G1 = Q0, G2 = Q0, GD = Q0;
 #if GSLM_BAND_SKIP
-#pragma unroll
-            for (int p = 0; p < 4; p++) {
-                if ((mask_word(m0, m1, 2 * p) | mask_word(m0, m1, 2 * p + 1)) == 0u) continue;
-                f2 dy;
-                const f2 araw = pair_alpha(c, i, m0, m1, p, dy);
+            f2 dyc = splat(0.f);
+            auto pair = [&](int p, bool clampable, auto chain) {
+                f2& dy = dyc;
+                const f2 araw = pair_alpha<decltype(chain)::value && GSLM_DYCHAIN>(c, i, m0, m1, p, dy);
                 f2 a = araw;
-                if (q2.w > 0.99f) { a.x = fminf(0.99f, a.x); a.y = fminf(0.99f, a.y); }
+                if (clampable) { a.x = fminf(0.99f, a.x); a.y = fminf(0.99f, a.y); }
                 PairA& s = sa[p];
                 const f2 om = add2(splat(1.f), neg2(a));
                 const f2 r = make_float2(rcp_approx(om.x), rcp_approx(om.y));
@@ -292,6 +319,21 @@ __device__ __forceinline__ void adjoint_sweep(const WTile& c, WarpRing& ring, fl
                 G1 = fma2(w, s.g1, G1);
                 G2 = fma2(w, s.g2, G2);
                 if (WITH_D) GD = fma2(w, s.gd, GD);
+            };
+            const uint32_t b0 = m0.x | m0.y, b1 = m0.z | m0.w, b2 = m1.x | m1.y, b3 = m1.z | m1.w;
+#if GSLM_FASTPATH
+            const bool cl = q2.w > 0.99f;
+            if (b0 && b1 && b2 && b3 && !cl) {
+                pair(0, false, std::true_type{}); pair(1, false, std::true_type{}); pair(2, false, std::true_type{});
+                pair(3, false, std::true_type{});
+            } else
+#endif
+            {
+                const bool cl2 = q2.w > 0.99f;
+                if (b0) pair(0, cl2, std::false_type{});
+                if (b1) pair(1, cl2, std::false_type{});
+                if (b2) pair(2, cl2, std::false_type{});
+                if (b3) pair(3, cl2, std::false_type{});
             }
 #else
             f2 araw[4], a[4], dy[4];

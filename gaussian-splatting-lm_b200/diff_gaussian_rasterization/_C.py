@@ -109,7 +109,7 @@ EXPORTS = ("gslm_last_error", "gslm_abi_version", "gslm_sizeof", "gslm_camera_of
            "gslm_jvp_batch", "gslm_backward_batch_scratch_bytes", "gslm_backward_batch", "gslm_backward_batch_sliced",
            "gslm_activation_vjp_range", "gslm_loss_lin_bytes", "gslm_loss_blocks",
            "gslm_loss_blocks_jvp", "gslm_loss_blocks_vjp", "gslm_activation_jvp", "gslm_activation_vjp",
-           "gslm_densification_stats",
+           "gslm_densification_stats", "gslm_multimem_allreduce_f32",
            "gslm_buffer_view", "gslm_tangent_records", "gslm_timing_num_stages",
            "gslm_timing_stage_name", "gslm_timing_enable", "gslm_timing_collect")
 
@@ -165,6 +165,7 @@ def lib():
         L.gslm_loss_blocks_vjp.argtypes = [vp, vp, vp, vp, vp, C.c_int32, vp]
         L.gslm_activation_jvp.argtypes = [vp, vp, vp, vp]
         L.gslm_activation_vjp.argtypes = [vp, vp, vp, vp, vp, vp]
+        L.gslm_multimem_allreduce_f32.argtypes = [vp, C.c_size_t, C.c_int32, C.c_int32, vp]
         L.gslm_densification_stats.argtypes = [C.c_int32, vp, vp, vp, vp, vp, vp]
         L.gslm_buffer_view.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int64, vp, vp, vp, vp, vp]
         L.gslm_tangent_records.argtypes = [vp, vp, vp, vp, vp, vp, vp]
@@ -938,6 +939,11 @@ class Activations:
             d = (C.c_float * 6)(*[float(x) for x in damp6])
             _check(lib().gslm_activation_vjp_range(C.addressof(self.c), C.addressof(av), C.addressof(vv), d,
                                                    C.addressof(ov), int(g_lo), g_hi, _stream()))
+
+
+def multimem_allreduce(multicast_ptr, n_floats, rank, world):
+    """gslm_multimem_allreduce_f32 on the current stream (see include/gslm_b200.h)."""
+    _check(lib().gslm_multimem_allreduce_f32(int(multicast_ptr), int(n_floats), int(rank), int(world), _stream()))
 
 
 def densification_stats(radii, viewspace_grad, max_radii2D, xyz_gradient_accum, denom):

@@ -41,6 +41,55 @@ def _dist():
     return None
 
 
+_PEER_CACHE = {}        # (device index, floats) -> _PeerAccumulator; every rank creates them in the same order
+
+
+class _PeerAccumulator:
+    """The rank's activated-space accumulator (59 P floats) as a SYMMETRIC allocation with an NVSwitch multicast
+    mapping (torch.distributed._symmetric_memory supplies the allocation, the handle exchange and the cross-rank
+    barrier; the reduction itself is this library's multimem kernel, csrc/peer_reduce.cu)."""
+
+    def __init__(self, n, dev, dist):
+        import torch.distributed._symmetric_memory as sm
+        self.n = n
+        self.n_pad = (n + 3) // 4 * 4
+        self.t = sm.empty(self.n_pad, dtype=torch.float32, device=dev)
+        self.t.zero_()
+        self.hdl = sm.rendezvous(self.t, dist.group.WORLD.group_name)
+        self.mc = int(getattr(self.hdl, "multicast_ptr", 0) or 0)
+        if not self.mc:
+            raise RuntimeError("no multicast mapping (NVLS) for the symmetric accumulator")
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+
+    def allreduce(self):
+        """In place, on the current stream: barrier (all partials written) -> multimem reduce + broadcast of this
+        rank's slice -> barrier (all slices stored)."""
+        self.hdl.barrier(channel=0)
+        _C.multimem_allreduce(self.mc, self.n_pad, self.rank, self.world)
+        self.hdl.barrier(channel=0)
+
+
+def _peer_accumulator(n, dev, dist):
+    """The cached symmetric accumulator, or None when peer memory is disabled (GSLM_PEER_REDUCE=0) or unavailable on
+    this box (no NVSwitch multicast): the product then ends in an NCCL allreduce instead."""
+    import os
+    # measured (profiles/r2l_peer_reduce.txt, 236 MB): 8 GPUs 0.57 ms against NCCL's 0.64; 2 GPUs 0.60 against 0.47 --
+    # with two ranks the switch has nothing to save (each link carries half the payload either way), so the multimem
+    # path is taken from 3 ranks up unless GSLM_PEER_REDUCE forces it on (1) or off (0)
+    mode = os.environ.get("GSLM_PEER_REDUCE", "auto")
+    if mode == "0" or dev.type != "cuda" or (mode == "auto" and dist.get_world_size() < 3):
+        return None
+    key = (dev.index, n)
+    if key not in _PEER_CACHE:
+        try:
+            _PEER_CACHE[key] = _PeerAccumulator(n, dev, dist)
+        except Exception as e:      # noqa: BLE001 -- decided identically on every rank of the node
+            import warnings
+            warnings.warn(f"gslm_b200: peer-memory reduction unavailable ({type(e).__name__}: {e}); using NCCL")
+            _PEER_CACHE[key] = None
+    return _PEER_CACHE[key]
+
+
 class _ViewCache:
     """Linearisation state of one view (everything a CG iteration needs, all device-resident)."""
     __slots__ = ("cam", "H", "W", "R", "radii", "geom", "binning", "img", "weight", "mask", "residual", "cam_args")
@@ -478,8 +527,12 @@ class LinearSolverFunctions:
         the allreduce payload) and the 8-tuple of sinks the kernels write into."""
         a = self._act
         P, M = a["means3D"].shape[0], a["shs"].shape[1]
-        # torch.empty: the adjoint launches run in overwrite mode (the first chunk zero-fills its own rows in-kernel)
-        flat = torch.empty(P * (3 + 3 * M + 3 + 4 + 1), dtype=torch.float32, device=a["means3D"].device)
+        # uninitialised: the batched adjoint calls run in overwrite mode.  Multi-GPU: the accumulator is the rank's
+        # copy of a symmetric, multicast-mapped allocation, summed over ranks in place (csrc/peer_reduce.cu)
+        n = P * (3 + 3 * M + 3 + 4 + 1)
+        dev = a["means3D"].device
+        self._peer = _peer_accumulator(n, dev, self.dist) if self.dist else None
+        flat = self._peer.t[:n] if self._peer is not None else torch.empty(n, dtype=torch.float32, device=dev)
         off = 0
         views = {}
         for name, shape in (("means3D", (P, 3)), ("shs", (P, M, 3)), ("scales", (P, 3)), ("rotations", (P, 4)),
@@ -491,6 +544,7 @@ class LinearSolverFunctions:
             off += n
         sinks = (None, None, views["opacities"], views["means3D"], None, views["shs"], views["scales"],
                  views["rotations"])
+        self._flat_acc = flat
         return flat, views, sinks
 
     # Gaussian-range slices of the last adjoint launch when a collective follows (multi-GPU).  1 = the collective
@@ -673,7 +727,7 @@ class _ProductTail:
         self.d7 = None
         if damp is not None:
             self.d7 = damp.values() if isinstance(damp, GaussianModelDampMatrix) else (float(damp),) * 7
-        if self.dist:
+        if self.dist and self.n_slices > 1:
             dev = self.out.flat.device
             if getattr(F, "_comm_stream", None) is None:
                 F._comm_stream = torch.cuda.Stream(dev)
@@ -696,6 +750,16 @@ class _ProductTail:
             self._vjp(g_lo, g_hi)
             return
         import torch.distributed as dist
+        if self.n_slices == 1:
+            # the whole vector at once, on the caller's stream: the multimem kernel over NVSwitch peer memory, or one
+            # NCCL allreduce where no multicast mapping exists
+            peer = getattr(self.F, "_peer", None)
+            if peer is not None:
+                peer.allreduce()
+            else:
+                dist.all_reduce(self.flat_all())
+            self._vjp(g_lo, g_hi)
+            return
         ev = torch.cuda.Event()
         ev.record(self.cur)
         with torch.cuda.stream(self.comm):
@@ -706,9 +770,13 @@ class _ProductTail:
                         dist.all_reduce(r[g_lo:g_hi])
             self._vjp(g_lo, g_hi)
 
+    def flat_all(self):
+        """The packed 59 P-float accumulator the five group views alias."""
+        return self.F._flat_acc
+
     def finish(self):
         F = self.F
-        if self.dist:
+        if self.dist and self.n_slices > 1:
             self.cur.wait_stream(self.comm)
             for t in self.views.values():       # produced on `cur`, consumed on `comm`
                 t.record_stream(self.comm)

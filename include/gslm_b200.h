@@ -364,6 +364,16 @@ int32_t gslm_activation_vjp_range(const GslmActivations* act, const GslmActVecto
                                   const float* damp6, const GslmRawVector* out, int32_t g_lo, int32_t g_hi,
                                   void* stream);
 
+/* ---- multi-GPU: the sum of the per-rank parameter-space partials over NVSwitch peer memory ----------------------
+ * (no reference counterpart: the reference is single-GPU)  `multicast_ptr` is the NVSwitch multicast
+ * address of a symmetric allocation of n_floats floats that exists on every rank of the node (the caller creates it,
+ * e.g. torch.distributed._symmetric_memory: empty + rendezvous -> multicast_ptr).  Rank `rank` of `world` sums ITS
+ * 1/world slice over all ranks with multimem.ld_reduce (the switch adds the copies in the fabric) and writes the sums
+ * back into every rank's copy with multimem.st: after all ranks have run it, every copy holds the all-reduced
+ * vector.  The call does not synchronise the ranks: bracket it with a cross-rank barrier on the same stream (all
+ * partials written before; all slices stored after).  n_floats must be a multiple of 4, the buffer 16-byte aligned. */
+int32_t gslm_multimem_allreduce_f32(void* multicast_ptr, size_t n_floats, int32_t rank, int32_t world, void* stream);
+
 /* Densification bookkeeping of the training driver (train_jvp.py:311-316: max_radii2D[vis] = max(max_radii2D[vis],
  * radii[vis]); GaussianModel.add_densification_stats, scene/gaussian_model.py:561-563: xyz_gradient_accum[vis] +=
  * ||viewspace_grad[vis, :2]||, denom[vis] += 1) with vis = radii > 0, in one pass.  radii: int32 [P] (max over the
