@@ -244,3 +244,22 @@ def test_render_chunks_merge_whole_batches_of_one_size():
     assert chunks([], 4) == []
     covered = [v for s, bounds in chunks([a] * 7 + [b] * 9 + [a] * 3, 2) for v in range(s, bounds[-1])]
     assert covered == list(range(19))
+
+
+def test_balanced_view_assignment():
+    """Greedy (LPT) view -> rank assignment on per-view instance counts: a partition, at most ceil(V / N)
+    views per rank, deterministic, and better balanced than round robin on a skewed rig."""
+    from solver.solver_functions import balanced_view_assignment
+    costs = [100, 1, 1, 1, 90, 1, 1, 1, 80, 1, 1, 1, 70, 1, 1, 1]       # round robin would put all heavy views on rank 0
+    parts = balanced_view_assignment(costs, 4)
+    assert sorted(i for p in parts for i in p) == list(range(16))
+    assert all(len(p) == 4 and p == sorted(p) for p in parts)
+    loads = [sum(costs[i] for i in p) for p in parts]
+    rr = [sum(costs[r::4]) for r in range(4)]
+    assert max(loads) - min(loads) < max(rr) - min(rr) and max(loads) <= 103
+    assert balanced_view_assignment(costs, 4) == parts
+    # ragged: 5 views over 4 ranks, one rank gets two, nobody more; more ranks than views leaves ranks empty
+    p5 = balanced_view_assignment([5, 4, 3, 2, 1], 4)
+    assert sorted(len(p) for p in p5) == [1, 1, 1, 2] and sorted(i for p in p5 for i in p) == [0, 1, 2, 3, 4]
+    p2 = balanced_view_assignment([7, 7], 4)
+    assert sorted(len(p) for p in p2) == [0, 0, 1, 1]
