@@ -5,6 +5,7 @@
 // =============================================================================
 #include "gslm_common.cuh"
 #include <cstddef>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -132,6 +133,42 @@ static int adjoint_chunk(const GslmGaussians& g, int n, const GslmCamera* cams, 
         }
     }
     return 0;
+}
+
+// Internal streams ("lanes") of the batched render: small scenes leave most of the GPU idle behind ~25 short launches
+// per view (CUB scans and sorts), so independent views are issued on several streams and overlap.  Created once per
+// host thread; forked from / joined to the caller's stream with events, so the call stays stream-ordered for the caller.
+struct LanePool {
+    static constexpr int MAX = 4;
+    cudaStream_t s[MAX] = {};
+    cudaEvent_t done[MAX] = {};
+    cudaEvent_t fork = nullptr;
+    int n = 0;
+    int get(int want) {
+        if (want > MAX) want = MAX;
+        if (!fork && cudaEventCreateWithFlags(&fork, cudaEventDisableTiming) != cudaSuccess) return 0;
+        while (n < want) {
+            if (cudaStreamCreateWithFlags(&s[n], cudaStreamNonBlocking) != cudaSuccess) break;
+            if (cudaEventCreateWithFlags(&done[n], cudaEventDisableTiming) != cudaSuccess) break;
+            n++;
+        }
+        return n < want ? n : want;
+    }
+};
+static LanePool& lane_pool() {
+    static thread_local LanePool p;
+    return p;
+}
+static int render_lanes(int n_views) {
+    static int cfg = -1;
+    if (cfg < 0) {
+        const char* e = getenv("GSLM_RENDER_LANES");
+        cfg = e ? atoi(e) : 4;
+        if (cfg < 1) cfg = 1;
+    }
+    int k = cfg < n_views ? cfg : n_views;
+    if (stage_timing_enabled()) k = 1;      // the per-stage timers bracket one stream
+    return k;
 }
 
 // small grow-only pinned host buffer for the instance counts of a forward batch (so that the read-backs are truly
@@ -267,6 +304,27 @@ int32_t gslm_render_batch(const GslmGaussians* g, int32_t n_views, const GslmCam
     }
     cudaStream_t s = (cudaStream_t)stream;
     const int P = g->P;
+    // lanes: views are dealt round robin to K internal streams, each with its own image state and sort scratch
+    int K = render_lanes(n_views);
+    LanePool& pool = lane_pool();
+    if (K > 1) K = pool.get(K);
+    if (K < 1) K = 1;
+    const bool lanes = K > 1;
+    auto lane_stream = [&](int v) { return lanes ? pool.s[v % K] : s; };
+    auto fork_lanes = [&]() -> int {
+        if (!lanes) return 0;
+        GSLM_CUDA_OK(cudaEventRecord(pool.fork, s));
+        for (int k = 0; k < K; k++) GSLM_CUDA_OK(cudaStreamWaitEvent(pool.s[k], pool.fork, 0));
+        return 0;
+    };
+    auto join_lanes = [&]() -> int {
+        if (!lanes) return 0;
+        for (int k = 0; k < K; k++) {
+            GSLM_CUDA_OK(cudaEventRecord(pool.done[k], pool.s[k]));
+            GSLM_CUDA_OK(cudaStreamWaitEvent(s, pool.done[k], 0));
+        }
+        return 0;
+    };
     // one geometry allocation: n_views per-view states, the radii of views the caller does not want back, the totals
     const size_t gstride = align_up(gslm_geom_bytes(P)), rstride = align_up((size_t)P * sizeof(int32_t));
     size_t ibytes = 0;
@@ -276,20 +334,27 @@ int32_t gslm_render_batch(const GslmGaussians* g, int32_t n_views, const GslmCam
     }
     char* gbase = (char*)alloc(alloc_ctx, GSLM_BUF_GEOM,
                                128 + (size_t)n_views * (gstride + rstride) + align_up(n_views * sizeof(uint32_t)));
-    void* ibuf = alloc(alloc_ctx, GSLM_BUF_IMAGE, ibytes);      // reused view after view (stream order)
-    if (!gbase || !ibuf) { set_error("allocator returned null"); return 1; }
+    if (!gbase) { set_error("allocator returned null"); return 1; }
+    void* ibuf[LanePool::MAX] = {};
+    for (int k = 0; k < K; k++) {      // per lane, reused view after view in stream order
+        ibuf[k] = alloc(alloc_ctx, GSLM_BUF_IMAGE | (k << 8), ibytes);
+        if (!ibuf[k]) { set_error("allocator returned null"); return 1; }
+    }
     gbase = (char*)align_up((size_t)gbase);
     char* rbase = gbase + (size_t)n_views * gstride;
     uint32_t* totals = reinterpret_cast<uint32_t*>(rbase + (size_t)n_views * rstride);
     auto radii_of = [&](int v) { return (radii && radii[v]) ? radii[v] : reinterpret_cast<int32_t*>(rbase + v * rstride); };
     std::vector<uint32_t> R(n_views, 0u);
     if (P > 0) {
+        if (fork_lanes()) return 1;
         for (int v = 0; v < n_views; v++) {
+            cudaStream_t ls = lane_stream(v);
             GeomView gv = carve_geom(gbase + v * gstride, P);
-            if (launch_preprocess(*g, cams[v], gv, radii_of(v), s)) return 1;
-            if (cams[v].tile_culling && run_tile_cull(gv, radii_of(v), P, cams[v].width, cams[v].height, s)) return 1;
-            if (run_scan(gv, P, s)) return 1;
+            if (launch_preprocess(*g, cams[v], gv, radii_of(v), ls)) return 1;
+            if (cams[v].tile_culling && run_tile_cull(gv, radii_of(v), P, cams[v].width, cams[v].height, ls)) return 1;
+            if (run_scan(gv, P, ls)) return 1;
         }
+        if (join_lanes()) return 1;
         GeomView g0 = carve_geom(gbase, P);
         const size_t off = (size_t)((const char*)(g0.point_offsets + (P - 1)) - gbase);
         k_gather_totals<<<(n_views + 127) / 128, 128, 0, s>>>(gbase, gstride, off, n_views, totals);
@@ -300,20 +365,25 @@ int32_t gslm_render_batch(const GslmGaussians* g, int32_t n_views, const GslmCam
     }
     uint32_t Rmax = 0;
     for (int v = 0; v < n_views; v++) { num_rendered[v] = (int32_t)R[v]; Rmax = R[v] > Rmax ? R[v] : Rmax; }
-    void* tbuf = alloc(alloc_ctx, GSLM_BUF_BINNING_TEMP, gslm_binning_temp_bytes(P, Rmax));
-    if (!tbuf) { set_error("allocator returned null"); return 1; }
+    void* tbuf[LanePool::MAX] = {};
+    for (int k = 0; k < K; k++) {
+        tbuf[k] = alloc(alloc_ctx, GSLM_BUF_BINNING_TEMP | (k << 8), gslm_binning_temp_bytes(P, Rmax));
+        if (!tbuf[k]) { set_error("allocator returned null"); return 1; }
+    }
+    if (fork_lanes()) return 1;
     for (int v = 0; v < n_views; v++) {
         const GslmCamera& cam = cams[v];
+        cudaStream_t ls = lane_stream(v);
         GeomView gv = carve_geom(gbase + v * gstride, P);
-        ImageView iv = carve_image(ibuf, cam.width, cam.height);
-        BinningTemp bt = carve_binning_temp(tbuf, R[v], P);
-        if (run_binning(gv, radii_of(v), bt, iv, P, cam.width, cam.height, R[v], cam.tile_culling != 0, s)) return 1;
+        ImageView iv = carve_image(ibuf[v % K], cam.width, cam.height);
+        BinningTemp bt = carve_binning_temp(tbuf[v % K], R[v], P);
+        if (run_binning(gv, radii_of(v), bt, iv, P, cam.width, cam.height, R[v], cam.tile_culling != 0, ls)) return 1;
         const float* features = g->colors_precomp ? g->colors_precomp : gv.rgb;
         if (launch_blend_fwd(gv, bt, iv, cam.width, cam.height, features, cam.bg, out_color[v],
-                             out_invdepth ? out_invdepth[v] : nullptr, false, s)) return 1;
-        if (debug_sync(&cam, s, "render_batch")) return 1;
+                             out_invdepth ? out_invdepth[v] : nullptr, false, ls)) return 1;
+        if (debug_sync(&cam, ls, "render_batch")) return 1;
     }
-    return 0;
+    return join_lanes();
 }
 
 int32_t gslm_count_instances(const GslmGaussians* g, int32_t n_views, const GslmCamera* cams, GslmAllocFn alloc,
@@ -377,61 +447,90 @@ int32_t gslm_forward_batch(const GslmGaussians* g, int32_t n_views, const GslmCa
     uint32_t* R = host;
     uint32_t* Rc = host + n_views;
     for (int v = 0; v < 2 * n_views; v++) host[v] = 0u;
+    // lanes: views are dealt round robin to K >= 2 internal streams (one sort scratch each); see gslm_render_batch
+    int K = render_lanes(n_views);
+    if (K < 2 && !stage_timing_enabled()) K = n_views > 1 ? 2 : 1;
+    LanePool& pool = lane_pool();
+    if (K > 1) K = pool.get(K);
+    if (K < 1) K = 1;
+    const bool lanes = K > 1;
+    auto lane_stream = [&](int v) { return lanes ? pool.s[v % K] : s; };
+    auto fork_lanes = [&]() -> int {
+        if (!lanes) return 0;
+        GSLM_CUDA_OK(cudaEventRecord(pool.fork, s));
+        for (int k = 0; k < K; k++) GSLM_CUDA_OK(cudaStreamWaitEvent(pool.s[k], pool.fork, 0));
+        return 0;
+    };
+    auto join_lanes = [&]() -> int {
+        if (!lanes) return 0;
+        for (int k = 0; k < K; k++) {
+            GSLM_CUDA_OK(cudaEventRecord(pool.done[k], pool.s[k]));
+            GSLM_CUDA_OK(cudaStreamWaitEvent(s, pool.done[k], 0));
+        }
+        return 0;
+    };
     // phase 1: every view preprocessed, culled and scanned; ONE synchronisation for all instance counts
     if (P > 0) {
+        if (fork_lanes()) return 1;
         for (int v = 0; v < n_views; v++) {
-            if (launch_preprocess(*g, cams[v], gv[v], radii[v], s)) return 1;
-            if (cams[v].tile_culling && run_tile_cull(gv[v], radii[v], P, cams[v].width, cams[v].height, s)) return 1;
-            if (run_scan(gv[v], P, s)) return 1;
-            GSLM_CUDA_OK(cudaMemcpyAsync(R + v, gv[v].point_offsets + (P - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+            cudaStream_t ls = lane_stream(v);
+            if (launch_preprocess(*g, cams[v], gv[v], radii[v], ls)) return 1;
+            if (cams[v].tile_culling && run_tile_cull(gv[v], radii[v], P, cams[v].width, cams[v].height, ls)) return 1;
+            if (run_scan(gv[v], P, ls)) return 1;
+            GSLM_CUDA_OK(cudaMemcpyAsync(R + v, gv[v].point_offsets + (P - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, ls));
         }
+        if (join_lanes()) return 1;
         GSLM_CUDA_OK(cudaStreamSynchronize(s));
     }
     uint32_t Rmax = 0;
     for (int v = 0; v < n_views; v++) { num_rendered[v] = (int32_t)R[v]; Rmax = R[v] > Rmax ? R[v] : Rmax; }
-    // phase 2: bin + blend view v while the host waits for the compact count of view v - 1 (two sort scratches):
-    // the device never idles on a read-back
-    const int n_slots = n_views > 1 ? 2 : 1;
-    void* tbuf[2] = {nullptr, nullptr};
-    for (int k = 0; k < n_slots; k++) {
+    // phase 2, in rounds of K views: bin + blend + tile scan of the round's views are queued on their lanes, THEN the
+    // host waits for each view's compact count (sizes the persistent cache) and queues its compaction -- while it
+    // waits the device has the other lanes' work, and by the time it returns to a lane that lane's scratch is free
+    // again in stream order (compaction(v) precedes binning(v + K)).  With one lane (stage timers on) the wait is exposed.
+    void* tbuf[LanePool::MAX] = {};
+    for (int k = 0; k < K; k++) {
         tbuf[k] = alloc(alloc_ctx, GSLM_BUF_BINNING_TEMP | (k << 8), gslm_binning_temp_bytes(P, Rmax));
         if (!tbuf[k]) { set_error("allocator returned null"); return 1; }
     }
-    cudaEvent_t ev[2];
-    for (int k = 0; k < 2; k++) GSLM_CUDA_OK(cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming));
-    int rc = 0;
-    auto finish = [&](int u) -> int {
-        const GslmCamera& cam = cams[u];
-        const int T = ((cam.width + TILE_X - 1) / TILE_X) * ((cam.height + TILE_Y - 1) / TILE_Y);
-        (void)T;
-        GSLM_CUDA_OK(cudaEventSynchronize(ev[u & 1]));
-        num_cached[u] = (int32_t)Rc[u];
-        void* bbuf = alloc(alloc_ctx, GSLM_BUF_BINNING | (u << 8), gslm_binning_bytes(Rc[u]));
-        if (!bbuf) { set_error("allocator returned null"); return 1; }
-        BinningView bv = carve_binning(bbuf, Rc[u]);
-        BinningTemp bt = carve_binning_temp(tbuf[u % n_slots], R[u], P);
-        if (P > 0 && run_compaction(gv[u], bv, bt, iv[u], P, cam.width, cam.height, Rc[u], s)) return 1;
-        return 0;
-    };
-    for (int v = 0; v < n_views && !rc; v++) {
-        const GslmCamera& cam = cams[v];
-        const int W = cam.width, H = cam.height;
-        const int T = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
-        BinningTemp bt = carve_binning_temp(tbuf[v % n_slots], R[v], P);
-        const float* features = g->colors_precomp ? g->colors_precomp : gv[v].rgb;
-        rc = run_binning(gv[v], radii[v], bt, iv[v], P, W, H, R[v], cam.tile_culling != 0, s)
-             || launch_blend_fwd(gv[v], bt, iv[v], W, H, features, cam.bg, out_color[v],
-                                 out_invdepth ? out_invdepth[v] : nullptr, true, s)
-             || run_tile_scan(iv[v], W, H, s);
-        if (rc) break;
-        if (cudaMemcpyAsync(Rc + v, iv[v].cstart + T, sizeof(uint32_t), cudaMemcpyDeviceToHost, s) != cudaSuccess ||
-            cudaEventRecord(ev[v & 1], s) != cudaSuccess) { set_error("forward_batch: read-back failed"); rc = 1; break; }
-        if (epilogues && launch_residual_epilogue(out_color[v], W, H, epilogues[v], s)) { rc = 1; break; }
-        if (v >= 1) rc = finish(v - 1);
-        if (!rc && cam.debug) rc = debug_sync(&cam, s, "forward_batch");
+    cudaEvent_t ev[LanePool::MAX];
+    for (int k = 0; k < K; k++) GSLM_CUDA_OK(cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming));
+    int rc = fork_lanes();
+    for (int v0 = 0; v0 < n_views && !rc; v0 += K) {
+        const int n = (n_views - v0) < K ? (n_views - v0) : K;
+        for (int i = 0; i < n && !rc; i++) {
+            const int v = v0 + i;
+            const GslmCamera& cam = cams[v];
+            cudaStream_t ls = lane_stream(v);
+            const int W = cam.width, H = cam.height;
+            const int T = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+            BinningTemp bt = carve_binning_temp(tbuf[v % K], R[v], P);
+            const float* features = g->colors_precomp ? g->colors_precomp : gv[v].rgb;
+            rc = run_binning(gv[v], radii[v], bt, iv[v], P, W, H, R[v], cam.tile_culling != 0, ls)
+                 || launch_blend_fwd(gv[v], bt, iv[v], W, H, features, cam.bg, out_color[v],
+                                     out_invdepth ? out_invdepth[v] : nullptr, true, ls)
+                 || run_tile_scan(iv[v], W, H, ls);
+            if (rc) break;
+            if (cudaMemcpyAsync(Rc + v, iv[v].cstart + T, sizeof(uint32_t), cudaMemcpyDeviceToHost, ls) != cudaSuccess ||
+                cudaEventRecord(ev[v % K], ls) != cudaSuccess) { set_error("forward_batch: read-back failed"); rc = 1; break; }
+            if (epilogues && launch_residual_epilogue(out_color[v], W, H, epilogues[v], ls)) { rc = 1; break; }
+        }
+        for (int i = 0; i < n && !rc; i++) {
+            const int u = v0 + i;
+            const GslmCamera& cam = cams[u];
+            cudaStream_t ls = lane_stream(u);
+            if (cudaEventSynchronize(ev[u % K]) != cudaSuccess) { set_error("forward_batch: event wait failed"); rc = 1; break; }
+            num_cached[u] = (int32_t)Rc[u];
+            void* bbuf = alloc(alloc_ctx, GSLM_BUF_BINNING | (u << 8), gslm_binning_bytes(Rc[u]));
+            if (!bbuf) { set_error("allocator returned null"); rc = 1; break; }
+            BinningView bv = carve_binning(bbuf, Rc[u]);
+            BinningTemp bt = carve_binning_temp(tbuf[u % K], R[u], P);
+            if (P > 0 && run_compaction(gv[u], bv, bt, iv[u], P, cam.width, cam.height, Rc[u], ls)) { rc = 1; break; }
+            if (cam.debug) rc = debug_sync(&cam, ls, "forward_batch");
+        }
     }
-    if (!rc) rc = finish(n_views - 1);
-    for (int k = 0; k < 2; k++) cudaEventDestroy(ev[k]);
+    if (join_lanes()) rc = 1;
+    for (int k = 0; k < K; k++) cudaEventDestroy(ev[k]);
     return rc;
 }
 

@@ -109,13 +109,18 @@ __device__ __forceinline__ float ex2_approx(float x) {
 
 // forward.cu:354-369 / backward.cu:561-569: power, G = exp(power), alpha = min(0.99, o G) and the two
 // skip tests, q0 = (x, y, conic.x, conic.y), q1 = (conic.z, opacity, ., .).
-// The image is a DISCONTINUOUS function of alpha at the 1/255 and T < 1e-4 thresholds, so the roundings follow
-// the reference's own instruction sequence (nvcc's contraction of forward.cu:358:
-// power = fma(-0.5, fma(C dy, dy, (A dx) dx), -((B dx) dy)), exp = ex2(power log2e)); a cheaper reassociation flips
-// enough threshold decisions to move isolated pixels by 1e-3.  It is split in a part shared by the pixels of one
-// image column (alpha_column: dx, e = (A dx) dx, f = B dx) and a per-pixel part (alpha_pixel), and every
-// operation is explicitly rounded so that the primal, tangent and adjoint sweeps -- whatever their
-// pixel-to-thread mapping -- reproduce the same bits and therefore the same hit / skip decisions.
+// The image is a DISCONTINUOUS function of alpha at the 1/255 and T < 1e-4 thresholds, so `power` follows the
+// reference's own instruction sequence bit for bit (nvcc's contraction of forward.cu:358:
+// power = fma(-0.5, fma(C dy, dy, (A dx) dx), -((B dx) dy))); a cheaper reassociation flips enough threshold decisions
+// to move isolated pixels by 1e-3.  The exponential itself is ex2.approx(power log2e) where the reference (built
+// without -use_fast_math) calls libdevice expf: a few ulp apart, so alpha, the image and final_T agree with the
+// reference's kernels to rel 1e-4 but are NOT bit-identical, and a pixel whose alpha lies within that distance of
+// 1/255 can take one blend the reference skips (or vice versa) -- tests/test_gpu_vs_reference.py bounds both; only
+// the binning (radii, tiles_touched, point_list, ranges) is bit-exact.  The evaluation is split in a
+// part shared by the pixels of one image column (alpha_column: dx, e = (A dx) dx, f = B dx) and a per-pixel part
+// (alpha_pixel), and every operation is explicitly rounded so that every kernel of THIS library -- whatever its
+// pixel-to-thread mapping, with or without tile culling -- reproduces the same bits and therefore the same hit /
+// skip decisions.
 __device__ __forceinline__ void alpha_column(const float4& q0, float pxf, float& dx, float& e, float& f) {
     dx = __fsub_rn(q0.x, pxf);
     e = __fmul_rn(__fmul_rn(q0.z, dx), dx);

@@ -119,6 +119,7 @@ enum Stage { ST_PREPROCESS = 0, ST_SCAN, ST_KEYS, ST_SORT, ST_RANGES, ST_GATHER,
              ST_BLEND_JVP, ST_BLEND_BWD, ST_BLEND_JTJV, ST_PRE_BWD, ST_LOSS, ST_ACTIVATION, ST_COUNT };
 void stage_begin(int stage, cudaStream_t s);   // no-ops unless timing is enabled
 void stage_end(int stage, cudaStream_t s);
+bool stage_timing_enabled();
 struct StageScope {
     int st; cudaStream_t s;
     StageScope(int st_, cudaStream_t s_) : st(st_), s(s_) { stage_begin(st, s); }

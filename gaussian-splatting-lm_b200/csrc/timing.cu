@@ -49,6 +49,7 @@ void stage_begin(int stage, cudaStream_t s) {
     g_open[stage] = p;
     g_is_open[stage] = true;
 }
+bool stage_timing_enabled() { return g_on; }
 void stage_end(int stage, cudaStream_t s) {
     if (t_nvtx_depth > 0) { nvtxRangePop(); t_nvtx_depth--; }
     if (!g_on) return;

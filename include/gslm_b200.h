@@ -143,8 +143,10 @@ int32_t gslm_render(const GslmGaussians* g, const GslmCamera* cam, GslmAllocFn a
  * diff_gaussian_rasterization/batch_render.py:171-213).  This is the evaluation the back-tracking line search repeats
  * for every step size (train_jvp.py:262-279).  cams / out_color / num_rendered: HOST arrays of n_views entries;
  * out_invdepth and radii may be NULL (or hold NULL entries): the radii then live in the geometry allocation.
- * The allocator is asked once for GSLM_BUF_GEOM (all views), once for GSLM_BUF_IMAGE (largest view, reused) and
- * once for GSLM_BUF_BINNING_TEMP (largest view).  Results are bit-identical to n_views gslm_render calls. */
+ * Independent views are issued on up to 4 internal streams ("lanes", forked from and joined to `stream` with events;
+ * GSLM_RENDER_LANES overrides) so that the many short launches of small scenes overlap.  The allocator is asked once
+ * for GSLM_BUF_GEOM (all views) and, per lane k, for GSLM_BUF_IMAGE | (k << 8) (largest view, reused) and
+ * GSLM_BUF_BINNING_TEMP | (k << 8) (largest view).  Results are bit-identical to n_views gslm_render calls. */
 int32_t gslm_render_batch(const GslmGaussians* g, int32_t n_views, const GslmCamera* cams, GslmAllocFn alloc,
                           void* alloc_ctx, float* const* out_color, float* const* out_invdepth, int32_t* const* radii,
                           int32_t* num_rendered, void* stream);
@@ -177,10 +179,11 @@ typedef struct GslmResidualEpilogue {
  * for the passes that are differentiated afterwards (LinearSolverFunctions.linearize; the reference renders its views
  * one by one with a host synchronisation each, rasterizer_impl.cu:325, DGR/diff_gaussian_rasterization/batch_render.py:
  * 171-213).  Every view is preprocessed and scanned first and all instance counts come back with ONE synchronisation;
- * then view v is binned and blended while the host waits for the compact count of view v - 1 (two alternating sort
- * scratches), so the device never idles on a read-back.  The allocator is called with
+ * then the views are binned and blended in rounds on up to 4 internal streams ("lanes", as in gslm_render_batch), and
+ * the host waits for a view's compact count only after the whole round is queued, so the device never idles on a
+ * read-back.  The allocator is called with
  *   which = kind | (view << 8)   for GSLM_BUF_GEOM, GSLM_BUF_IMAGE, GSLM_BUF_BINNING (one each per view), and
- *   which = GSLM_BUF_BINNING_TEMP | (slot << 8), slot = 0, 1   for the sort scratches (dead when the call returns).
+ *   which = GSLM_BUF_BINNING_TEMP | (lane << 8)   for the sort scratches (dead when the call returns).
  * out_color / radii / num_rendered / num_cached: HOST arrays of n_views entries (radii entries must be non-NULL);
  * out_invdepth and epilogues may be NULL.  Buffers and results are bit-identical to n_views gslm_forward calls. */
 int32_t gslm_forward_batch(const GslmGaussians* g, int32_t n_views, const GslmCamera* cams, GslmAllocFn alloc,
