@@ -38,12 +38,19 @@ template <bool ACC> __device__ __forceinline__ void put(float* p, size_t i, floa
 }
 
 // the whole per-Gaussian adjoint of Gaussian idx for the view described by (a, sV, sPV, sCam)
-template <bool ACC>
+// PHASED (the dense multi-view kernel): lanes of one warp may hold the SAME Gaussian for different views.  Everything
+// up to the two store sites runs concurrently; at each store site the lanes take turns in view order (`rank` among the
+// lanes with equal idx, `maxrank` its warp maximum, `callmask` the lanes inside this call), so the read-modify-write
+// sequence on a row is exactly the view-by-view sequence of the unphased kernel: same bits.
+template <bool ACC, bool PHASED = false>
 __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __restrict__ sV, const float* __restrict__ sPV,
-                                             const float* __restrict__ sCam, int idx) {
+                                             const float* __restrict__ sCam, int idx, uint32_t callmask = 0xffffffffu,
+                                             int rank = 0, int maxrank = 0) {
     const size_t i = idx;
     const int ncoef = a.shs ? a.M : 0;
     const uint32_t beg = a.g_off[idx], end = a.g_off[idx + 1];
+    uint32_t syncmask = callmask;
+    if (PHASED) syncmask = __ballot_sync(callmask, !(a.radii[idx] <= 0 || beg == end));
     // culled, or visible but blended by no pixel: every gradient is exactly zero
     if (a.radii[idx] <= 0 || beg == end) {
         if (!ACC) {  // overwrite mode: culled Gaussians get exact zeros
@@ -257,19 +264,29 @@ __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __re
             // coefficients >= used have bv = 0: accumulate mode skips those chunks, overwrite mode stores zeros.
             // All loads of the row are issued before its first store: the sinks are not __restrict__, a load placed
             // after a store would wait for it (12 dependent round trips per Gaussian instead of one).
-            float4 q[12];
+            auto update_row = [&]() {
+                float4 q[12];
 #pragma unroll
-            for (int c = 0; c < 12; c++)
-                q[c] = (ACC && 4 * c < 3 * used && 4 * c < 3 * a.M) ? d4[c] : make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int c = 0; c < 12; c++)
+                    q[c] = (ACC && 4 * c < 3 * used && 4 * c < 3 * a.M) ? d4[c] : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-            for (int c = 0; c < 12; c++) {
-                if ((!ACC || 4 * c < 3 * used) && 4 * c < 3 * a.M) {
-                    q[c].x += bv[(4 * c) / 3] * g3[(4 * c) % 3];
-                    q[c].y += bv[(4 * c + 1) / 3] * g3[(4 * c + 1) % 3];
-                    q[c].z += bv[(4 * c + 2) / 3] * g3[(4 * c + 2) % 3];
-                    q[c].w += bv[(4 * c + 3) / 3] * g3[(4 * c + 3) % 3];
-                    d4[c] = q[c];
+                for (int c = 0; c < 12; c++) {
+                    if ((!ACC || 4 * c < 3 * used) && 4 * c < 3 * a.M) {
+                        q[c].x += bv[(4 * c) / 3] * g3[(4 * c) % 3];
+                        q[c].y += bv[(4 * c + 1) / 3] * g3[(4 * c + 1) % 3];
+                        q[c].z += bv[(4 * c + 2) / 3] * g3[(4 * c + 2) % 3];
+                        q[c].w += bv[(4 * c + 3) / 3] * g3[(4 * c + 3) % 3];
+                        d4[c] = q[c];
+                    }
                 }
+            };
+            if (PHASED) {
+                for (int ph = 0; ph <= maxrank; ph++) {
+                    if (rank == ph) update_row();
+                    __syncwarp(syncmask);
+                }
+            } else {
+                update_row();
             }
         }
         if (!ACC && dsh && !vecd)
@@ -336,33 +353,43 @@ __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __re
     const bool w_sr = a.scales != nullptr || !ACC;     // without scales the overwrite mode still stores zeros
     float* const sc = w_sr ? a.g.dL_dscales : nullptr;
     float* const rq = w_sr ? a.g.dL_drotations : nullptr;
-    auto ld = [&](const float* p, size_t j) { return (ACC && p) ? p[j] : 0.f; };
-    float o_sr[7], o_m2[2], o_col[3], o_m3[3], o_cov[6];
+    auto update_small = [&]() {
+        auto ld = [&](const float* p, size_t j) { return (ACC && p) ? p[j] : 0.f; };
+        float o_sr[7], o_m2[2], o_col[3], o_m3[3], o_cov[6];
 #pragma unroll
-    for (int k = 0; k < 3; k++) o_sr[k] = ld(sc, 3 * i + k);
+        for (int k = 0; k < 3; k++) o_sr[k] = ld(sc, 3 * i + k);
 #pragma unroll
-    for (int k = 0; k < 4; k++) o_sr[3 + k] = ld(rq, 4 * i + k);
-    o_m2[0] = ld(a.g.dL_dmeans2D, 3 * i); o_m2[1] = ld(a.g.dL_dmeans2D, 3 * i + 1);
+        for (int k = 0; k < 4; k++) o_sr[3 + k] = ld(rq, 4 * i + k);
+        o_m2[0] = ld(a.g.dL_dmeans2D, 3 * i); o_m2[1] = ld(a.g.dL_dmeans2D, 3 * i + 1);
 #pragma unroll
-    for (int k = 0; k < 3; k++) { o_col[k] = ld(a.g.dL_dcolors, 3 * i + k); o_m3[k] = ld(a.g.dL_dmeans3D, 3 * i + k); }
-    const float o_op = ld(a.g.dL_dopacity, i);
+        for (int k = 0; k < 3; k++) { o_col[k] = ld(a.g.dL_dcolors, 3 * i + k); o_m3[k] = ld(a.g.dL_dmeans3D, 3 * i + k); }
+        const float o_op = ld(a.g.dL_dopacity, i);
 #pragma unroll
-    for (int k = 0; k < 6; k++) o_cov[k] = ld(a.g.dL_dcov3D, 6 * i + k);
-    auto st = [&](float* p, size_t j, float old, float v) { if (p) p[j] = ACC ? old + v : v; };
+        for (int k = 0; k < 6; k++) o_cov[k] = ld(a.g.dL_dcov3D, 6 * i + k);
+        auto st = [&](float* p, size_t j, float old, float v) { if (p) p[j] = ACC ? old + v : v; };
 #pragma unroll
-    for (int k = 0; k < 3; k++) st(sc, 3 * i + k, o_sr[k], sr[k]);
+        for (int k = 0; k < 3; k++) st(sc, 3 * i + k, o_sr[k], sr[k]);
 #pragma unroll
-    for (int k = 0; k < 4; k++) st(rq, 4 * i + k, o_sr[3 + k], sr[3 + k]);
-    st(a.g.dL_dmeans2D, 3 * i, o_m2[0], g2x);
-    st(a.g.dL_dmeans2D, 3 * i + 1, o_m2[1], g2y);
-    if (!ACC) st(a.g.dL_dmeans2D, 3 * i + 2, 0.f, 0.f);
+        for (int k = 0; k < 4; k++) st(rq, 4 * i + k, o_sr[3 + k], sr[3 + k]);
+        st(a.g.dL_dmeans2D, 3 * i, o_m2[0], g2x);
+        st(a.g.dL_dmeans2D, 3 * i + 1, o_m2[1], g2y);
+        if (!ACC) st(a.g.dL_dmeans2D, 3 * i + 2, 0.f, 0.f);
 #pragma unroll
-    for (int k = 0; k < 3; k++) st(a.g.dL_dcolors, 3 * i + k, o_col[k], dcol[k]);
-    st(a.g.dL_dopacity, i, o_op, dL_dop);
+        for (int k = 0; k < 3; k++) st(a.g.dL_dcolors, 3 * i + k, o_col[k], dcol[k]);
+        st(a.g.dL_dopacity, i, o_op, dL_dop);
 #pragma unroll
-    for (int k = 0; k < 3; k++) st(a.g.dL_dmeans3D, 3 * i + k, o_m3[k], dmean[k]);
+        for (int k = 0; k < 3; k++) st(a.g.dL_dmeans3D, 3 * i + k, o_m3[k], dmean[k]);
 #pragma unroll
-    for (int k = 0; k < 6; k++) st(a.g.dL_dcov3D, 6 * i + k, o_cov[k], dcov[k]);
+        for (int k = 0; k < 6; k++) st(a.g.dL_dcov3D, 6 * i + k, o_cov[k], dcov[k]);
+    };
+    if (PHASED) {
+        for (int ph = 0; ph <= maxrank; ph++) {
+            if (rank == ph) update_small();
+            __syncwarp(syncmask);
+        }
+    } else {
+        update_small();
+    }
 }
 
 template <bool ACC>
@@ -465,6 +492,75 @@ k_preprocess_bwd_views(BwdArgs a, const __grid_constant__ BwdBatch vb, int range
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Dense variant (round 2).  The kernel above gives every view its own pass over the warp's slice of that view's active
+// list: ~20 of the 256 Gaussians of a range are active per view, so a pass keeps ~20 of 32 lanes busy and the stage is
+// 16 dependent-latency passes per launch.  Here the (view, active Gaussian) items of the range are ONE list in
+// view-major order (prefix sums of the 16 slice lengths, per warp, in shared memory) and the lanes take 32 consecutive
+// items per pass whatever view they belong to: ~10 full passes instead of 16 two-thirds-empty ones.  Two lanes of a pass
+// can then hold the same Gaussian (for different views): __match_any_sync finds them and the PHASED store sites of
+// bwd_gaussian let them update the row in view order, so the sums are taken in exactly the old order (same bits).
+// ---------------------------------------------------------------------------------------------
+#ifndef GSLM_BWDV_DENSE
+#define GSLM_BWDV_DENSE 1
+#endif
+__global__ void __launch_bounds__(128, GSLM_BWDV_MINB)
+k_preprocess_bwd_views_dense(BwdArgs a, const __grid_constant__ BwdBatch vb, int range_lo, int range_hi) {
+    __shared__ float sCamAll[MAX_BATCH_VIEWS][36];   // V[16] | PV[16] | campos[3]
+    __shared__ BwdView sView[MAX_BATCH_VIEWS];
+    __shared__ uint32_t sLo[4][MAX_BATCH_VIEWS], sCum[4][MAX_BATCH_VIEWS + 1];
+    for (int t = threadIdx.x; t < vb.n * 36; t += blockDim.x) {
+        const int v = t / 36, k = t % 36;
+        const BwdView& vw = vb.v[v];
+        float x = 0.f;
+        if (k < 16) x = vw.viewmatrix[k];
+        else if (k < 32) x = vw.projmatrix[k - 16];
+        else if (k < 35 && vw.campos) x = vw.campos[k - 32];
+        sCamAll[v][k] = x;
+    }
+    if ((int)threadIdx.x < vb.n) sView[threadIdx.x] = vb.v[threadIdx.x];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int r = range_lo + blockIdx.x * (blockDim.x >> 5) + w;
+    if (r >= range_hi) return;
+    // the range's slice of every view's active list and the prefix sums of the slice lengths
+    uint32_t lo = 0, cnt = 0;
+    if (lane < vb.n) {
+        lo = __ldg(sView[lane].act_range + r);
+        cnt = __ldg(sView[lane].act_range + r + 1) - lo;
+    }
+    uint32_t inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += up;
+    }
+    if (lane < vb.n) { sLo[w][lane] = lo; sCum[w][lane + 1] = inc; }
+    if (lane == 0) sCum[w][0] = 0;
+    const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+    __syncwarp();
+    for (uint32_t base = 0; base < total; base += 32) {
+        const uint32_t t = base + lane;
+        const bool valid = t < total;
+        const uint32_t callmask = __ballot_sync(0xffffffffu, valid);
+        if (valid) {
+            int v = 0;
+            while (v + 1 < vb.n && sCum[w][v + 1] <= t) v++;
+            const BwdView& vw = sView[v];
+            const int idx = (int)__ldg(vw.active_ids + sLo[w][v] + (t - sCum[w][v]));
+            const uint32_t same = __match_any_sync(callmask, idx);
+            const int rank = __popc(same & ((1u << lane) - 1u));
+            const int maxrank = __reduce_max_sync(callmask, rank);
+            BwdArgs b = a;
+            b.W = vw.W; b.H = vw.H; b.tan_fovx = vw.tan_fovx; b.tan_fovy = vw.tan_fovy;
+            b.radii = vw.radii; b.clamped = vw.clamped; b.g_off = vw.g_off; b.inst_grads = vw.inst_grads;
+            if (vw.cov3D) b.cov3D = vw.cov3D;
+            bwd_gaussian<true, true>(b, sCamAll[v], sCamAll[v] + 16, sCamAll[v] + 32, idx, callmask, rank, maxrank);
+        }
+        __syncwarp();   // the next pass may touch a row of this one from another lane
+    }
+}
+
 static void fill_common(BwdArgs& a, const GslmGaussians& g, const GslmCamera& cam, bool has_invdepth_grad,
                         const GslmGrads& grads) {
     a.P = g.P; a.D = g.sh_degree; a.M = g.M; a.W = cam.width; a.H = cam.height;
@@ -522,7 +618,14 @@ int launch_preprocess_bwd_views(const GslmGaussians& g, int n_views, const GslmC
     if (range_lo < 0) range_lo = 0;
     if (range_lo >= range_hi) return 0;
     StageScope ts(ST_PRE_BWD, s);
-    k_preprocess_bwd_views<<<(range_hi - range_lo + 3) / 4, 128, 0, s>>>(a, vb, range_lo, range_hi, zero_first ? 1 : 0);
+    // the dense kernel's phased stores cover the float4 SH-row path only (M % 4 == 0, 16-byte aligned rows) -- every
+    // degree-0 / degree-3 layout the solver produces; anything else takes the per-view passes
+    const bool dense = GSLM_BWDV_DENSE && !zero_first &&
+                       (!grads.dL_dsh || !a.shs || ((g.M & 3) == 0 && (reinterpret_cast<size_t>(grads.dL_dsh) & 15u) == 0));
+    if (dense)
+        k_preprocess_bwd_views_dense<<<(range_hi - range_lo + 3) / 4, 128, 0, s>>>(a, vb, range_lo, range_hi);
+    else
+        k_preprocess_bwd_views<<<(range_hi - range_lo + 3) / 4, 128, 0, s>>>(a, vb, range_lo, range_hi, zero_first ? 1 : 0);
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
 }

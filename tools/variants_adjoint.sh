@@ -1,6 +1,6 @@
 #!/bin/bash
 # usage: tools/variants_adjoint.sh "<EXTRA flags 1>" ...   (GPU box; full rebuild per variant: ACT_RANGE lives in the common header)
-cd /root/repo
+cd "$(dirname "$0")/.."
 for v in "$@"; do
   touch gaussian-splatting-lm_b200/csrc/gslm_common.cuh
   make -C gaussian-splatting-lm_b200/csrc EXTRA="$v" -j16 > /dev/null 2>&1 || { echo "build failed: $v"; continue; }
