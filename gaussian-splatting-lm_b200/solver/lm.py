@@ -75,7 +75,9 @@ def cg_normal_equations(F, damp=None, max_iter=2, tol=1e-10, rhs=None, x0=None, 
 
     g = None
     for k in range(max_iter):
-        if graph and k == 1 and max_iter > 2 and callback is None:
+        # (multi-GPU products end in a symmetric-memory barrier + multimem kernel or an NCCL call on the caller's
+        # stream; their capture is not exercised on hardware here, so the graph is a single-GPU feature for now)
+        if graph and k == 1 and max_iter > 2 and callback is None and getattr(F, "dist", None) is None:
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 iteration()
