@@ -708,14 +708,17 @@ class LinearSolverFunctions:
 
 
 class _ProductTail:
-    """Callable handed to the library as the per-slice callback of gslm_jtjv_batch_sliced / gslm_backward_batch_sliced.
+    """Callable handed to the library as the per-slice callback of gslm_jtjv_batch_sliced / gslm_backward_batch_sliced:
+    the end of every parameter-space product.
 
     Single GPU: one call for [0, P): the activation VJP (+ damping) on the caller's stream.
-    Multi-GPU: the library cuts the last adjoint launch into N_SLICES Gaussian ranges; after each launch this object
-    records an event on the compute stream and, on a communication stream, (1) all-reduces the five row blocks of the
-    slice (means3D, shs, scales, rotations, opacities rows [g_lo, g_hi)) as ONE grouped NCCL call and (2) runs the
-    activation VJP of the slice -- so the reduction of slice k and its VJP overlap the production of slice k + 1, and
-    only the last slice's collective is exposed.  finish() joins the streams and returns the masked raw-space state."""
+    Multi-GPU, N_SLICES == 1 (default): one call for [0, P) on the caller's stream: the sum over ranks -- in place on
+    the symmetric accumulator through this library's multimem kernel (csrc/peer_reduce.cu) from 3 ranks up, one NCCL
+    allreduce otherwise -- then the activation VJP.
+    Multi-GPU, N_SLICES > 1 (kept for measurement, slower on B200: DESIGN.md 5): the library cuts the last adjoint
+    launch into Gaussian ranges; after each launch this object records an event on the compute stream and, on a
+    communication stream, all-reduces the five row blocks of the range as ONE grouped NCCL call and runs the
+    activation VJP of the range.  finish() joins the streams and returns the masked raw-space state."""
 
     _GROUPS = ("means3D", "shs", "scales", "rotations", "opacities")
 

@@ -480,3 +480,27 @@ def test_densification_bookkeeping_matches_the_reference_lines():
     assert torch.equal(model.max_radii2D, ref_max.view(-1))
     assert torch.equal(model.denom, ref_den)
     assert h.rel_l2(model.xyz_gradient_accum.cpu().numpy(), ref_acc.cpu().numpy()) < 1e-3
+
+
+def test_host_pipeline_streams_host_vectors_through_the_product():
+    """solver.HostPipeline (bench.py's end-to-end leg): host-resident vectors go through normal_matvec with the copies
+    double-buffered on side streams -- every result equals the device-resident product of the same vector, bit for bit,
+    also when the host reuses its buffers as soon as submit() returns the slot."""
+    from solver.solver_functions import LinearSolverFunctions
+    model, cams, loss_func, pipe, bg = _setup(P=3000)
+    F = LinearSolverFunctions(loss_func, model, cams, batch_size=2)
+    F.evaluate_loss()
+    states = [_rand_state(model, 20 + k) for k in range(5)]
+    want = [F.normal_matvec(s).packed().clone() for s in states]
+    n = states[0].length
+    ins = [torch.empty(n).pin_memory() for _ in states]
+    outs = [torch.empty(n).pin_memory() for _ in states]
+    for h_in, s in zip(ins, states):
+        h_in.copy_(s.packed().cpu())
+    hp = F.host_pipeline(depth=2)
+    for h_in, h_out in zip(ins, outs):
+        hp.submit(h_in, h_out)
+    hp.flush()
+    for k in range(len(states)):
+        assert torch.equal(outs[k].cuda(), want[k]), k
+    assert hp.bytes_in == 4 * n and hp.bytes_out == 4 * n
