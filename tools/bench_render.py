@@ -92,6 +92,13 @@ def main():
                     row["ref_fwd_ms"] = timed(lambda: gs_ref.forward(gr, ct, antialiasing=aa), a.iters)
                     Rr, cr, ir, rr = gs_ref.forward(gr, ct, antialiasing=aa)
                     row["ref_bwd_ms"] = timed(lambda: gs_ref.backward(gr, ct, rr, u, antialiasing=aa), a.iters)
+                    if gs_ref.has_jvp():
+                        # the reference's own forward-mode pass (forwardJvp = primal + tangent in one sweep, built with
+                        # the functional float_grad.h stand-in of oracle/ref_shim): what its matvec costs per view
+                        tg = {k: t[k] for k in ("means3D", "opacities", "scales", "rotations", "shs")}
+                        row["ref_fwd_jvp_ms"] = timed(lambda: gs_ref.forward_jvp(gr, ct, tg=tg, antialiasing=aa), max(2, a.iters // 2))
+                        row["ref_jtjv_composed_ms"] = row["ref_fwd_jvp_ms"] + row["ref_bwd_ms"]
+                        row["jtjv_speedup"] = row["ref_jtjv_composed_ms"] / row["ours_jtjv_cached_ms"]
                     row["fwd_speedup"] = row["ref_fwd_ms"] / row["ours_fwd_ms"]
                     row["fwd_batch_speedup"] = row["ref_fwd_ms"] / row["ours_fwd_batch_ms_per_view"]
                     row["bwd_speedup"] = row["ref_bwd_ms"] / row["ours_bwd_ms"]
@@ -100,11 +107,11 @@ def main():
                 rows.append(row)
                 del fwd, geom, binning, img, plan, outs
                 torch.cuda.empty_cache()
-    print(f"\n{'P':>9} {'deg':>3} {'aa':>2} {'R':>10} {'Rc':>9} | {'fwd':>7} {'fwd/16':>7} {'bwd':>7} {'Jv':>7} {'JtJv':>7} | {'ref fwd':>8} {'ref bwd':>8} | fwd+bwd  fwd(batch) speed-up")
+    print(f"\n{'P':>9} {'deg':>3} {'aa':>2} {'R':>10} {'Rc':>9} | {'fwd':>7} {'fwd/16':>7} {'bwd':>7} {'Jv':>7} {'JtJv':>7} | {'ref fwd':>8} {'ref bwd':>8} | fwd+bwd  fwd(batch) speed-up | ref fwdJvp  JtJv speed-up")
     for r in rows:
         print(f"{r['P']:9d} {r['sh_degree']:3d} {int(r['antialiasing']):2d} {r['R']:10d} {r['Rc']:9d} | "
               f"{r['ours_fwd_ms']:7.3f} {r['ours_fwd_batch_ms_per_view']:7.3f} {r['ours_bwd_ms']:7.3f} {r['ours_jvp_cached_ms']:7.3f} {r['ours_jtjv_cached_ms']:7.3f} | "
-              f"{r.get('ref_fwd_ms', float('nan')):8.3f} {r.get('ref_bwd_ms', float('nan')):8.3f} | {r.get('fwd_bwd_speedup', float('nan')):5.2f}x   {r.get('fwd_batch_speedup', float('nan')):5.2f}x")
+              f"{r.get('ref_fwd_ms', float('nan')):8.3f} {r.get('ref_bwd_ms', float('nan')):8.3f} | {r.get('fwd_bwd_speedup', float('nan')):5.2f}x   {r.get('fwd_batch_speedup', float('nan')):5.2f}x | {r.get('ref_fwd_jvp_ms', float('nan')):8.3f}   {r.get('jtjv_speedup', float('nan')):6.1f}x")
 
 
 if __name__ == "__main__":
