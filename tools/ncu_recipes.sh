@@ -30,7 +30,7 @@ case "$recipe" in
   adjoint)    # per-Gaussian stages of the CG iteration (profiles/*_pergauss_ncu_full.txt)
     $BENCH > "$out/${tag}_bench_plain.json"
     ncu --set full --clock-control none --import-source on \
-        -k "regex:k_preprocess_bwd_views|k_preprocess_tangent|k_activation" --launch-skip 6 --launch-count 5 $extra \
+        -k "regex:k_preprocess_bwd_views|k_preprocess_tangent|k_activation|k_multimem" --launch-skip 6 --launch-count 5 $extra \
         -o "$out/${tag}_pergauss" -f $BENCH > "$out/${tag}_pergauss.log" 2>&1
     ;;
   forward)    # primal path at 1M Gaussians / 1080p with tile culling (profiles/*_fwd_*_ncu_full.txt)
