@@ -103,3 +103,21 @@ def test_utils_tangent_helpers():
         d = fwAD.make_dual(x, 2 * x)
         assert has_tangent(d) and has_tangent([x, d])
         assert torch.equal(get_tangent(d), 2 * x)
+
+
+def test_argument_validation_without_a_gpu(lib):
+    """Entry points reject malformed arguments before touching the device: checked here on the CPU-only box."""
+    lib.gslm_last_error.restype = ctypes.c_char_p
+    lib.gslm_multimem_allreduce_f32.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int32, ctypes.c_int32,
+                                                ctypes.c_void_p]
+    assert lib.gslm_multimem_allreduce_f32(None, 1024, 0, 2, None) != 0            # no multicast mapping
+    assert b"multimem" in lib.gslm_last_error()
+    assert lib.gslm_multimem_allreduce_f32(ctypes.c_void_p(4096), 1023, 0, 2, None) != 0   # n not a multiple of 4
+    assert lib.gslm_multimem_allreduce_f32(ctypes.c_void_p(4096), 1024, 2, 2, None) != 0   # rank outside the world
+    assert lib.gslm_multimem_allreduce_f32(ctypes.c_void_p(4100), 1024, 0, 2, None) != 0   # misaligned buffer
+    lib.gslm_forward_batch.argtypes = [ctypes.c_void_p] + [ctypes.c_int32] + [ctypes.c_void_p] * 10
+    assert lib.gslm_forward_batch(None, 1, None, None, None, None, None, None, None, None, None, None) != 0
+    lib.gslm_densification_stats.argtypes = [ctypes.c_int32] + [ctypes.c_void_p] * 6
+    assert lib.gslm_densification_stats(10, None, None, None, None, None, None) != 0
+    assert lib.gslm_densification_stats(0, None, None, None, None, None, None) == 0      # empty model: nothing to do
+    assert lib.gslm_abi_version() >= 3
