@@ -66,11 +66,13 @@ def cg_normal_equations(F, damp=None, max_iter=2, tol=1e-10, rhs=None, x0=None, 
         pAp = torch.dot(p, Apf)
         live = (rs > (tol * tol) * rs0) & (pAp > tiny)
         alpha = torch.where(live, rs / pAp.clamp_min(tiny), torch.zeros_like(rs))
-        x.add_(alpha * p)
-        r.sub_(alpha * Apf)
+        # one pass per vector update (the scalar stays on the device and is broadcast inside the kernel): 13 sweeps
+        # over the 59 P floats per iteration instead of 20 with temporaries
+        x.addcmul_(alpha, p)                          # x += alpha p
+        r.addcmul_(alpha, Apf, value=-1.0)            # r -= alpha A p
         rs_new = torch.dot(r, r)
         beta = torch.where(live, rs_new / rs.clamp_min(tiny), torch.zeros_like(rs))
-        p.mul_(beta).add_(r)
+        torch.addcmul(r, beta, p, out=p)              # p = r + beta p
         rs.copy_(rs_new)
 
     g = None
