@@ -8,7 +8,7 @@ A "step" = one Gauss-Newton product J^T J v over ALL views of the workload (conf
 LinearSolverFunctions.normal_matvec -- per view: tangent preprocess, the fused tangent->adjoint tile kernel,
 the per-Gaussian adjoint kernel; then (N > 1) ONE NCCL allreduce of the packed 59 P-float result.  The
 linearisation (forward render, sort, records) is done once before the timed region, exactly as in an LM step
-where one linearisation serves the whole CG solve; its cost is reported separately (`linearize_ms`).
+where one linearisation serves the whole CG solve; its cost is reported separately (`workload_stats.linearize_ms`).
 Views are sharded round-robin over ranks (strong scaling: the total work is fixed).
 
 value  : matvecs/s with v already resident in HBM (device-timed with CUDA events, max over ranks).
@@ -121,7 +121,8 @@ def run_reference(a):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": len(times),
         "warmup": a.warmup, "ms_per_step": per_view * V * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(a, P, V, W, H)},
+        "config": {"workload": workload_name(a, P, V, W, H), "mask_xyz": bool(a.mask_xyz),
+                   "l2_policy": "inputs larger than L2 (per-view records + gradients >> 126 MB)"},
         "ms_per_step_extrapolated": True, "measured_s": sum(times),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -402,15 +403,17 @@ def main():
         "metric": METRIC, "value": 1e3 / ms_step, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": workload_name(a, P, V, W, H), "views_per_rank": len(F._views),
-                   "instances_total_rank0": R_total, "instances_cached_rank0": R_cached,
-                   "visible_gaussians_per_view_mean_rank0": (sum(p_vis) / len(p_vis)) if p_vis else 0,
-                   "tile_list_length_rank0": tile_q,
-                   "l2_policy": "inputs larger than L2 (per-view records + gradients >> 126 MB)",
-                   "linearize_ms": round(linearize_ms, 2), "linearize_cold_ms": round(linearize_cold_ms, 2),
-                   "linearize_warm_passes_ms_and_cudaMallocs": lin_passes,
-                   "view_ids_rank0": F.view_ids if len(F.view_ids) <= 64 else F.view_ids[:64],
-                   "mask_xyz": bool(a.mask_xyz)},
+        # `config` names the workload and is the same dict in both arms (--impl reference prints it too); everything
+        # measured about the workload on this rank lives in `workload_stats`
+        "config": {"workload": workload_name(a, P, V, W, H), "mask_xyz": bool(a.mask_xyz),
+                   "l2_policy": "inputs larger than L2 (per-view records + gradients >> 126 MB)"},
+        "workload_stats": {"views_per_rank": len(F._views),
+                           "instances_total_rank0": R_total, "instances_cached_rank0": R_cached,
+                           "visible_gaussians_per_view_mean_rank0": (sum(p_vis) / len(p_vis)) if p_vis else 0,
+                           "tile_list_length_rank0": tile_q,
+                           "linearize_ms": round(linearize_ms, 2), "linearize_cold_ms": round(linearize_cold_ms, 2),
+                           "linearize_warm_passes_ms_and_cudaMallocs": lin_passes,
+                           "view_ids_rank0": F.view_ids if len(F.view_ids) <= 64 else F.view_ids[:64]},
         "check": check,
         "e2e": {"value": 1e3 / ms_e2e, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": 4 * n_flat,
                 "d2h_bytes_per_step": 4 * n_flat, "per_rank_bytes": moved,
