@@ -45,6 +45,19 @@ def main():
     per = (v.length + world - 1) // world
     lo, hi = rank * per, min((rank + 1) * per, v.length)
     assert torch.equal(back[lo:hi], host[lo:hi]) and (back[:lo] == -1).all() and (back[hi:] == -1).all()
+    # a rank that owns NO view (more ranks than views) must still enter every collective -- loss scalars,
+    # residual-space dots and the parameter-space allreduce -- instead of deadlocking the others
+    lonely = LinearSolverFunctions(loss_func, m, cams[:1], batch_size=1)
+    assert lonely.B == (1 if rank == 0 else 0)
+    one = LinearSolverFunctions(loss_func, m, cams[:1], batch_size=1, shard_views=False)
+    for F in (lonely, one):
+        F.evaluate_loss()
+    assert abs(float(lonely.loss_scalar) - float(one.loss_scalar)) < 1e-5 * float(one.loss_scalar)
+    assert abs(float(lonely.Ll1_scalar) - float(one.Ll1_scalar)) < 1e-5 * float(one.Ll1_scalar)
+    a1, b1 = lonely.normal_matvec(v), one.normal_matvec(v)
+    assert torch.allclose(a1.packed(), b1.packed(), rtol=1e-5, atol=1e-6)
+    J1, J2 = lonely.matvec(v), one.matvec(v)
+    assert abs(lonely.dot(J1, J1) - one.dot(J2, J2)) < 1e-5 * abs(one.dot(J2, J2))
     dist.barrier()
     if rank == 0:
         print("DIST_OK")
