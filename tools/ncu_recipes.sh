@@ -19,7 +19,7 @@ extra=${NCU_EXTRA:-}
 case "$recipe" in
   launches)   # launch list of one bench run: per-kernel SHARE of the step (profiles/*_launches_summary.txt)
     $BENCH > "$out/${tag}_bench_plain.json"
-    ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv $extra \
+    ncu --metrics gpu__time_duration.sum --clock-control none -c 8000 --csv $extra \
         --log-file "$out/${tag}_launches.csv" $BENCH > "$out/${tag}_launches.log" 2>&1
     ;;
   jtjv)       # the dominant kernel, one 16-view launch at config C (profiles/*_jtjv_ncu_full.txt, traffic.json)
