@@ -60,6 +60,23 @@ def products(F, model):
     return out
 
 
+def lm_outcome(dev, ssim):
+    """One whole LM step (train_jvp.py:237-288: linearise, 2 CG iterations, 6-point line search) on a fresh copy of the
+    scene: what a sharded run must reproduce."""
+    from solver.gaussian_model_state import GaussianModelParamGroupMask
+    from solver.lm import lm_step
+    model, cams, loss_func = build(dev, ssim=ssim)
+    with torch.no_grad():
+        gen = torch.Generator().manual_seed(4)
+        model._features_dc.data += 0.2 * torch.randn(model._features_dc.shape, generator=gen).to(dev)
+        model._opacity.data += 0.3 * torch.randn(model._opacity.shape, generator=gen).to(dev)
+    r = lm_step(loss_func, model, cams[:8], val_cams=cams[8:], param_mask=GaussianModelParamGroupMask(mask_xyz=True),
+                cg_iters=2, batch_size=4)
+    return {"lm_start": torch.as_tensor(r["start_loss"]), "lm_val": torch.as_tensor(r["val_loss"]),
+            "lm_alpha": torch.as_tensor(r["best_alpha"]), "lm_step_norm": torch.linalg.vector_norm(r["step"].packed()).cpu(),
+            "lm_trace": torch.tensor([v for _, v in r["trace"]])}
+
+
 def main():
     out_dir = sys.argv[1]
     ssim = len(sys.argv) > 2 and sys.argv[2] == "ssim"
@@ -74,6 +91,7 @@ def main():
     F = LinearSolverFunctions(loss_func, model, cams, batch_size=4)
     assert F.cached and F.dist is not None and F.B == len(cams) // world
     res = products(F, model)
+    res.update(lm_outcome(dev, ssim))
     res["view_ids"] = torch.tensor(F.view_ids)
     res["view_costs"] = torch.tensor(getattr(F, "view_costs", []))
     torch.save(res, os.path.join(out_dir, f"rank{rank}.pt"))

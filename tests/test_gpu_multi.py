@@ -57,3 +57,11 @@ def test_sharded_cached_path_equals_single_gpu(tmp_path, mode):
         assert float(ranks[1][key]) == a, key
         assert abs(a - b) <= 1e-5 * abs(b), (key, a, b)
     assert torch.allclose(ranks[0]["cg_norms"], single["cg_norms"], rtol=1e-3)
+    # a whole LM step (linearise, CG, line search on sharded validation views) lands on the same point
+    lm = w.lm_outcome(dev, mode == "ssim")
+    for key in ("lm_start", "lm_val", "lm_step_norm"):
+        a, b = float(ranks[0][key]), float(lm[key])
+        assert float(ranks[1][key]) == a, key
+        assert abs(a - b) <= 1e-4 * abs(b), (key, a, b)
+    assert float(ranks[0]["lm_alpha"]) == float(ranks[1]["lm_alpha"]) == float(lm["lm_alpha"])
+    assert torch.allclose(ranks[0]["lm_trace"], lm["lm_trace"], rtol=1e-4)
