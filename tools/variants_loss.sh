@@ -1,6 +1,6 @@
 #!/bin/bash
 # usage: tools/variants_loss.sh "<EXTRA flags 1>" "<EXTRA flags 2>" ...   (runs on the GPU box; rebuilds loss_blocks.o per variant)
-cd /root/repo
+cd "$(dirname "$0")/.."
 for v in "$@"; do
   touch gaussian-splatting-lm_b200/csrc/loss_blocks.cu
   make -C gaussian-splatting-lm_b200/csrc EXTRA="$v" -j8 > /dev/null 2>&1 || { echo "build failed: $v"; continue; }
