@@ -41,7 +41,7 @@ template <bool ACC> __device__ __forceinline__ void put(float* p, size_t i, floa
 // PHASED (the dense multi-view kernel): lanes of one warp may hold the SAME Gaussian for different views.  Everything
 // up to the two store sites runs concurrently; at each store site the lanes take turns in view order (`rank` among the
 // lanes with equal idx, `maxrank` its warp maximum, `callmask` the lanes inside this call), so the read-modify-write
-// sequence on a row is exactly the view-by-view sequence of the unphased kernel: same bits.
+// sequence on a row is exactly the view-by-view sequence of the unphased kernel.
 template <bool ACC, bool PHASED = false>
 __device__ __forceinline__ void bwd_gaussian(const BwdArgs& a, const float* __restrict__ sV, const float* __restrict__ sPV,
                                              const float* __restrict__ sCam, int idx, uint32_t callmask = 0xffffffffu,
@@ -499,7 +499,8 @@ k_preprocess_bwd_views(BwdArgs a, const __grid_constant__ BwdBatch vb, int range
 // view-major order (prefix sums of the 16 slice lengths, per warp, in shared memory) and the lanes take 32 consecutive
 // items per pass whatever view they belong to: ~10 full passes instead of 16 two-thirds-empty ones.  Two lanes of a pass
 // can then hold the same Gaussian (for different views): __match_any_sync finds them and the PHASED store sites of
-// bwd_gaussian let them update the row in view order, so the sums are taken in exactly the old order (same bits).
+// bwd_gaussian let them update the row in view order, so the sums are taken in exactly the old order (deterministic;
+// the compiler's fma contraction inside the two instantiations may differ in the last bit).
 // ---------------------------------------------------------------------------------------------
 #ifndef GSLM_BWDV_DENSE
 #define GSLM_BWDV_DENSE 1
