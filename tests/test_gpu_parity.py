@@ -425,3 +425,58 @@ def test_compact_cache_structure(C):
                     assert last == 0
     # derivative-form records: q1.y = log2(opacity kept in q2.w)
     assert torch.allclose(rec[:, 5], torch.log2(rec[:, 11]), atol=1e-5)
+
+
+@pytest.mark.parametrize("deg", [3, 1])
+def test_dense_multi_view_adjoint_with_repeated_views(C, deg):
+    """The dense multi-view adjoint kernel (k_preprocess_bwd_views_dense: SH rows of 16 / 4 coefficients) against the
+    per-view fused calls accumulated in the same order.  Six of the views are the SAME camera, so nearly every Gaussian
+    is held by several lanes of one pass and the phased store sites (rank among equal ids, up to six deep) carry the
+    whole sum; the remaining views mix sizes across the 16-view chunk boundary."""
+    g = ss.make_gaussians(4000, sh_degree=deg, seed=31, scale_mult=0.9)
+    t = ss.random_tangent(g, seed=32)
+    gd, td = h.to_dev(g), h.to_dev(t)
+    rig = ss.hemisphere_rig(9, 128, 96)
+    cams = [rig[2]] * 4 + rig[:5] + [rig[2]] * 2 + rig[5:] + ss.hemisphere_rig(6, 96, 64)
+    assert len(cams) > 16
+    views = []
+    gen = torch.Generator().manual_seed(6)
+    for i, cam in enumerate(cams):
+        ct = h.cam_tensors(cam, bg=(0.0, 0.1, 0.2))
+        R, color, radii, geom, binning, img, invd = h.c_forward(C, gd, ct)
+        w = None if i % 4 == 0 else (torch.rand(color.shape, generator=gen) > 0.2).float().cuda() * 2.0
+        views.append((h.cam_args(ct), radii, geom, R, binning, img, w))
+    P, M = g["means3D"].shape[0], g["shs"].shape[1]
+    assert M % 4 == 0          # the layout the dense kernel's float4 row updates cover
+    zz = lambda *s: torch.zeros(s, device="cuda")
+    mk = lambda: (zz(P, 3), None, zz(P, 1), zz(P, 3), None, zz(P, M, 3), zz(P, 3), zz(P, 4))
+    ref = mk()
+    for v in views:
+        C.jtjv(h.gauss_args(gd), h.tangent_args(td), *v, ref)
+    plan = C.JtjvBatchPlan(views, torch.device("cuda"))
+    out = mk()
+    C.jtjv_batch(h.gauss_args(gd), h.tangent_args(td), plan, out)
+    for name, a, b in zip(("means2D", "", "opacity", "means3D", "", "sh", "scales", "rotations"), out, ref):
+        if a is not None:
+            assert float(b.abs().sum()) > 0, name
+            assert h.relerr(a.cpu().numpy(), b.cpu().numpy()) < 1e-6, name
+    again = mk()
+    C.jtjv_batch(h.gauss_args(gd), h.tangent_args(td), plan, again)
+    for a, b in zip(out, again):
+        if a is not None:
+            assert torch.equal(a, b)
+    # J^T u through the batched backward of the same plan (matvec_T's path) against per-view backward calls
+    cots = [torch.randn((3, v[0][5], v[0][6]), generator=gen).cuda() for v in views]
+    ref_b = mk()
+    for v, cot in zip(views, cots):
+        bgc, vm, pm, tfx, tfy, H, W, campos, aa, dbg = v[0]
+        e = torch.empty(0, device="cuda")
+        C.rasterize_gaussians_backward(bgc, gd["means3D"], v[1], e, gd["opacities"], gd["scales"], gd["rotations"], 1.0, e,
+                                       vm, pm, tfx, tfy, cot, None, gd["shs"], deg, campos, v[2], v[3], v[4], v[5], aa, dbg,
+                                       accumulate_into=tuple(x if x is not None else zz(P, 3 if k == 1 else 6)
+                                                             for k, x in enumerate(ref_b)))
+    out_b = mk()
+    C.backward_batch(h.gauss_args(gd), plan, cots, out_b)
+    for name, a, b in zip(("means2D", "", "opacity", "means3D", "", "sh", "scales", "rotations"), out_b, ref_b):
+        if a is not None:
+            assert h.relerr(a.cpu().numpy(), b.cpu().numpy()) < 1e-6, name
