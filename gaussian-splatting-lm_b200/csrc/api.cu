@@ -7,6 +7,7 @@
 #include <cstddef>
 #include <cstdlib>
 #include <cstring>
+#include <pthread.h>
 #include <vector>
 
 using namespace gslm;
@@ -872,6 +873,73 @@ int32_t gslm_buffer_view(int32_t P, int32_t width, int32_t height, int64_t num_r
         out->n_contrib_c = iv.n_contrib_c; out->cstart = iv.cstart;
     }
     return 0;
+}
+
+// ---- J v with built-in scratch: gslm_jvp_cached_noalloc ---------------------------------------
+// Some hosts of this library have no way to hand us device scratch: a C / Go / Java embedder that links the
+// rasterizer without torch has no device allocator of its own; a process whose framework pool has already claimed
+// all of HBM cannot get more from cudaMalloc; an interactive viewer cannot afford the device-wide synchronisation
+// cudaMalloc / cudaFree imply inside its frame loop.  For them the per-Gaussian tangent records (the only scratch
+// J v needs: 48 B per Gaussian) live in the library image itself.  Every GPU that loads the library carries these
+// GSLM_NOALLOC_MAX_GAUSSIANS * 48 B = 12 MiB until the process exits, used or not.
+static __device__ __align__(256) float4 g_builtin_tangent_records[(size_t)GSLM_NOALLOC_MAX_GAUSSIANS * REC_F4];
+
+// `g_builtin_tangent_records` in HOST code is only the handle the runtime knows the symbol by, not a device
+// address: a kernel given it would fault (or scribble over host memory on systems where the GPU can reach it).
+// The real address differs per device and comes from cudaGetSymbolAddress with that device current.
+static const int MAX_DEVICES = 64;
+static float4* g_builtin_records_addr[MAX_DEVICES];   // [device ordinal] -> device address, 0 = not looked up yet
+static pthread_mutex_t g_builtin_records_lock = PTHREAD_MUTEX_INITIALIZER;
+
+static int builtin_tangent_records(float4** out) {
+    int dev = -1;
+    GSLM_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEVICES) { set_error("device ordinal %d outside 0..%d", dev, MAX_DEVICES - 1); return 1; }
+    pthread_mutex_lock(&g_builtin_records_lock);
+    float4* p = g_builtin_records_addr[dev];
+    if (!p) {
+        void* sym = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&sym, g_builtin_tangent_records);
+        if (e != cudaSuccess || !sym) {
+            pthread_mutex_unlock(&g_builtin_records_lock);
+            set_error("cudaGetSymbolAddress(built-in tangent records) on device %d: %s", dev, cudaGetErrorString(e));
+            return 1;
+        }
+        p = g_builtin_records_addr[dev] = reinterpret_cast<float4*>(sym);
+    }
+    pthread_mutex_unlock(&g_builtin_records_lock);
+    *out = p;
+    return 0;
+}
+
+int32_t gslm_jvp_cached_noalloc(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam,
+                                const int32_t* radii, const void* geom_buffer, const void* binning_buffer,
+                                const void* image_buffer, int32_t num_cached, float* out_color_tangent,
+                                float* out_invdepth_tangent, void* stream) {
+    (void)radii;
+    if (check_inputs(g, cam)) return 1;
+    if (!out_color_tangent || !image_buffer || !binning_buffer || !geom_buffer) { set_error("null argument"); return 1; }
+    if (g->P > GSLM_NOALLOC_MAX_GAUSSIANS) {
+        set_error("gslm_jvp_cached_noalloc: P = %d exceeds the built-in scratch (GSLM_NOALLOC_MAX_GAUSSIANS = %d); "
+                  "use gslm_jvp_cached with caller-provided scratch", g->P, GSLM_NOALLOC_MAX_GAUSSIANS);
+        return 1;
+    }
+    // first call on this device: looks the array's address up (nothing is allocated; the array is part of the
+    // loaded module).  Later calls only read the table.
+    float4* tgeom = nullptr;
+    if (builtin_tangent_records(&tgeom)) return 1;
+    cudaStream_t s = (cudaStream_t)stream;
+    GeomView gv = carve_geom(const_cast<void*>(geom_buffer), g->P);
+    ImageView iv = carve_image(const_cast<void*>(image_buffer), cam->width, cam->height);
+    BinningView bv = carve_binning(const_cast<void*>(binning_buffer), num_cached);
+    TangentPtrs t = make_tangents(gt, nullptr);
+    // Nothing here has to start from zero: the tangent stage writes the record of every Gaussian that is active in
+    // this view, and the tile sweep reads records of cached instances only, all of which are active.  Records left
+    // by an earlier call (another scene, another view) stay in the other rows and are never read.
+    if (launch_preprocess_tangent(*g, t, *cam, gv, tgeom, s)) return 1;
+    if (launch_blend_jvp(bv, iv, cam->width, cam->height, tgeom, cam->bg, nullptr, out_color_tangent,
+                         out_invdepth_tangent, s)) return 1;
+    return debug_sync(cam, s, "jvp_cached_noalloc");
 }
 
 }  // extern "C"

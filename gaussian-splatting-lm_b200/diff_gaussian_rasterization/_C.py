@@ -104,7 +104,7 @@ SLICE_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int32, C.c_int32, C.c_int32)
 EXPORTS = ("gslm_last_error", "gslm_abi_version", "gslm_sizeof", "gslm_camera_offsetof", "gslm_geom_bytes", "gslm_image_bytes", "gslm_binning_bytes", "gslm_binning_temp_bytes",
            "gslm_mark_visible", "gslm_forward", "gslm_render", "gslm_render_batch", "gslm_forward_batch",
            "gslm_count_instances", "gslm_fp32_probe_scratch_bytes", "gslm_fp32_peak_probe", "gslm_forward_jvp", "gslm_backward_scratch_bytes", "gslm_backward",
-           "gslm_jvp_scratch_bytes", "gslm_jvp_cached", "gslm_jtjv_scratch_bytes", "gslm_jtjv",
+           "gslm_jvp_scratch_bytes", "gslm_jvp_cached", "gslm_jvp_cached_noalloc", "gslm_jtjv_scratch_bytes", "gslm_jtjv",
            "gslm_jtjv_batch_scratch_bytes", "gslm_jtjv_batch", "gslm_jtjv_batch_sliced", "gslm_jvp_batch_scratch_bytes",
            "gslm_jvp_batch", "gslm_backward_batch_scratch_bytes", "gslm_backward_batch", "gslm_backward_batch_sliced",
            "gslm_activation_vjp_range", "gslm_loss_lin_bytes", "gslm_loss_blocks",
@@ -146,6 +146,7 @@ def lib():
         L.gslm_forward_jvp.argtypes = [vp, vp, vp, vp, ALLOC_FN, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         L.gslm_backward.argtypes = [vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
         L.gslm_jvp_cached.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp]
+        L.gslm_jvp_cached_noalloc.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp]
         L.gslm_jtjv.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
         L.gslm_jtjv_batch_scratch_bytes.argtypes = [C.c_int32, C.c_int32, vp]
         L.gslm_jtjv_batch.argtypes = [vp, vp, C.c_int32, vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, vp, vp, vp]
@@ -627,6 +628,33 @@ def jvp_cached(gauss_args, tangent_args, cam_args, radii, geomBuffer, R, binning
                              out_t.data_ptr(),
                              _ptr(out_d), _stream()))
     return out_t, out_d
+
+
+NOALLOC_MAX_GAUSSIANS = 262144   # GSLM_NOALLOC_MAX_GAUSSIANS in include/gslm_b200.h
+
+
+def jvp_cached_noalloc(gauss_args, tangent_args, cam_args, radii, geomBuffer, R, binningBuffer, imageBuffer,
+                       out_color_tangent, out_invdepth_tangent=None):
+    """gslm_jvp_cached_noalloc: J v for a linearised view without any device allocation inside the call.  Meant for
+    hosts that cannot give the library scratch memory (no device allocator in their language, HBM already owned by
+    another pool, or a frame loop that must not synchronise on cudaMalloc).  The caller brings the outputs
+    (`out_color_tangent` [3,H,W] float32, optionally `out_invdepth_tangent` [1,H,W]); the tangent records go to a
+    12 MiB array inside the library, shared by every call on the device: keep calls on one stream.  Raises for more
+    than NOALLOC_MAX_GAUSSIANS Gaussians.  Arguments otherwise as jvp_cached."""
+    L = lib()
+    g, k1 = _gaussians(*gauss_args)
+    gt, k3 = _tangent_gaussians(*tangent_args)
+    bg, vm, pm, tfx, tfy, H, W, campos, aa, dbg = cam_args
+    cam, k2 = _camera(bg, vm, pm, tfx, tfy, H, W, campos, False, aa, dbg)
+    assert out_color_tangent.is_cuda and out_color_tangent.dtype == torch.float32 and \
+        out_color_tangent.is_contiguous() and tuple(out_color_tangent.shape) == (3, H, W)
+    if out_invdepth_tangent is not None:
+        assert out_invdepth_tangent.dtype == torch.float32 and out_invdepth_tangent.is_contiguous() and \
+            tuple(out_invdepth_tangent.shape) == (1, H, W)
+    _check(L.gslm_jvp_cached_noalloc(C.addressof(g), C.addressof(gt), C.addressof(cam), _ptr(radii), _ptr(geomBuffer),
+                                     _ptr(binningBuffer), _ptr(imageBuffer), _cached(R, imageBuffer, W, H),
+                                     out_color_tangent.data_ptr(), _ptr(out_invdepth_tangent), _stream()))
+    return out_color_tangent, out_invdepth_tangent
 
 
 def tangent_records(gauss_args, tangent_args, cam_args, geomBuffer, cam_tangent=None):

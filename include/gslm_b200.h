@@ -224,6 +224,27 @@ int32_t gslm_jvp_cached(const GslmGaussians* g, const GslmGaussians* gt, const G
                         int32_t num_cached, void* scratch, float* out_color_tangent, float* out_invdepth_tangent,
                         void* stream);
 
+/* gslm_jvp_cached for callers that cannot supply device scratch.  (No counterpart in the reference: its binding
+ * always allocates through torch.)  Who needs it: an embedder that links this library from C, Go or Java and has no
+ * device allocator at hand; a process whose tensor framework has already taken all of HBM into its own pool, so a
+ * plain cudaMalloc fails; a viewer whose frame loop must not hit the device-wide synchronisation cudaMalloc/cudaFree
+ * bring.  Same arguments and same result as gslm_jvp_cached, bit for bit, minus `scratch`: the per-Gaussian tangent
+ * records (48 B each) go to an array built into the library, which every GPU that loads the library holds until the
+ * process exits (GSLM_NOALLOC_MAX_GAUSSIANS x 48 B = 12 MiB).
+ *  - g->P > GSLM_NOALLOC_MAX_GAUSSIANS is refused with an error naming the limit; nothing is launched.
+ *  - The function calls no cudaMalloc / cudaFree and no allocating library routine.
+ *  - The first call on each device looks the array's device address up (cudaGetSymbolAddress, with that device
+ *    current -- so the device of `stream` must be the current one).  Make that first call outside any stream capture.
+ *  - All calls on a device share the one array, and it keeps whatever the last call wrote.  Nothing in it needs
+ *    clearing between calls (each call writes every record it reads), but two calls that can overlap on the GPU --
+ *    different streams, or two host threads without ordering -- race on it.  Issue them on one stream, or order
+ *    them with events. */
+#define GSLM_NOALLOC_MAX_GAUSSIANS 262144
+int32_t gslm_jvp_cached_noalloc(const GslmGaussians* g, const GslmGaussians* gt, const GslmCamera* cam,
+                                const int32_t* radii, const void* geom_buffer, const void* binning_buffer,
+                                const void* image_buffer, int32_t num_cached, float* out_color_tangent,
+                                float* out_invdepth_tangent, void* stream);
+
 /* Fused Gauss-Newton product for one linearised view, J never materialised:
  *   grads (+)= J^T diag(w) J v      with per-pixel weight image `weight` [3,H,W]
  * (w = residual multiplicity x clamp/alpha mask squared; solver/batch_training_loss.py:10-31,
