@@ -41,36 +41,59 @@ def _dist():
     return None
 
 
-_PEER_CACHE = {}        # (device index, floats) -> _PeerAccumulator; every rank creates them in the same order
+_PEER_CACHE = {}        # device index -> _PeerAccumulator or None (decided once per device, on all ranks alike)
 
 
 class _PeerAccumulator:
     """The rank's activated-space accumulator (59 P floats) as a SYMMETRIC allocation with an NVSwitch multicast
     mapping (torch.distributed._symmetric_memory supplies the allocation, the handle exchange and the cross-rank
-    barrier; the reduction itself is this library's multimem kernel, csrc/peer_reduce.cu)."""
+    barrier; the reduction itself is this library's multimem kernel, csrc/peer_reduce.cu).
+    ONE buffer per device: `view(n)` hands out its first n floats and re-allocates (collectively: every rank sees
+    the same n, P being replicated) only when n outgrows the capacity or falls below a quarter of it, so densification /
+    pruning / a new scene do not pile up rendezvoused buffers."""
+
+    HEADROOM = 1.25         # capacity over the requested size: the Gaussian count drifts between LM steps
 
     def __init__(self, n, dev, dist):
+        self.dev, self.dist = dev, dist
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        self.t = self.hdl = None
+        self.cap = self.mc = 0
+        self._allocate(n)
+
+    def _allocate(self, n):
         import torch.distributed._symmetric_memory as sm
-        self.n = n
-        self.n_pad = (n + 3) // 4 * 4
-        self.t = sm.empty(self.n_pad, dtype=torch.float32, device=dev)
+        self.t = self.hdl = None                    # drop the old buffer before asking for the new one
+        cap = (int(n * self.HEADROOM) + 3) // 4 * 4
+        self.t = sm.empty(cap, dtype=torch.float32, device=self.dev)
         self.t.zero_()
-        self.hdl = sm.rendezvous(self.t, dist.group.WORLD.group_name)
+        self.hdl = sm.rendezvous(self.t, self.dist.group.WORLD.group_name)
         self.mc = int(getattr(self.hdl, "multicast_ptr", 0) or 0)
         if not self.mc:
             raise RuntimeError("no multicast mapping (NVLS) for the symmetric accumulator")
-        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        self.cap = cap
 
-    def allreduce(self):
-        """In place, on the current stream: barrier (all partials written) -> multimem reduce + broadcast of this
-        rank's slice -> barrier (all slices stored)."""
+    def view(self, n):
+        """The first n floats of the buffer.  Views handed out earlier stay valid (several LinearSolverFunctions of
+        different sizes may share the buffer) until a re-allocation; allreduce() refuses a view that outlived one."""
+        if n > self.cap or (n + 3) // 4 * 4 < self.cap // 4:
+            self._allocate(n)
+        return self.t[:n]
+
+    def allreduce(self, flat):
+        """Sum `flat` (a tensor from view()) over the ranks, in place, on the current stream: barrier (all partials
+        written) -> multimem reduce + broadcast of this rank's slice -> barrier (all slices stored)."""
+        if flat.data_ptr() != self.t.data_ptr() or flat.numel() > self.cap:
+            raise RuntimeError("gslm_b200: accumulator view is stale (the symmetric buffer was re-allocated for "
+                               "another size since); linearize again before the next product")
+        n_pad = (flat.numel() + 3) // 4 * 4         # <= cap; the floats past the view are summed too and never read
         self.hdl.barrier(channel=0)
-        _C.multimem_allreduce(self.mc, self.n_pad, self.rank, self.world)
+        _C.multimem_allreduce(self.mc, n_pad, self.rank, self.world)
         self.hdl.barrier(channel=0)
 
 
 def _peer_accumulator(n, dev, dist):
-    """The cached symmetric accumulator, or None when peer memory is disabled (GSLM_PEER_REDUCE=0) or unavailable on
+    """The device's symmetric accumulator, or None when peer memory is disabled (GSLM_PEER_REDUCE=0) or unavailable on
     this box (no NVSwitch multicast): the product then ends in an NCCL allreduce instead."""
     import os
     # measured (profiles/r2l_peer_reduce.txt, 236 MB): 8 GPUs 0.57 ms against NCCL's 0.64; 2 GPUs 0.60 against 0.47 --
@@ -79,14 +102,22 @@ def _peer_accumulator(n, dev, dist):
     mode = os.environ.get("GSLM_PEER_REDUCE", "auto")
     if mode == "0" or dev.type != "cuda" or (mode == "auto" and dist.get_world_size() < 3):
         return None
-    key = (dev.index, n)
+    key = dev.index
     if key not in _PEER_CACHE:
+        acc, why = None, ""
         try:
-            _PEER_CACHE[key] = _PeerAccumulator(n, dev, dist)
-        except Exception as e:      # noqa: BLE001 -- decided identically on every rank of the node
+            acc = _PeerAccumulator(n, dev, dist)
+        except Exception as e:      # noqa: BLE001
+            why = f"{type(e).__name__}: {e}"
+        # the ranks must agree: one rank on NCCL while the others wait in the symmetric-memory barrier would hang
+        ok = torch.tensor([1 if acc is not None else 0], dtype=torch.int32, device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0:
             import warnings
-            warnings.warn(f"gslm_b200: peer-memory reduction unavailable ({type(e).__name__}: {e}); using NCCL")
-            _PEER_CACHE[key] = None
+            warnings.warn("gslm_b200: peer-memory reduction unavailable on at least one rank"
+                          + (f" (here: {why})" if why else "") + "; using NCCL")
+            acc = None
+        _PEER_CACHE[key] = acc
     return _PEER_CACHE[key]
 
 
@@ -532,7 +563,7 @@ class LinearSolverFunctions:
         n = P * (3 + 3 * M + 3 + 4 + 1)
         dev = a["means3D"].device
         self._peer = _peer_accumulator(n, dev, self.dist) if self.dist else None
-        flat = self._peer.t[:n] if self._peer is not None else torch.empty(n, dtype=torch.float32, device=dev)
+        flat = self._peer.view(n) if self._peer is not None else torch.empty(n, dtype=torch.float32, device=dev)
         off = 0
         views = {}
         for name, shape in (("means3D", (P, 3)), ("shs", (P, M, 3)), ("scales", (P, 3)), ("rotations", (P, 4)),
@@ -758,7 +789,7 @@ class _ProductTail:
             # NCCL allreduce where no multicast mapping exists
             peer = getattr(self.F, "_peer", None)
             if peer is not None:
-                peer.allreduce()
+                peer.allreduce(self.flat_all())
             else:
                 dist.all_reduce(self.flat_all())
             self._vjp(g_lo, g_hi)

@@ -60,6 +60,22 @@ def products(F, model):
     return out
 
 
+def one_view_products(dev, model, cams, loss_func):
+    """J^T J v twice in a row and J^T u over ONE view: on two ranks, rank 1 owns no view and must still enter every
+    collective (its accumulator contributes zeros); a smaller-P product would reuse the same symmetric buffer."""
+    from solver.gaussian_model_state import GaussianModelState
+    from solver.solver_functions import LinearSolverFunctions
+    F1 = LinearSolverFunctions(loss_func, model, cams[:1], batch_size=4)
+    F1.evaluate_loss()
+    v = GaussianModelState.from_gaussians(model)
+    v.packed().copy_(torch.randn(v.length, generator=torch.Generator().manual_seed(13)).to(v.packed().device))
+    v.exposure_grad.zero_()
+    first = F1.normal_matvec(v).packed().clone()
+    second = F1.normal_matvec(v).packed().clone()        # back to back on the shared accumulator
+    return {"one_view_n_local": torch.as_tensor(F1.B), "one_view_jtjv": first.cpu(), "one_view_jtjv_again": second.cpu(),
+            "one_view_jtu": F1.matvec_T(-1 * F1.loss).packed().cpu()}
+
+
 def lm_outcome(dev, ssim):
     """One whole LM step (train_jvp.py:237-288: linearise, 2 CG iterations, 6-point line search) on a fresh copy of the
     scene: what a sharded run must reproduce."""
@@ -91,6 +107,13 @@ def main():
     F = LinearSolverFunctions(loss_func, model, cams, batch_size=4)
     assert F.cached and F.dist is not None and F.B == len(cams) // world
     res = products(F, model)
+    # which reduction ended the products: the multimem kernel over the symmetric accumulator (GSLM_PEER_REDUCE=1, or
+    # auto from 3 ranks up) or NCCL
+    res["peer_used"] = torch.as_tensor(getattr(F, "_peer", None) is not None)
+    if res["peer_used"]:
+        from solver import solver_functions as sf
+        assert F._flat_acc.data_ptr() == sf._PEER_CACHE[dev.index].t.data_ptr()
+    res.update(one_view_products(dev, model, cams, loss_func))
     res.update(lm_outcome(dev, ssim))
     res["view_ids"] = torch.tensor(F.view_ids)
     res["view_costs"] = torch.tensor(getattr(F, "view_costs", []))

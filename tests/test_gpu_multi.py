@@ -21,20 +21,27 @@ def _need_two():
 
 
 @pytest.mark.timeout(600)
-@pytest.mark.parametrize("mode", ["l1", "ssim"])
-def test_sharded_cached_path_equals_single_gpu(tmp_path, mode):
+@pytest.mark.parametrize("mode,peer", [("l1", "auto"), ("ssim", "auto"), ("l1", "1")])
+def test_sharded_cached_path_equals_single_gpu(tmp_path, mode, peer):
+    """peer = GSLM_PEER_REDUCE: "auto" ends every product in an NCCL allreduce on two ranks; "1" forces the multimem
+    reduction over the symmetric, multicast-mapped accumulator (csrc/peer_reduce.cu; the default from 3 ranks up), so
+    that path -- aliasing of the accumulator, its two barriers, reuse of one buffer across products -- is compared
+    with the single-GPU result too."""
     _need_two()
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import dist_gpu_worker as w
     from solver.solver_functions import LinearSolverFunctions
     script = os.path.join(ROOT, "tests", "dist_gpu_worker.py")
-    port = "29531" if mode == "l1" else "29533"
-    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=port)
+    port = {"l1auto": "29531", "ssimauto": "29533", "l11": "29535"}[mode + peer]
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=port, GSLM_PEER_REDUCE=peer)
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                           "--master-addr", "127.0.0.1", "--master-port", port, script, str(tmp_path), mode],
                          capture_output=True, text=True, env=env, timeout=560)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     ranks = [torch.load(os.path.join(tmp_path, f"rank{r}.pt")) for r in range(2)]
+    if peer == "1" and not all(bool(r["peer_used"]) for r in ranks):
+        pytest.skip("no NVSwitch multicast mapping on this box: the products fell back to NCCL (all ranks alike)")
+    assert all(bool(r["peer_used"]) == (peer == "1") for r in ranks)
     # single process, all views on one GPU
     dev = torch.device("cuda", 0)
     model, cams, loss_func = w.build(dev, ssim=(mode == "ssim"))
@@ -57,6 +64,14 @@ def test_sharded_cached_path_equals_single_gpu(tmp_path, mode):
         assert float(ranks[1][key]) == a, key
         assert abs(a - b) <= 1e-5 * abs(b), (key, a, b)
     assert torch.allclose(ranks[0]["cg_norms"], single["cg_norms"], rtol=1e-3)
+    # one view on two ranks: rank 1 owns nothing and still enters every collective; two products in a row
+    one = w.one_view_products(dev, model, cams, loss_func)
+    assert [int(r["one_view_n_local"]) for r in ranks] == [1, 0] and int(one["one_view_n_local"]) == 1
+    for key in ("one_view_jtjv", "one_view_jtu"):
+        assert torch.equal(ranks[0][key], ranks[1][key]), f"{key} differs between ranks"
+        assert h.rel_l2(ranks[0][key].numpy(), one[key].numpy()) < 1e-5, key
+    for r in ranks:
+        assert torch.equal(r["one_view_jtjv"], r["one_view_jtjv_again"])
     # a whole LM step (linearise, CG, line search on sharded validation views) lands on the same point
     lm = w.lm_outcome(dev, mode == "ssim")
     for key in ("lm_start", "lm_val", "lm_step_norm"):

@@ -40,12 +40,14 @@ pa = _PeerAccumulator(n, dev, dist)
 # correctness: sum of rank-dependent vectors
 g = torch.Generator(device=dev).manual_seed(7)
 base = torch.randn(n, device=dev, generator=g)
-pa.t[:n].copy_(base * (rank + 1))
-pa.allreduce()
+acc = pa.view(n)
+n_pad = (n + 3) // 4 * 4
+acc.copy_(base * (rank + 1))
+pa.allreduce(acc)
 want = base * (world * (world + 1) / 2)
-err = float((pa.t[:n] - want).abs().max() / want.abs().max())
-t_full = timed(pa.allreduce)
-t_kernel = timed(lambda: _C.multimem_allreduce(pa.mc, pa.n_pad, rank, world))
+err = float((acc - want).abs().max() / want.abs().max())
+t_full = timed(lambda: pa.allreduce(acc))
+t_kernel = timed(lambda: _C.multimem_allreduce(pa.mc, n_pad, rank, world))
 t_barrier = timed(lambda: pa.hdl.barrier(channel=0))
 if rank == 0:
     mb = 4 * n / 1e6
