@@ -98,8 +98,8 @@ static int clear_sinks(const GslmGrads& acc, int P, int M, cudaStream_t s) {
     return 0;
 }
 
-// The per-Gaussian adjoint of one chunk of views.  overwrite: the first chunk of an overwrite-mode product zero-fills
-// inside the kernel.  On the LAST chunk the launch may be cut into n_slices Gaussian ranges with a host callback after
+// The per-Gaussian adjoint of one chunk of views (always accumulating: overwrite-mode products clear the sinks
+// first).  On the LAST chunk the launch may be cut into n_slices Gaussian ranges with a host callback after
 // each (the caller starts the collective / the activation VJP of that slice while the next one is produced).
 // the callbacks a product with NO local views owes its caller (same slice boundaries as adjoint_chunk: a rank without
 // views must still enter the same sequence of collectives as the others)
@@ -116,18 +116,18 @@ static void empty_product_callbacks(int P, int n_slices, GslmSliceFn on_slice, v
 }
 
 static int adjoint_chunk(const GslmGaussians& g, int n, const GslmCamera* cams, const int32_t* const* radii,
-                         const GeomView* gv, const float4* const* inst, const GslmGrads& acc, bool overwrite, bool last,
+                         const GeomView* gv, const float4* const* inst, const GslmGrads& acc, bool last,
                          int n_slices, GslmSliceFn on_slice, void* slice_ctx, cudaStream_t s) {
     const int nranges = (g.P + ACT_RANGE - 1) / ACT_RANGE;
     if (!last || n_slices <= 1) {
-        if (launch_preprocess_bwd_views(g, n, cams, radii, gv, inst, acc, s, 0, nranges, overwrite)) return 1;
+        if (launch_preprocess_bwd_views(g, n, cams, radii, gv, inst, acc, s, 0, nranges)) return 1;
         if (last && on_slice) on_slice(slice_ctx, 0, 0, g.P);
         return 0;
     }
     if (n_slices > nranges) n_slices = nranges;
     for (int k = 0; k < n_slices; k++) {
         const int lo = (int)((int64_t)nranges * k / n_slices), hi = (int)((int64_t)nranges * (k + 1) / n_slices);
-        if (launch_preprocess_bwd_views(g, n, cams, radii, gv, inst, acc, s, lo, hi, overwrite)) return 1;
+        if (launch_preprocess_bwd_views(g, n, cams, radii, gv, inst, acc, s, lo, hi)) return 1;
         if (on_slice) {
             const int64_t g_hi = (int64_t)hi * ACT_RANGE;
             on_slice(slice_ctx, k, lo * ACT_RANGE, (int32_t)(g_hi < g.P ? g_hi : g.P));
@@ -138,7 +138,7 @@ static int adjoint_chunk(const GslmGaussians& g, int n, const GslmCamera* cams, 
 
 // Internal streams ("lanes") of the batched render: small scenes leave most of the GPU idle behind ~25 short launches
 // per view (CUB scans and sorts), so independent views are issued on several streams and overlap.  Created once per
-// host thread; forked from / joined to the caller's stream with events, so the call stays stream-ordered for the caller.
+// host thread and device; forked from / joined to the caller's stream with events, so the call stays stream-ordered for the caller.
 struct LanePool {
     static constexpr int MAX = 4;
     cudaStream_t s[MAX] = {};
@@ -156,9 +156,14 @@ struct LanePool {
         return n < want ? n : want;
     }
 };
-static LanePool& lane_pool() {
-    static thread_local LanePool p;
-    return p;
+// One pool per host thread AND device: streams and events belong to the device that was current when they were
+// created, so a thread that moves to another GPU must not be handed the first one's lanes.
+static LanePool* lane_pool() {
+    static constexpr int MAX_DEV = 64;
+    static thread_local LanePool p[MAX_DEV];
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEV) return nullptr;
+    return &p[dev];
 }
 static int render_lanes(int n_views) {
     static int cfg = -1;
@@ -307,7 +312,9 @@ int32_t gslm_render_batch(const GslmGaussians* g, int32_t n_views, const GslmCam
     const int P = g->P;
     // lanes: views are dealt round robin to K internal streams, each with its own image state and sort scratch
     int K = render_lanes(n_views);
-    LanePool& pool = lane_pool();
+    LanePool* pool_p = lane_pool();
+    if (!pool_p) { set_error("no current CUDA device for the render lanes"); return 1; }
+    LanePool& pool = *pool_p;
     if (K > 1) K = pool.get(K);
     if (K < 1) K = 1;
     const bool lanes = K > 1;
@@ -325,6 +332,13 @@ int32_t gslm_render_batch(const GslmGaussians* g, int32_t n_views, const GslmCam
             GSLM_CUDA_OK(cudaStreamWaitEvent(s, pool.done[k], 0));
         }
         return 0;
+    };
+    // error exit after a fork: the caller is about to release the buffers the lanes may still be working on, and
+    // nothing orders its stream behind them any more -- drain the lanes on the host before reporting the failure
+    auto fail_lanes = [&]() -> int {
+        if (lanes)
+            for (int k = 0; k < K; k++) cudaStreamSynchronize(pool.s[k]);
+        return 1;
     };
     // one geometry allocation: n_views per-view states, the radii of views the caller does not want back, the totals
     const size_t gstride = align_up(gslm_geom_bytes(P)), rstride = align_up((size_t)P * sizeof(int32_t));
@@ -347,15 +361,15 @@ int32_t gslm_render_batch(const GslmGaussians* g, int32_t n_views, const GslmCam
     auto radii_of = [&](int v) { return (radii && radii[v]) ? radii[v] : reinterpret_cast<int32_t*>(rbase + v * rstride); };
     std::vector<uint32_t> R(n_views, 0u);
     if (P > 0) {
-        if (fork_lanes()) return 1;
+        if (fork_lanes()) return fail_lanes();
         for (int v = 0; v < n_views; v++) {
             cudaStream_t ls = lane_stream(v);
             GeomView gv = carve_geom(gbase + v * gstride, P);
-            if (launch_preprocess(*g, cams[v], gv, radii_of(v), ls)) return 1;
-            if (cams[v].tile_culling && run_tile_cull(gv, radii_of(v), P, cams[v].width, cams[v].height, ls)) return 1;
-            if (run_scan(gv, P, ls)) return 1;
+            if (launch_preprocess(*g, cams[v], gv, radii_of(v), ls)) return fail_lanes();
+            if (cams[v].tile_culling && run_tile_cull(gv, radii_of(v), P, cams[v].width, cams[v].height, ls)) return fail_lanes();
+            if (run_scan(gv, P, ls)) return fail_lanes();
         }
-        if (join_lanes()) return 1;
+        if (join_lanes()) return fail_lanes();
         GeomView g0 = carve_geom(gbase, P);
         const size_t off = (size_t)((const char*)(g0.point_offsets + (P - 1)) - gbase);
         k_gather_totals<<<(n_views + 127) / 128, 128, 0, s>>>(gbase, gstride, off, n_views, totals);
@@ -369,22 +383,22 @@ int32_t gslm_render_batch(const GslmGaussians* g, int32_t n_views, const GslmCam
     void* tbuf[LanePool::MAX] = {};
     for (int k = 0; k < K; k++) {
         tbuf[k] = alloc(alloc_ctx, GSLM_BUF_BINNING_TEMP | (k << 8), gslm_binning_temp_bytes(P, Rmax));
-        if (!tbuf[k]) { set_error("allocator returned null"); return 1; }
+        if (!tbuf[k]) { set_error("allocator returned null"); return fail_lanes(); }
     }
-    if (fork_lanes()) return 1;
+    if (fork_lanes()) return fail_lanes();
     for (int v = 0; v < n_views; v++) {
         const GslmCamera& cam = cams[v];
         cudaStream_t ls = lane_stream(v);
         GeomView gv = carve_geom(gbase + v * gstride, P);
         ImageView iv = carve_image(ibuf[v % K], cam.width, cam.height);
         BinningTemp bt = carve_binning_temp(tbuf[v % K], R[v], P);
-        if (run_binning(gv, radii_of(v), bt, iv, P, cam.width, cam.height, R[v], cam.tile_culling != 0, ls)) return 1;
+        if (run_binning(gv, radii_of(v), bt, iv, P, cam.width, cam.height, R[v], cam.tile_culling != 0, ls)) return fail_lanes();
         const float* features = g->colors_precomp ? g->colors_precomp : gv.rgb;
         if (launch_blend_fwd(gv, bt, iv, cam.width, cam.height, features, cam.bg, out_color[v],
-                             out_invdepth ? out_invdepth[v] : nullptr, false, ls)) return 1;
-        if (debug_sync(&cam, ls, "render_batch")) return 1;
+                             out_invdepth ? out_invdepth[v] : nullptr, false, ls)) return fail_lanes();
+        if (debug_sync(&cam, ls, "render_batch")) return fail_lanes();
     }
-    return join_lanes();
+    return join_lanes() ? fail_lanes() : 0;
 }
 
 int32_t gslm_count_instances(const GslmGaussians* g, int32_t n_views, const GslmCamera* cams, GslmAllocFn alloc,
@@ -451,7 +465,9 @@ int32_t gslm_forward_batch(const GslmGaussians* g, int32_t n_views, const GslmCa
     // lanes: views are dealt round robin to K >= 2 internal streams (one sort scratch each); see gslm_render_batch
     int K = render_lanes(n_views);
     if (K < 2 && !stage_timing_enabled()) K = n_views > 1 ? 2 : 1;
-    LanePool& pool = lane_pool();
+    LanePool* pool_p = lane_pool();
+    if (!pool_p) { set_error("no current CUDA device for the render lanes"); return 1; }
+    LanePool& pool = *pool_p;
     if (K > 1) K = pool.get(K);
     if (K < 1) K = 1;
     const bool lanes = K > 1;
@@ -470,18 +486,28 @@ int32_t gslm_forward_batch(const GslmGaussians* g, int32_t n_views, const GslmCa
         }
         return 0;
     };
+    // error exit after a fork: the caller is about to release the buffers the lanes may still be working on, and
+    // nothing orders its stream behind them any more -- drain the lanes on the host before reporting the failure
+    auto fail_lanes = [&]() -> int {
+        if (lanes)
+            for (int k = 0; k < K; k++) cudaStreamSynchronize(pool.s[k]);
+        return 1;
+    };
     // phase 1: every view preprocessed, culled and scanned; ONE synchronisation for all instance counts
     if (P > 0) {
-        if (fork_lanes()) return 1;
+        if (fork_lanes()) return fail_lanes();
         for (int v = 0; v < n_views; v++) {
             cudaStream_t ls = lane_stream(v);
-            if (launch_preprocess(*g, cams[v], gv[v], radii[v], ls)) return 1;
-            if (cams[v].tile_culling && run_tile_cull(gv[v], radii[v], P, cams[v].width, cams[v].height, ls)) return 1;
-            if (run_scan(gv[v], P, ls)) return 1;
-            GSLM_CUDA_OK(cudaMemcpyAsync(R + v, gv[v].point_offsets + (P - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, ls));
+            if (launch_preprocess(*g, cams[v], gv[v], radii[v], ls)) return fail_lanes();
+            if (cams[v].tile_culling && run_tile_cull(gv[v], radii[v], P, cams[v].width, cams[v].height, ls)) return fail_lanes();
+            if (run_scan(gv[v], P, ls)) return fail_lanes();
+            if (cudaMemcpyAsync(R + v, gv[v].point_offsets + (P - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, ls) != cudaSuccess) {
+                set_error("forward_batch: count read-back failed");
+                return fail_lanes();
+            }
         }
-        if (join_lanes()) return 1;
-        GSLM_CUDA_OK(cudaStreamSynchronize(s));
+        if (join_lanes()) return fail_lanes();
+        if (cudaStreamSynchronize(s) != cudaSuccess) { set_error("forward_batch: synchronisation failed"); return fail_lanes(); }
     }
     uint32_t Rmax = 0;
     for (int v = 0; v < n_views; v++) { num_rendered[v] = (int32_t)R[v]; Rmax = R[v] > Rmax ? R[v] : Rmax; }
@@ -531,6 +557,7 @@ int32_t gslm_forward_batch(const GslmGaussians* g, int32_t n_views, const GslmCa
         }
     }
     if (join_lanes()) rc = 1;
+    if (rc) fail_lanes();
     for (int k = 0; k < K; k++) cudaEventDestroy(ev[k]);
     return rc;
 }
@@ -683,11 +710,10 @@ int32_t gslm_jtjv_batch_sliced(const GslmGaussians* g, const GslmGaussians* gt, 
     if (P == 0) return 0;
     TangentPtrs t = make_tangents(gt, nullptr);
     GslmGrads acc = *grads;
-    // overwrite semantics = clear, then accumulate every view.  (cudaMemsetAsync beats zero-filling inside the first
-    // adjoint launch -- kept as launch_preprocess_bwd_views(zero_first) -- by 0.06 ms per product at P = 1M: the
-    // stores delay the start of every warp's dependent chain.)
+    // overwrite semantics = clear, then accumulate every view.  (cudaMemsetAsync beat zero-filling inside the first
+    // adjoint launch by 0.06 ms per product at P = 1M -- the stores delay the start of every warp's dependent
+    // chain -- so that variant was removed.)
     if (!acc.accumulate && clear_sinks(acc, P, g->M, s)) return 1;
-    const bool overwrite = false;
     acc.accumulate = 1;
     if (n_views == 0) {
         empty_product_callbacks(P, n_slices, on_slice, slice_ctx);
@@ -714,7 +740,7 @@ int32_t gslm_jtjv_batch_sliced(const GslmGaussians* g, const GslmGaussians* gt, 
         if (launch_preprocess_tangent_batch(*g, t, n, cams + v0, gv, tgeom, s)) return 1;
         if (launch_blend_jtjv_batch(n, bv, iv, cams + v0, tgeom, weights ? weights + v0 : nullptr, inst, out_vJJv, s))
             return 1;
-        if (adjoint_chunk(*g, n, cams + v0, radii + v0, gv, inst, acc, overwrite && v0 == 0,
+        if (adjoint_chunk(*g, n, cams + v0, radii + v0, gv, inst, acc,
                           v0 + MAX_BATCH_VIEWS >= n_views, n_slices, on_slice, slice_ctx, s)) return 1;
     }
     return 0;
@@ -722,8 +748,9 @@ int32_t gslm_jtjv_batch_sliced(const GslmGaussians* g, const GslmGaussians* gt, 
 
 // ---- batched linear maps on cached linearisations (matvec / matvec_T of the solver) ----
 size_t gslm_jvp_batch_scratch_bytes(int32_t P, int32_t n_views) {
+    if (n_views <= 0) return 0;     // a rank that owns no view (multi-GPU) brings no scratch
     const int n = n_views < MAX_BATCH_VIEWS ? n_views : MAX_BATCH_VIEWS;
-    return (size_t)(n > 0 ? n : 0) * align_up((size_t)P * REC_F4 * sizeof(float4)) + 128;
+    return (size_t)n * align_up((size_t)P * REC_F4 * sizeof(float4)) + 128;
 }
 
 int32_t gslm_jvp_batch(const GslmGaussians* g, const GslmGaussians* gt, int32_t n_views, const GslmCamera* cams,
@@ -807,7 +834,6 @@ int32_t gslm_backward_batch_sliced(const GslmGaussians* g, int32_t n_views, cons
     if (P == 0) return 0;
     GslmGrads acc = *grads;
     if (!acc.accumulate && clear_sinks(acc, P, g->M, s)) return 1;
-    const bool overwrite = false;
     acc.accumulate = 1;
     if (n_views == 0) {
         empty_product_callbacks(P, n_slices, on_slice, slice_ctx);
@@ -829,7 +855,7 @@ int32_t gslm_backward_batch_sliced(const GslmGaussians* g, int32_t n_views, cons
             p += align_up((size_t)num_cached[v] * REC_F4 * sizeof(float4));
         }
         if (launch_blend_bwd_batch(n, bv, iv, cams + v0, dL_dcolor + v0, inst, s)) return 1;
-        if (adjoint_chunk(*g, n, cams + v0, radii + v0, gv, inst, acc, overwrite && v0 == 0,
+        if (adjoint_chunk(*g, n, cams + v0, radii + v0, gv, inst, acc,
                           v0 + MAX_BATCH_VIEWS >= n_views, n_slices, on_slice, slice_ctx, s)) return 1;
     }
     return 0;

@@ -433,24 +433,8 @@ struct BwdBatch { BwdView v[MAX_BATCH_VIEWS]; int n; };
 #ifndef GSLM_BWDV_MINB
 #define GSLM_BWDV_MINB 4   // 128 registers: the per-Gaussian chain needs the ILP (96 registers: 1.52 ms per 16-view launch, 128: 0.95; profiles/r1i_adjoint_variants.txt)
 #endif
-// zero_first != 0: the launch OVERWRITES the sinks -- every warp first zero-fills the rows of its own Gaussian range
-// (coalesced float4 / float stores, L2-resident when the first view's read-modify-write follows), so no memset of the
-// 59 P-float accumulators is needed before the first chunk of a product.
-__device__ __forceinline__ void zero_rows(float* p, size_t row, size_t g_lo, size_t g_hi, int lane) {
-    if (!p) return;
-    float* b = p + row * g_lo;
-    const size_t n = row * (g_hi - g_lo);
-    size_t i = 0;
-    if ((reinterpret_cast<size_t>(b) & 15u) == 0) {
-        const size_t n4 = n >> 2;
-        for (size_t k = lane; k < n4; k += 32) reinterpret_cast<float4*>(b)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-        i = n4 << 2;
-    }
-    for (size_t k = i + lane; k < n; k += 32) b[k] = 0.f;
-}
-
 __global__ void __launch_bounds__(128, GSLM_BWDV_MINB)
-k_preprocess_bwd_views(BwdArgs a, const __grid_constant__ BwdBatch vb, int range_lo, int range_hi, int zero_first) {
+k_preprocess_bwd_views(BwdArgs a, const __grid_constant__ BwdBatch vb, int range_lo, int range_hi) {
     __shared__ float sCamAll[MAX_BATCH_VIEWS][36];   // V[16] | PV[16] | campos[3]
     for (int t = threadIdx.x; t < vb.n * 36; t += blockDim.x) {
         const int v = t / 36, k = t % 36;
@@ -465,18 +449,6 @@ k_preprocess_bwd_views(BwdArgs a, const __grid_constant__ BwdBatch vb, int range
     const int lane = threadIdx.x & 31;
     const int r = range_lo + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (r >= range_hi) return;
-    if (zero_first) {
-        const size_t g_lo = (size_t)r * ACT_RANGE, g_hi = min((size_t)a.P, g_lo + ACT_RANGE);
-        zero_rows(a.g.dL_dmeans2D, 3, g_lo, g_hi, lane);
-        zero_rows(a.g.dL_dcolors, 3, g_lo, g_hi, lane);
-        zero_rows(a.g.dL_dopacity, 1, g_lo, g_hi, lane);
-        zero_rows(a.g.dL_dmeans3D, 3, g_lo, g_hi, lane);
-        zero_rows(a.g.dL_dcov3D, 6, g_lo, g_hi, lane);
-        zero_rows(a.g.dL_dsh, (size_t)3 * a.M, g_lo, g_hi, lane);
-        zero_rows(a.g.dL_dscales, 3, g_lo, g_hi, lane);
-        zero_rows(a.g.dL_drotations, 4, g_lo, g_hi, lane);
-        __syncwarp();   // the rows are re-read by other lanes of this warp below
-    }
     for (int v = 0; v < vb.n; v++) {
         const BwdView& vw = vb.v[v];
         const uint32_t lo = __ldg(vw.act_range + r), hi = __ldg(vw.act_range + r + 1);
@@ -595,7 +567,7 @@ int launch_preprocess_bwd(const GslmGaussians& g, const GslmCamera& cam, const i
 
 int launch_preprocess_bwd_views(const GslmGaussians& g, int n_views, const GslmCamera* cams, const int32_t* const* radii,
                                 const GeomView* gvs, const float4* const* inst_grads, const GslmGrads& grads,
-                                cudaStream_t s, int range_lo, int range_hi, bool zero_first) {
+                                cudaStream_t s, int range_lo, int range_hi) {
     if (g.P == 0 || n_views == 0) return 0;
     if (n_views > MAX_BATCH_VIEWS) { set_error("too many views in one batch"); return 1; }
     BwdArgs a;
@@ -621,12 +593,12 @@ int launch_preprocess_bwd_views(const GslmGaussians& g, int n_views, const GslmC
     StageScope ts(ST_PRE_BWD, s);
     // the dense kernel's phased stores cover the float4 SH-row path only (M % 4 == 0, 16-byte aligned rows) -- every
     // degree-0 / degree-3 layout the solver produces; anything else takes the per-view passes
-    const bool dense = GSLM_BWDV_DENSE && !zero_first &&
+    const bool dense = GSLM_BWDV_DENSE &&
                        (!grads.dL_dsh || !a.shs || ((g.M & 3) == 0 && (reinterpret_cast<size_t>(grads.dL_dsh) & 15u) == 0));
     if (dense)
         k_preprocess_bwd_views_dense<<<(range_hi - range_lo + 3) / 4, 128, 0, s>>>(a, vb, range_lo, range_hi);
     else
-        k_preprocess_bwd_views<<<(range_hi - range_lo + 3) / 4, 128, 0, s>>>(a, vb, range_lo, range_hi, zero_first ? 1 : 0);
+        k_preprocess_bwd_views<<<(range_hi - range_lo + 3) / 4, 128, 0, s>>>(a, vb, range_lo, range_hi);
     GSLM_CUDA_OK(cudaGetLastError());
     return 0;
 }

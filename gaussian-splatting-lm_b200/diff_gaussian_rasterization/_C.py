@@ -464,6 +464,23 @@ class ResidualSpec:
         e.apply_alpha_mask, e.subtract_gt = int(bool(self.apply_alpha_mask)), int(bool(self.subtract_gt))
         return e
 
+    def fill_from(self, color):
+        """The same outputs from an image that did not come out of gslm_forward_batch: the scene without Gaussians,
+        whose all-zero images (DGR/rasterize_points.cu:69,96) forward_batch produces view by view.  Same arithmetic as k_residual_epilogue."""
+        m = ((color >= 0) & (color <= 1)).to(color.dtype)
+        img = color.clamp(0, 1)
+        if self.apply_alpha_mask and self.alpha_mask is not None:
+            am = self.alpha_mask.reshape(1, color.shape[-2], color.shape[-1])
+            img, m = img * am, m * am
+        if self.gt is not None and self.subtract_gt:
+            img = img - self.gt
+        if self.image is not None:
+            self.image.copy_(img)
+        if self.mask is not None:
+            self.mask.copy_(m)
+        if self.weight is not None:
+            self.weight.copy_(float(self.weight_scale) * m * m)
+
 
 def forward_batch(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, views, sh,
                   degree, antialiasing, debug, residual=None, tile_culling=None, want_invdepth=False):
@@ -478,9 +495,13 @@ def forward_batch(background, means3D, colors, opacity, scales, rotations, scale
     if n == 0:
         return []
     if g.P == 0:
-        return [rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
-                                    cov3D_precomp, v[0], v[1], v[2], v[3], v[4], v[5], sh, degree, v[6], False,
-                                    antialiasing, debug, tile_culling) for v in views]
+        out = [rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                                   cov3D_precomp, v[0], v[1], v[2], v[3], v[4], v[5], sh, degree, v[6], False,
+                                   antialiasing, debug, tile_culling) for v in views]
+        for o, spec in zip(out, residual or ()):
+            if spec is not None:
+                spec.fill_from(o[1])        # the caller's residual / mask / weight tensors are torch.empty
+        return out
     cams, keep = _camera_array(background, views, antialiasing, debug, tile_culling)
     sizes = [(int(v[4]), int(v[5])) for v in views]
     colors_out = [torch.empty((3, H, W), dtype=torch.float32, device=dev) for H, W in sizes]

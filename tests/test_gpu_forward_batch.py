@@ -103,6 +103,33 @@ def test_residual_epilogue_matches_the_torch_composition():
         assert torch.equal(cm[i, :, :H, :W], ((color >= 0) & (color <= 1)).float())
 
 
+def test_residual_epilogue_of_a_scene_without_gaussians():
+    """P = 0: the images are all zero, as in the reference (DGR/rasterize_points.cu:69,96: out_color is zero-filled and
+    the rasterizer is not called), and the residual / mask / weight outputs are still written (the solver hands them
+    over uninitialised)."""
+    from diff_gaussian_rasterization import _C
+    sizes = [(72, 40), (48, 56)]
+    views, cams = _views(sizes, 2)
+    e = torch.empty(0, device="cuda")
+    z = lambda *s: torch.zeros(s, device="cuda")
+    bg = torch.tensor([0.25, 1.5, -0.5], device="cuda")
+    gen = torch.Generator(device="cuda").manual_seed(2)
+    specs, keep = [], []
+    for W, H in sizes:
+        gt = torch.rand((3, H, W), device="cuda", generator=gen)
+        am = (torch.rand((1, H, W), device="cuda", generator=gen) > 0.3).float()
+        r, m, w = (torch.full((3, H, W), float("nan"), device="cuda") for _ in range(3))
+        keep.append((gt, am, r, m, w))
+        specs.append(_C.ResidualSpec(image=r, mask=m, weight=w, gt=gt, alpha_mask=am[0], weight_scale=2.0))
+    out = _C.forward_batch(bg, z(0, 3), e, z(0, 1), z(0, 3), z(0, 4), 1.0, e, views, z(0, 16, 3), 3, False, False,
+                           residual=specs, tile_culling=True)
+    for (W, H), o, (gt, am, r, m, w) in zip(sizes, out, keep):
+        color = o[1]
+        assert tuple(color.shape) == (3, H, W) and float(color.abs().max()) == 0.0
+        assert torch.equal(m, am.expand(3, H, W)) and torch.equal(w, 2.0 * m * m)      # 0 lies inside the clamp
+        assert torch.equal(r, -gt)
+
+
 def test_render_batch_lanes_are_bit_identical(monkeypatch):
     """gslm_render_batch on its internal streams == one gslm_render call per view."""
     from diff_gaussian_rasterization import _C
