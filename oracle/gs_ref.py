@@ -18,6 +18,21 @@ def available():
     return os.path.exists(PATH)
 
 
+def variant(name):
+    """A second instance of this module bound to oracle/_ref/libgsref_<name>.so, or None when that library was not
+    built.  "shfix": the reference with the one-line SH-coefficient indexing repair in its forward-mode colour
+    evaluation (oracle/Makefile explains it), the oracle for JVPs at SH degree >= 1."""
+    import importlib.util
+    path = os.path.join(_HERE, "_ref", f"libgsref_{name}.so")
+    if not os.path.exists(path):
+        return None
+    spec = importlib.util.spec_from_file_location(f"gs_ref_{name}", os.path.abspath(__file__))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    m.PATH = path
+    return m
+
+
 def lib():
     global _LIB
     if _LIB is None:

@@ -176,7 +176,7 @@ def test_ref_jvp_shim_reproduces_fixture(RJ, golden):
     assert h.relerr(out["color"].cpu().numpy(), color_ref.cpu().numpy()) < 1e-5     # expf on duals vs the primal kernel's contraction
 
 
-JVP_CASES = [("A", 0, False), ("A", 2, True), ("B", 5, False), ("B", 11, True)]   # SH degree 0: SURVEY F7
+JVP_CASES = [("A", 0, False), ("A", 2, True), ("B", 5, False), ("B", 11, True), ("C", 17, False)]   # SH degree 0: SURVEY F7
 
 
 def _our_jvp(C, gd, td, ct, aa, deg=0, tcam=None):
@@ -198,17 +198,65 @@ def test_jvp_matches_reference_kernels(C, RJ, name, view, aa):
     """gslm_forward_jvp against the reference's forwardJvp on the same inputs and Gaussian-parameter tangents:
     image / inverse-depth tangents rel 1e-3 (north_star), at SH degree 0 (for degree >= 1 the reference's dual SH
     evaluation mis-indexes its coefficients, SURVEY F7, and is not a specification)."""
-    g, cams = ss.make_config(name, sh_degree=0, views=view + 1)
+    _jvp_against(C, RJ, name, view, 0, aa)
+
+
+@pytest.fixture(scope="module")
+def RJX(RJ):
+    """The reference with its forward-mode SH evaluation repaired at build time (sh[k] -> sh1[k] inside
+    computeColorFromSH, forward_impl.h:42-74; oracle/Makefile): every other line is the reference's own."""
+    v = RJ.variant("shfix")
+    if v is None:
+        pytest.skip("oracle/_ref/libgsref_shfix.so not built")
+    v.lib()
+    assert v.has_jvp()
+    return v
+
+
+def test_sh_repaired_reference_is_the_reference_at_degree_0(RJ, RJX):
+    """The build-time repair touches the degree >= 1 terms only: at SH degree 0 both libraries agree bit for bit."""
+    g, cams = ss.make_config("A", sh_degree=0, views=2)
+    t = ss.random_tangent(g, seed=9)
+    gd, td, ct = h.to_dev(g), h.to_dev(t), h.cam_tensors(cams[1], bg=(0.1, 0.2, 0.3))
+    a, b = RJ.forward_jvp(gd, ct, tg=td), RJX.forward_jvp(gd, ct, tg=td)
+    for k in ("color", "color_t", "invdepth", "invdepth_t", "radii"):
+        assert torch.equal(a[k], b[k]), k
+    vis = a["radii"] > 0                    # rows of culled Gaussians are never written (uninitialised in both)
+    assert int(vis.sum()) > 1000
+    for k in ("t_rgb", "t_conic_opacity", "t_means2D", "t_depths", "rgb"):
+        assert torch.equal(a[k][vis], b[k][vis]), k
+
+
+# SH degree 1-3 -- the degrees of the headline benchmark -- on reference code (VERDICT r2, weak 1): config A, B and
+# the full size C (1M Gaussians, 1920x1080)
+JVP_SH_CASES = [("A", 0, 3, False), ("A", 2, 1, True), ("B", 5, 3, False), ("B", 11, 2, True), ("C", 17, 3, False)]
+
+
+@pytest.mark.parametrize("name,view,deg,aa", JVP_SH_CASES)
+def test_jvp_matches_sh_repaired_reference_kernels(C, RJX, name, view, deg, aa):
+    """gslm_forward_jvp at SH degree 1-3 (tangents on every parameter group, SH coefficients included) against the
+    reference's forwardJvp with the repaired coefficient indexing: image / inverse-depth tangents rel 1e-3, and the
+    per-Gaussian records (colour tangents from the degree-`deg` dual SH evaluation among them)."""
+    _jvp_against(C, RJX, name, view, deg, aa)
+
+
+def _jvp_against(C, RJ, name, view, deg, aa):
+    g, cams = ss.make_config(name, sh_degree=deg, views=view + 1)
     cam = cams[view]
     t = ss.random_tangent(g, seed=9)
     gd, td, ct = h.to_dev(g), h.to_dev(t), h.cam_tensors(cam, bg=(0.1, 0.2, 0.3))
     ref = RJ.forward_jvp(gd, ct, tg=td, antialiasing=aa)
-    out = _our_jvp(C, gd, td, ct, aa)
+    out = _our_jvp(C, gd, td, ct, aa, deg=deg)
     R, color, radii, geom, binning, img, invd, color_t, invd_t = out
     # the dual kernel's primal half rounds differently from the plain kernel (no FMA contraction across the dual
     # operators): a radius may move by one on isolated Gaussians
     assert R == ref["R"] and float((radii != ref["radii"]).float().mean()) < 1e-4
-    assert h.relerr(color.cpu().numpy(), ref["color"].cpu().numpy()) < 1e-4
+    # primal image: rel 1e-4 (north_star) in the l2 sense and on all but 1e-5 of the pixels -- against the DUAL
+    # kernel's primal half a hit decision flips on isolated pixels (2 of 2M at config C reach 2.7e-4); the image
+    # itself is held to the max-norm 1e-4 against the reference's plain forward in test_forward_bit_exact_binning_and_image
+    cn, rn = color.cpu().numpy(), ref["color"].cpu().numpy()
+    assert h.rel_l2(cn, rn) < 1e-4 and h.relerr(cn, rn) < 1e-3
+    assert float((np.abs(cn - rn) > 1e-4 * np.abs(rn).max()).mean()) < 1e-5
     rt, rd = ref["color_t"].cpu().numpy(), ref["invdepth_t"].cpu().numpy()
     assert h.rel_l2(color_t.cpu().numpy(), rt) < 1e-3
     assert h.rel_l2(invd_t.cpu().numpy(), rd) < 1e-3
@@ -291,11 +339,23 @@ def test_tangent_records_match_golden_fixture(C, golden):
         assert h.rel_l2(rec[:, k], want[:, k]) < 1e-4, k
 
 
-@pytest.mark.parametrize("name,view,aa", [("A", 1, False), ("B", 3, False), ("B", 9, True)])
+@pytest.mark.parametrize("name,view,aa", [("A", 1, False), ("B", 3, False), ("B", 9, True), ("C", 17, False)])
 def test_fused_jtjv_matches_reference_composition(C, RJ, name, view, aa):
     """The headline product on reference code end to end: J^T (W (J v)) with J v from the reference's forwardJvp and
     J^T from the reference's backward kernels, against ONE call of our fused gslm_jtjv.  rel 1e-3 (north_star)."""
-    g, cams = ss.make_config(name, sh_degree=0, views=view + 1)
+    _fused_against(C, RJ, name, view, 0, aa)
+
+
+@pytest.mark.parametrize("name,view,deg,aa", [("A", 1, 3, False), ("B", 3, 2, False), ("B", 9, 1, True),
+                                              ("C", 17, 3, False)])
+def test_fused_jtjv_matches_sh_repaired_reference_composition(C, RJX, name, view, deg, aa):
+    """The same at SH degree 1-3, the headline configuration (config C, degree 3) included: J v from the repaired
+    forwardJvp, J^T from the reference's (unmodified) backward kernels of the same library."""
+    _fused_against(C, RJX, name, view, deg, aa)
+
+
+def _fused_against(C, RJ, name, view, deg, aa):
+    g, cams = ss.make_config(name, sh_degree=deg, views=view + 1)
     cam = cams[view]
     t = ss.random_tangent(g, seed=13)
     gd, td, ct = h.to_dev(g), h.to_dev(t), h.cam_tensors(cam, bg=(0.0, 0.0, 0.0))
