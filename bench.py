@@ -163,6 +163,97 @@ class ClockSampler(threading.Thread):
 
 
 # --------------------------------------------------------------------------------------- GPU arm
+def render_leg(F, _C, dev, hits_per_view, fp32_peak, world, n_views=8, iters=3):
+    """Render forward + backward, ms per view (BASELINE.json's second metric), on the first `n_views` local views of
+    the workload through the reference-facing per-view calls (_C.rasterize_gaussians -> gslm_forward,
+    _C.rasterize_gaussians_backward -> gslm_backward: rasterize_points.cu:36-141, :300-399), device-timed with CUDA
+    events (median over `iters` passes, max over ranks), then once more with the stage timers on for the two tile
+    kernels' own durations.  Algorithmic flops (on the compact lists as for the fused product): forward
+    12 per tested pair + 18 per hit, backward 12 per tested pair + (18 + 85) per hit (it re-derives the forward
+    quantities of every hit); tested pairs: see the comment at the roofline loop."""
+    import torch
+    import torch.distributed as dist
+    views = F._views[:n_views]
+    if not views:
+        return None
+    a = F._act
+    e = torch.empty(0, device=dev)
+    gen = torch.Generator(device=dev).manual_seed(11)
+    cots = {(vc.H, vc.W): None for vc in views}
+    for k in cots:
+        cots[k] = torch.randn((3,) + k, device=dev, generator=gen)
+
+    def fwd(vc):
+        bg, vm, pm, tfx, tfy, H, W, campos, aa, dbg = vc.cam_args
+        return _C.rasterize_gaussians(bg, a["means3D"], e, a["opacities"], a["scales"], a["rotations"], 1.0, e, vm, pm,
+                                      tfx, tfy, H, W, a["shs"], a["sh_degree"], campos, False, aa, False)
+
+    def bwd(vc, out):
+        bg, vm, pm, tfx, tfy, H, W, campos, aa, dbg = vc.cam_args
+        R, color, radii, geom, binning, img, invd = out
+        return _C.rasterize_gaussians_backward(bg, a["means3D"], radii, e, a["opacities"], a["scales"], a["rotations"],
+                                               1.0, e, vm, pm, tfx, tfy, cots[(H, W)], e, a["shs"], a["sh_degree"],
+                                               campos, geom, R, binning, img, aa, False)
+
+    def one_pass(timed_events):
+        tf = tb = 0.0
+        for vc in views:
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            ev[0].record()
+            out = fwd(vc)
+            ev[1].record()
+            g = bwd(vc, out)
+            ev[2].record()
+            torch.cuda.synchronize()
+            tf += ev[0].elapsed_time(ev[1])
+            tb += ev[1].elapsed_time(ev[2])
+            del out, g
+        return tf / len(views), tb / len(views)
+
+    one_pass(False)
+    one_pass(False)
+    runs = sorted(one_pass(True) for _ in range(iters))
+    t = torch.tensor(runs[len(runs) // 2], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_f, ms_b = float(t[0]), float(t[1])
+    _C.timing_enable(True)
+    _C.timing_collect()
+    one_pass(False)
+    st = _C.timing_collect()
+    _C.timing_enable(False)
+    rc = sum(int(vc.R.cached) for vc in views)
+    hv = sum(hits_per_view[:len(views)])
+    # pairs the forward sweep tests: every pixel walks its tile's FULL depth-sorted list up to its last contributor
+    # (n_contrib, forward.cu:330-395) -- the linearisation cache does not exist yet when it runs; the backward sweep
+    # runs on the compact lists the forward left (256 per cached instance, the conservative count of the fused product)
+    P = a["means3D"].shape[0]
+    tested_fwd = 0
+    for vc in views:
+        out = fwd(vc)
+        tested_fwd += int(_C.buffer_view(P, vc.W, vc.H, out[0], None, None, out[5])["n_contrib"].sum())
+        del out
+    roofs = {}
+    for name, key, tested, per_hit in (("k_blend_fwd_warp", "blend_fwd", tested_fwd, 18.0),
+                                       ("k_blend_bwd", "blend_bwd", 256 * rc, 18.0 + 85.0)):
+        ms, n = st.get(key, (0.0, 0))
+        if not n:
+            continue
+        flops = (12.0 * tested + per_hit * hv) / len(views)          # per launch = per view
+        launch_s = ms / n * 1e-3
+        tf = flops / launch_s / 1e12
+        roofs[name] = {"bound": "fp32", "achieved": tf, "peak": fp32_peak, "unit": "TFLOP/s",
+                       "frac": tf / fp32_peak if fp32_peak else 0.0, "launch_ms": ms / n,
+                       "alg_flops_per_launch": flops, "pairs_tested_per_launch": tested / len(views),
+                       "pairs_hit_per_launch": hv / len(views), "traffic": None}
+    return {"metric": "render fwd+bwd ms/view", "unit": "ms/view", "higher_is_better": False,
+            "value": ms_f + ms_b, "forward_ms": ms_f, "backward_ms": ms_b, "views_timed": len(views),
+            "api": "one gslm_forward + one gslm_backward call per view (two host read-backs in the forward: the "
+                   "instance count and the compact count); the batched forward (gslm_forward_batch) is what the solver uses",
+            "stage_ms_per_view": {k: round(ms / len(views), 4) for k, (ms, c) in st.items() if c},
+            "roofline": roofs}
+
+
 def main():
     a = parse()
     if a.impl == "reference":
@@ -372,12 +463,16 @@ def main():
     # what actually binds it: FP32 issue / FMA pipe.  Algorithmic flops: 24 per tested (pixel, instance)
     # pair + 154 per hit, on the compact lists: tested = 256 per cached instance, hits = popcount of the hit masks.
     hits = 0
+    hits_per_view = []
     for vc in F._views:
         m = _C.buffer_view(P, vc.W, vc.H, vc.R, None, vc.binning, vc.img).get("masks")
+        hv = 0
         if m is not None:
             x = m.view(torch.uint8)
             lut = torch.tensor([bin(i).count("1") for i in range(256)], dtype=torch.int64, device=dev)
-            hits += int(lut[x.long()].sum())
+            hv = int(lut[x.long()].sum())
+        hits_per_view.append(hv)
+        hits += hv
     alg_flops = (24.0 * 256 * R_cached + 154.0 * hits) / launches
     if a.ssim:
         alg_flops = pix * 3 * (3 * 44.0 + 8) * 2 / launches       # 3 separable 11-tap blurs (22 FMA) + epilogue
@@ -386,6 +481,7 @@ def main():
     probe = {name: round(_C.fp32_peak_probe(mode, dev)[0], 2) for mode, name in
              ((0, "scalar_ffma"), (1, "ffma2_3reg"), (2, "ffma2_3reg_mufu"))}
     fp32_peak = probe["scalar_ffma"]
+    render = None if a.ssim else render_leg(F, _C, dev, hits_per_view, fp32_peak, world)
     traffic = None
     executed = None
     tj = os.path.join(ROOT, "profiles", "traffic.json")   # counters of the same kernel from the ncu --set full capture
@@ -431,6 +527,9 @@ def main():
                     "matches_device_result": e2e_equal,
                     "note": "same copies every step, double-buffered: the H2D of step k+1 and the D2H of step k-1 "
                             "overlap the kernels of step k (solver.HostPipeline); valid for independent products only"}},
+        # the second half of BASELINE.json's metric: rasterizer forward / backward per view through the per-view
+        # entry points the reference binding maps to (gslm_forward / gslm_backward), with the blend kernels' rooflines
+        "render_fwd_bwd": render,
         "gpu_launches": int(launches_per_step) * a.steps,
         "stage_ms_per_step": stage_share,
     }
