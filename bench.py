@@ -175,6 +175,8 @@ def render_leg(F, _C, dev, hits_per_view, fp32_peak, world, n_views=8, iters=3):
     import torch.distributed as dist
     views = F._views[:n_views]
     if not views:
+        if world > 1:       # a rank without views still enters the collective of the others
+            dist.all_reduce(torch.zeros(2, device=dev, dtype=torch.float64), op=dist.ReduceOp.MAX)
         return None
     a = F._act
     e = torch.empty(0, device=dev)
